@@ -1,0 +1,156 @@
+"""ctypes bindings of include/b200_kernels.h (the C ABI of libb200_kernels.so).
+
+Used by the parity tests and smoke(): device memory comes from torch (plumbing only), every
+compute call goes through the C entry points.  No fallback: a missing library raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+from . import KERNELS_SO
+
+F32, F16, Q4_0, Q8_0, Q8_1, Q4_K, Q6_K, I32, I64, BF16, MXFP4 = 0, 1, 2, 8, 9, 12, 14, 26, 27, 30, 39
+GLU_NONE, GLU_REGLU, GLU_GEGLU, GLU_SWIGLU, GLU_SWIGLU_OAI, GLU_GEGLU_ERF, GLU_GEGLU_QUICK = -1, 0, 1, 2, 3, 4, 5
+
+
+class Tensor(C.Structure):
+    _fields_ = [("data", C.c_void_p), ("type", C.c_int32), ("_pad", C.c_int32),
+                ("ne", C.c_int64 * 4), ("nb", C.c_int64 * 4)]
+
+
+class MmvqArgs(C.Structure):
+    _fields_ = [("w", Tensor), ("xq", C.c_void_p), ("xq_ne0_padded", C.c_int64), ("x_ne", C.c_int64 * 4),
+                ("dst", Tensor), ("ids", C.POINTER(Tensor)), ("bias", C.POINTER(Tensor)),
+                ("gate_w", C.POINTER(Tensor)), ("gate_bias", C.POINTER(Tensor)),
+                ("glu_op", C.c_int32), ("glu_alpha", C.c_float), ("glu_limit", C.c_float)]
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load libb200_kernels.so (built in-tree by csrc/Makefile). Raises if absent."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(KERNELS_SO):
+            raise RuntimeError(f"{KERNELS_SO} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                               "(there is no CPU fallback)")
+        L = C.CDLL(KERNELS_SO)
+        L.b200_last_error.restype = C.c_char_p
+        L.b200_launch_count.restype = C.c_uint64
+        L.b200_type_size.restype = C.c_size_t
+        L.b200_type_size.argtypes = [C.c_int]
+        L.b200_blck_size.restype = C.c_int64
+        L.b200_blck_size.argtypes = [C.c_int]
+        L.b200_row_size.restype = C.c_size_t
+        L.b200_row_size.argtypes = [C.c_int, C.c_int64]
+        L.b200_q8_1_buffer_size.restype = C.c_size_t
+        L.b200_q8_1_buffer_size.argtypes = [C.POINTER(Tensor), C.c_int64]
+        L.b200_quantize_q8_1.argtypes = [C.POINTER(Tensor), C.c_void_p, C.c_int64, C.c_void_p]
+        L.b200_mmvq_supported.argtypes = [C.POINTER(MmvqArgs)]
+        L.b200_mul_mat_vec_q.argtypes = [C.POINTER(MmvqArgs), C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        raise RuntimeError(f"{what}: b200 error {rc}: {lib().b200_last_error().decode()}")
+
+
+def row_size(ttype: int, ne0: int) -> int:
+    return lib().b200_row_size(ttype, ne0)
+
+
+def make_tensor(ptr: int, ttype: int, ne, nb=None) -> Tensor:
+    """Descriptor for `ptr` with ggml shape `ne` (ne[0] fastest); contiguous strides by default."""
+    ne = list(ne) + [1] * (4 - len(ne))
+    t = Tensor()
+    t.data = ptr
+    t.type = ttype
+    if nb is None:
+        ts = lib().b200_type_size(ttype)
+        nb = [ts, lib().b200_row_size(ttype, ne[0])]
+        nb.append(nb[1] * ne[1])
+        nb.append(nb[2] * ne[2])
+    for i in range(4):
+        t.ne[i] = ne[i]
+        t.nb[i] = nb[i]
+    return t
+
+
+_TORCH_TYPE = None
+
+
+def from_torch(x, ttype: int | None = None, ne=None) -> Tensor:
+    """Descriptor of a contiguous CUDA torch tensor. Quantized data is a uint8 tensor + explicit (ttype, ne)."""
+    import torch
+    assert x.is_cuda and x.is_contiguous()
+    if ttype is None:
+        ttype = {torch.float32: F32, torch.float16: F16, torch.int32: I32, torch.int64: I64, torch.bfloat16: BF16}[x.dtype]
+        ne = list(reversed(x.shape))
+    return make_tensor(x.data_ptr(), ttype, ne)
+
+
+def stream_ptr() -> int:
+    import torch
+    return torch.cuda.current_stream().cuda_stream
+
+
+def quantize_q8_1(x, ne0_padded: int | None = None):
+    """x: CUDA f32 torch tensor [..., K] -> uint8 tensor of q8_1 blocks [rows, K_pad/32*36]."""
+    import torch
+    K = x.shape[-1]
+    if ne0_padded is None:
+        ne0_padded = -(-K // 32) * 32
+    tx = from_torch(x)
+    rows = x.numel() // K
+    y = torch.empty(rows * (ne0_padded // 32) * 36, dtype=torch.uint8, device=x.device)
+    check(lib().b200_quantize_q8_1(C.byref(tx), y.data_ptr(), ne0_padded, stream_ptr()), "quantize_q8_1")
+    return y.view(rows, -1)
+
+
+def mul_mat_vec_q(w_bytes, wtype: int, w_ne, x, ids=None, bias=None, gate_bytes=None, gate_bias=None,
+                  glu_op: int = GLU_NONE, alpha: float = 1.702, limit: float = 7.0, ne0_padded: int | None = None,
+                  w_nb=None):
+    """dst = W . x through b200_quantize_q8_1 + b200_mul_mat_vec_q.
+
+    w_bytes: CUDA uint8 tensor with packed weights of ggml shape w_ne = [K, M, ne02, ne03];
+    x: CUDA f32 tensor of torch shape [ne13, ne12, ne11, K] (or fewer leading dims);
+    ids: CUDA int32 tensor [n_tokens, n_used] for MUL_MAT_ID.  Returns f32 dst (torch layout).
+    """
+    import torch
+    K = x.shape[-1]
+    xs = [1] * (4 - x.dim()) + list(x.shape)       # [ne13, ne12, ne11, K]
+    if ne0_padded is None:
+        ne0_padded = -(-K // 512) * 512
+    xq = quantize_q8_1(x, ne0_padded)
+    a = MmvqArgs()
+    a.w = make_tensor(w_bytes.data_ptr(), wtype, w_ne, w_nb)
+    a.xq = xq.data_ptr()
+    a.xq_ne0_padded = ne0_padded
+    for i, v in enumerate([K, xs[2], xs[1], xs[0]]):
+        a.x_ne[i] = v
+    M = w_ne[1]
+    if ids is not None:
+        n_tok, n_used = ids.shape
+        dst = torch.empty(n_tok, n_used, M, dtype=torch.float32, device=x.device)
+        tids = from_torch(ids)
+        a.ids = C.pointer(tids)
+    else:
+        dst = torch.empty(xs[0], xs[1], xs[2], M, dtype=torch.float32, device=x.device)
+    a.dst = from_torch(dst)
+    keep = []
+    for name, t in (("bias", bias), ("gate_bias", gate_bias)):
+        if t is not None:
+            d = from_torch(t)
+            keep.append(d)
+            setattr(a, name, C.pointer(d))
+    if gate_bytes is not None:
+        g = make_tensor(gate_bytes.data_ptr(), wtype, w_ne, w_nb)
+        keep.append(g)
+        a.gate_w = C.pointer(g)
+    a.glu_op, a.glu_alpha, a.glu_limit = glu_op, alpha, limit
+    check(lib().b200_mul_mat_vec_q(C.byref(a), stream_ptr()), "mul_mat_vec_q")
+    return dst

@@ -1,0 +1,231 @@
+// mmvq.cu — K4: quantized GEMV for decode MUL_MAT / MUL_MAT_ID (C-ABI b200_mul_mat_vec_q).
+// Replaces ggml_cuda_mul_mat_vec_q (reference ggml-cuda/mmvq.cu:638-736).
+//
+//   MUL_MAT    : dst[m,n,c,s] = sum_k W[k,m,c/r2,s/r3] * x[k,n,c,s]         (n = ne11 <= 8)
+//   MUL_MAT_ID : dst[m,e,t]   = sum_k W[k,m,ids[e,t]]  * x[k,e % ne11,t]    (one column per (e,t))
+//
+// This file holds the GENERIC kernel: any strides, batch/broadcast, ids, fused bias/gate/GLU,
+// byte-granular loads, one warp per output row.  The streaming fast path for contiguous decode
+// weights lives in mmvq_stream.cu and is selected by the launcher below when it applies.
+#include "vecdot.cuh"
+
+namespace b200 {
+
+struct mmvq_params {
+    const uint8_t * w; const uint8_t * gate_w;
+    const blk_q8_1 * xq;
+    float * dst;
+    const int32_t * ids;
+    const float * bias; const float * gate_bias;
+    int64_t K, M;
+    int64_t w_nb1, w_nb2, w_nb3;
+    int64_t xq_col, xq_chan, xq_samp;      // strides in q8_1 blocks
+    int64_t dst_col, dst_chan, dst_samp;   // strides in floats
+    int64_t ids_nb1;                       // ids stride between tokens, in i32 elements
+    int64_t bias_chan;                     // bias stride per expert (MUL_MAT_ID), floats
+    int32_t ne11;                          // activation channels per token (MUL_MAT_ID broadcast)
+    int32_t r2, r3;                        // broadcast ratios ne12/ne02, ne13/ne03
+    int32_t glu_op; float glu_alpha, glu_limit;
+};
+
+__device__ __forceinline__ float apply_glu(int op, float g, float x, float alpha, float limit) {
+    switch (op) {
+        case B200_GLU_REGLU:  return fmaxf(g, 0.0f) * x;
+        case B200_GLU_GEGLU: {
+            const float c = 0.79788456080286535587989211986876f, a = 0.044715f;
+            return 0.5f * g * (1.0f + tanhf(c * g * (1.0f + a * g * g))) * x;
+        }
+        case B200_GLU_SWIGLU: return g / (1.0f + expf(-g)) * x;
+        case B200_GLU_SWIGLU_OAI: {
+            g = fminf(g, limit);
+            x = fmaxf(fminf(x, limit), -limit);
+            return g / (1.0f + expf(-g * alpha)) * (1.0f + x);
+        }
+        case B200_GLU_GEGLU_ERF:   return 0.5f * g * (1.0f + erff(g * 0.70710678118654752440f)) * x;
+        case B200_GLU_GEGLU_QUICK: return g / (1.0f + expf(-1.702f * g)) * x;
+        default: return x;
+    }
+}
+
+// grid: (ceil(M/NW), channels, samples|tokens); block: (32, NW). One warp = one row, NCOLS columns.
+template <int TYPE, int NCOLS, bool IDS, bool FUSED, int NW>
+__global__ void __launch_bounds__(32 * NW) mmvq_generic_kernel(const mmvq_params p) {
+    using F = fmt<TYPE>;
+    pdl_launch_dependents();
+    const int lane = threadIdx.x;
+    const int64_t row = (int64_t) blockIdx.x * NW + threadIdx.y;
+    const int chan = blockIdx.y, samp = blockIdx.z;
+    if (row >= p.M) return;   // whole warp exits together
+
+    pdl_wait();
+    int64_t w_off, x_off, bias_off = 0;
+    if (IDS) {   // chan = expert slot e, samp = token t
+        const int expert = p.ids[chan + (int64_t) samp * p.ids_nb1];
+        w_off = (int64_t) expert * p.w_nb2;
+        x_off = (int64_t) (chan % p.ne11) * p.xq_chan + (int64_t) samp * p.xq_samp;
+        bias_off = (int64_t) expert * p.bias_chan;
+    } else {
+        w_off = (int64_t) (chan / p.r2) * p.w_nb2 + (int64_t) (samp / p.r3) * p.w_nb3;
+        x_off = (int64_t) chan * p.xq_chan + (int64_t) samp * p.xq_samp;
+    }
+    const uint8_t * wrow = p.w + w_off + row * p.w_nb1;
+    const uint8_t * grow = FUSED && p.gate_w ? p.gate_w + w_off + row * p.w_nb1 : nullptr;
+    const blk_q8_1 * x = p.xq + x_off;
+
+    float acc[NCOLS], accg[NCOLS];
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) { acc[c] = 0.0f; accg[c] = 0.0f; }
+
+    const int64_t nunits = p.K / 32;
+    for (int64_t u = lane; u < nunits; u += 32) {
+        unit_w w;
+        F::unpack(wrow, u, w);
+#pragma unroll
+        for (int c = 0; c < NCOLS; ++c) acc[c] += unit_dot<F::has_min>(w, x + c * p.xq_col + u);
+        if (FUSED && grow) {
+            F::unpack(grow, u, w);
+#pragma unroll
+            for (int c = 0; c < NCOLS; ++c) accg[c] += unit_dot<F::has_min>(w, x + c * p.xq_col + u);
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) {
+        acc[c] = warp_sum(acc[c]);
+        if (FUSED && grow) accg[c] = warp_sum(accg[c]);
+    }
+    if (lane == 0) {
+        float * d = p.dst + (int64_t) chan * p.dst_chan + (int64_t) samp * p.dst_samp + row;
+#pragma unroll
+        for (int c = 0; c < NCOLS; ++c) {
+            float r = acc[c];
+            if (FUSED) {
+                if (p.bias) r += p.bias[bias_off + row];
+                if (grow) {
+                    float g = accg[c];
+                    if (p.gate_bias) g += p.gate_bias[bias_off + row];
+                    r = apply_glu(p.glu_op, g, r, p.glu_alpha, p.glu_limit);   // glu(gate) * up
+                }
+            }
+            d[c * p.dst_col] = r;
+        }
+    }
+}
+
+template <int TYPE, int NCOLS>
+static int launch_generic(const mmvq_params & p, bool ids, bool fused, dim3 grid_cs, cudaStream_t st) {
+    constexpr int NW = 4;
+    dim3 grid((unsigned) ((p.M + NW - 1) / NW), grid_cs.y, grid_cs.z), block(32, NW);
+    if (ids) {
+        if (NCOLS != 1) return B200_ERR_UNSUPPORTED;
+        if (fused) mmvq_generic_kernel<TYPE, 1, true, true, NW><<<grid, block, 0, st>>>(p);
+        else       mmvq_generic_kernel<TYPE, 1, true, false, NW><<<grid, block, 0, st>>>(p);
+    } else {
+        if (fused) mmvq_generic_kernel<TYPE, NCOLS, false, true, NW><<<grid, block, 0, st>>>(p);
+        else       mmvq_generic_kernel<TYPE, NCOLS, false, false, NW><<<grid, block, 0, st>>>(p);
+    }
+    count_launch();
+    return check_launch("mmvq_generic");
+}
+
+template <int TYPE>
+static int launch_type(const mmvq_params & p, int ncols, bool ids, bool fused, dim3 g, cudaStream_t st) {
+    switch (ncols) {
+        case 1: return launch_generic<TYPE, 1>(p, ids, fused, g, st);
+        case 2: return launch_generic<TYPE, 2>(p, ids, fused, g, st);
+        case 3: return launch_generic<TYPE, 3>(p, ids, fused, g, st);
+        case 4: return launch_generic<TYPE, 4>(p, ids, fused, g, st);
+        case 5: return launch_generic<TYPE, 5>(p, ids, fused, g, st);
+        case 6: return launch_generic<TYPE, 6>(p, ids, fused, g, st);
+        case 7: return launch_generic<TYPE, 7>(p, ids, fused, g, st);
+        case 8: return launch_generic<TYPE, 8>(p, ids, fused, g, st);
+        default: return B200_ERR_UNSUPPORTED;
+    }
+}
+
+int mmvq_stream_try(const b200_mmvq_args * a, void * stream);   // mmvq_stream.cu; B200_ERR_UNSUPPORTED if n/a
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_mmvq_supported(const b200_mmvq_args * a) {
+    if (!a) return 0;
+    const b200_tensor & w = a->w; const b200_tensor & d = a->dst;
+    switch (w.type) { case B200_Q4_0: case B200_Q8_0: case B200_MXFP4: case B200_Q4_K: case B200_Q6_K: break; default: return 0; }
+    const int64_t K = w.ne[0], M = w.ne[1];
+    if (K <= 0 || M <= 0 || K % b200_blck_size(w.type) != 0 || K != a->x_ne[0]) return 0;
+    if (w.nb[0] != (int64_t) b200_type_size(w.type) || d.type != B200_F32 || d.nb[0] != 4 || d.ne[0] != M) return 0;
+    if (a->xq_ne0_padded % 32 != 0 || a->xq_ne0_padded < K) return 0;
+    if (a->ids) {
+        const b200_tensor & ids = *a->ids;   // [n_used, n_tokens]
+        if (ids.type != B200_I32 || ids.nb[0] != 4 || ids.nb[1] % 4 != 0) return 0;
+        if (d.ne[1] != ids.ne[0] || d.ne[2] != ids.ne[1] || d.ne[3] != 1 || w.ne[3] != 1) return 0;
+        if (a->x_ne[2] != d.ne[2] || (a->x_ne[1] != 1 && a->x_ne[1] != d.ne[1]) || a->x_ne[3] != 1) return 0;
+        if (d.ne[1] > 65535 || d.ne[2] > 65535) return 0;
+    } else {
+        if (a->x_ne[1] < 1 || a->x_ne[1] > 8 || d.ne[1] != a->x_ne[1]) return 0;
+        if (d.ne[2] != a->x_ne[2] || d.ne[3] != a->x_ne[3]) return 0;
+        if (w.ne[2] < 1 || w.ne[3] < 1 || d.ne[2] % w.ne[2] != 0 || d.ne[3] % w.ne[3] != 0) return 0;
+        if (d.ne[2] > 65535 || d.ne[3] > 65535) return 0;
+    }
+    if (a->gate_w) {
+        const b200_tensor & g = *a->gate_w;
+        if (g.type != w.type) return 0;
+        for (int i = 0; i < 4; ++i) if (g.ne[i] != w.ne[i] || g.nb[i] != w.nb[i]) return 0;
+        if (a->glu_op < B200_GLU_REGLU || a->glu_op > B200_GLU_GEGLU_QUICK) return 0;
+    }
+    if (a->bias || a->gate_w) {   // fused epilogue: single column per (channel)
+        if (a->ids ? d.ne[2] != 1 : d.ne[1] != 1) return 0;
+        if (!a->ids && (d.ne[2] != 1 || d.ne[3] != 1)) return 0;
+    }
+    if (a->bias && (a->bias->type != B200_F32 || a->bias->ne[0] != M || a->bias->nb[0] != 4)) return 0;
+    if (a->gate_bias && (!a->gate_w || a->gate_bias->type != B200_F32 || a->gate_bias->ne[0] != M || a->gate_bias->nb[0] != 4)) return 0;
+    return 1;
+}
+
+extern "C" int b200_mul_mat_vec_q(const b200_mmvq_args * a, void * stream) {
+    if (!b200_mmvq_supported(a)) { set_error("b200_mul_mat_vec_q: unsupported arguments"); return B200_ERR_UNSUPPORTED; }
+    const b200_tensor & w = a->w; const b200_tensor & d = a->dst;
+    if (nelements(d) == 0) return B200_OK;
+
+    const int rs = mmvq_stream_try(a, stream);
+    if (rs != B200_ERR_UNSUPPORTED) return rs;
+
+    mmvq_params p{};
+    p.w = (const uint8_t *) w.data; p.gate_w = a->gate_w ? (const uint8_t *) a->gate_w->data : nullptr;
+    p.xq = (const blk_q8_1 *) a->xq; p.dst = (float *) d.data;
+    p.ids = a->ids ? (const int32_t *) a->ids->data : nullptr;
+    p.bias = a->bias ? (const float *) a->bias->data : nullptr;
+    p.gate_bias = a->gate_bias ? (const float *) a->gate_bias->data : nullptr;
+    p.K = w.ne[0]; p.M = w.ne[1];
+    p.w_nb1 = w.nb[1]; p.w_nb2 = w.nb[2]; p.w_nb3 = w.nb[3];
+    const int64_t bpr = a->xq_ne0_padded / 32;   // q8_1 layout: [bpr, ne11, ne12, ne13]
+    const int64_t x1 = bpr, x2 = bpr * a->x_ne[1], x3 = x2 * a->x_ne[2];
+    p.glu_op = a->glu_op; p.glu_alpha = a->glu_alpha; p.glu_limit = a->glu_limit;
+    const bool fused = a->bias || a->gate_w;
+    int ncols; dim3 g(1, 1, 1);
+    if (a->ids) {
+        ncols = 1;
+        p.xq_col = 0; p.xq_chan = x1; p.xq_samp = x2;
+        p.dst_col = 0; p.dst_chan = d.nb[1] / 4; p.dst_samp = d.nb[2] / 4;
+        p.ids_nb1 = a->ids->nb[1] / 4; p.ne11 = (int32_t) a->x_ne[1];
+        p.bias_chan = a->bias ? a->bias->nb[1] / 4 : (a->gate_bias ? a->gate_bias->nb[1] / 4 : 0);
+        p.r2 = p.r3 = 1;
+        g.y = (unsigned) d.ne[1]; g.z = (unsigned) d.ne[2];
+    } else {
+        ncols = (int) a->x_ne[1];
+        p.xq_col = x1; p.xq_chan = x2; p.xq_samp = x3;
+        p.dst_col = d.nb[1] / 4; p.dst_chan = d.nb[2] / 4; p.dst_samp = d.nb[3] / 4;
+        p.r2 = (int32_t) (d.ne[2] / w.ne[2]); p.r3 = (int32_t) (d.ne[3] / w.ne[3]); p.ne11 = 1;
+        g.y = (unsigned) d.ne[2]; g.z = (unsigned) d.ne[3];
+    }
+    cudaStream_t st = (cudaStream_t) stream;
+    switch (w.type) {
+        case B200_Q4_0:  return launch_type<B200_Q4_0>(p, ncols, a->ids != nullptr, fused, g, st);
+        case B200_Q8_0:  return launch_type<B200_Q8_0>(p, ncols, a->ids != nullptr, fused, g, st);
+        case B200_MXFP4: return launch_type<B200_MXFP4>(p, ncols, a->ids != nullptr, fused, g, st);
+        case B200_Q4_K:  return launch_type<B200_Q4_K>(p, ncols, a->ids != nullptr, fused, g, st);
+        case B200_Q6_K:  return launch_type<B200_Q6_K>(p, ncols, a->ids != nullptr, fused, g, st);
+        default: return B200_ERR_UNSUPPORTED;
+    }
+}
