@@ -80,10 +80,85 @@ typedef struct b200_mmvq_args {
     const b200_tensor * gate_bias;  /* f32 (or NULL) */
     int32_t glu_op;                 /* b200_glu_op, used iff gate_w != NULL */
     float   glu_alpha, glu_limit;   /* SWIGLU_OAI parameters */
+    /* optional column window [col_begin, col_begin+col_count) of x/dst dim 1 (0,0 = all columns);
+     * lets a caller walk an activation batch wider than 8 columns in chunks (MUL_MAT only) */
+    int32_t col_begin, col_count;
 } b200_mmvq_args;
 
 B200_API int b200_mmvq_supported(const b200_mmvq_args * a);
 B200_API int b200_mul_mat_vec_q(const b200_mmvq_args * a, void * stream);
+
+
+/* ---- validation mode ------------------------------------------------------------------
+ * Passing B200_STREAM_VALIDATE as `stream` to any op below makes it check its arguments and
+ * return B200_OK / B200_ERR_UNSUPPORTED without touching the GPU.  The plugin's supports_op uses
+ * this so "claimed" and "implemented" cannot drift apart. */
+#define B200_STREAM_VALIDATE ((void *) (intptr_t) -1)
+
+/* ---- row G: decode glue ops (reference ggml-cuda/{getrows,norm,binbcast,rope,set-rows,cpy,unary,
+ * scale,softmax}.cu).  All f32 compute; shapes/strides as in ggml. -------------------------- */
+
+/* GET_ROWS (getrows.cu:238): dst[:, i, b, c] = dequant(src[:, ids[i,b,c], b, c]); src f32/f16/q4_0/q8_0/q4_K/q6_K/mxfp4, dst f32 */
+B200_API int b200_get_rows(const b200_tensor * src, const b200_tensor * ids, const b200_tensor * dst, void * stream);
+
+/* RMS_NORM (+MUL (+ADD)) (norm.cu:476 and the fused forms ggml-cuda.cu:3844-3854):
+ * dst = x * rsqrt(mean(x^2) + eps) [* mul] [+ add]; mul/add broadcast over rows (may be NULL) */
+B200_API int b200_rms_norm(const b200_tensor * x, const b200_tensor * mul, const b200_tensor * add,
+                           const b200_tensor * dst, float eps, void * stream);
+
+/* ADD/SUB/MUL/DIV with ggml broadcasting of b over a (binbcast.cu); f32 (dst may be f16 for ADD) */
+enum b200_bin_op { B200_BIN_ADD = 0, B200_BIN_SUB = 1, B200_BIN_MUL = 2, B200_BIN_DIV = 3 };
+B200_API int b200_bin_bcast(int op, const b200_tensor * a, const b200_tensor * b, const b200_tensor * dst, void * stream);
+
+/* SCALE (scale.cu): dst = x * scale + bias */
+B200_API int b200_scale(const b200_tensor * x, const b200_tensor * dst, float scale, float bias, void * stream);
+
+/* GLU (unary.cu:337): dst = act(gate) * up. `up` NULL => single tensor split in halves along ne0
+ * (first half is the activated one unless swapped) */
+B200_API int b200_glu(int glu_op, const b200_tensor * gate, const b200_tensor * up, const b200_tensor * dst,
+                      int swapped, float alpha, float limit, void * stream);
+
+/* unary ops on contiguous f32 (unary.cu) */
+enum b200_unary_op { B200_UNARY_SILU = 0, B200_UNARY_GELU = 1, B200_UNARY_RELU = 2, B200_UNARY_SIGMOID = 3,
+                     B200_UNARY_TANH = 4, B200_UNARY_GELU_QUICK = 5, B200_UNARY_NEG = 6, B200_UNARY_EXP = 7 };
+B200_API int b200_unary(int op, const b200_tensor * x, const b200_tensor * dst, void * stream);
+
+/* CPY / CONT / DUP (cpy.cu): same element count, arbitrary strides; f32<->f16/bf16, f32->q8_0 (contiguous dst), same-type copies */
+B200_API int b200_cpy(const b200_tensor * src, const b200_tensor * dst, void * stream);
+
+/* SET_ROWS (set-rows.cu:318): dst[:, idx[i,b%ne11,c%ne12], b, c] = convert(src[:, i, b, c]);
+ * src f32, idx i64/i32, dst f32/f16/bf16/q8_0/q4_0 (q8_0/q4_0 blocks bit-exact vs quantize_row_*_ref) */
+B200_API int b200_set_rows(const b200_tensor * src, const b200_tensor * idx, const b200_tensor * dst, void * stream);
+
+/* ROPE (rope.cu:563): modes NORMAL(0) and NEOX(2); YaRN parameters as in ggml_rope_ext */
+typedef struct b200_rope_params {
+    int32_t n_dims, mode, n_ctx_orig;
+    float freq_base, freq_scale, ext_factor, attn_factor, beta_fast, beta_slow;
+} b200_rope_params;
+/* x f32 [head_dim, n_head, n_tok, 1]; pos i32 [n_tok]; freq_factors f32 [n_dims/2] or NULL.
+ * Optional fused SET_ROWS (ggml-cuda.cu:3614-3621): when set_idx != NULL the rotated rows are written
+ * to set_dst (f16/f32 rows of head_dim*n_head elements, row index from set_idx) instead of dst. */
+B200_API int b200_rope(const b200_tensor * x, const b200_tensor * pos, const b200_tensor * freq_factors,
+                       const b200_tensor * dst, const b200_rope_params * p,
+                       const b200_tensor * set_idx, const b200_tensor * set_dst, void * stream);
+
+/* SOFT_MAX (softmax.cu): dst = softmax(x*scale + slope*mask [, sinks]) over ne0; mask f16/f32 broadcast */
+B200_API int b200_soft_max(const b200_tensor * x, const b200_tensor * mask, const b200_tensor * sinks,
+                           const b200_tensor * dst, float scale, float max_bias, void * stream);
+
+/* ---- K7: FLASH_ATTN_EXT decode (fattn-vec.cuh:19-507, fattn-common.cuh:728-779, launch :781-1036)
+ * q f32 [D, n_q, H, n_seq]; k,v f16 or q8_0 [D, n_kv, H_kv, n_seq] (row stride = cache stride);
+ * mask f16 [n_kv, n_q_pad, 1|.., 1|n_seq] or NULL; sinks f32 [H] or NULL; dst f32 [D, H, n_q, n_seq].
+ * Split-KV across SMs with an in-kernel last-block combine; scratch must hold b200_fattn_scratch_size(). */
+typedef struct b200_fattn_args {
+    b200_tensor q, k, v, dst;
+    const b200_tensor * mask;
+    const b200_tensor * sinks;
+    float scale, max_bias, logit_softcap;
+    void * scratch; size_t scratch_size;
+} b200_fattn_args;
+B200_API size_t b200_fattn_scratch_size(const b200_fattn_args * a);
+B200_API int    b200_flash_attn_ext(const b200_fattn_args * a, void * stream);
 
 #ifdef __cplusplus
 }

@@ -23,7 +23,8 @@ class MmvqArgs(C.Structure):
     _fields_ = [("w", Tensor), ("xq", C.c_void_p), ("xq_ne0_padded", C.c_int64), ("x_ne", C.c_int64 * 4),
                 ("dst", Tensor), ("ids", C.POINTER(Tensor)), ("bias", C.POINTER(Tensor)),
                 ("gate_w", C.POINTER(Tensor)), ("gate_bias", C.POINTER(Tensor)),
-                ("glu_op", C.c_int32), ("glu_alpha", C.c_float), ("glu_limit", C.c_float)]
+                ("glu_op", C.c_int32), ("glu_alpha", C.c_float), ("glu_limit", C.c_float),
+                ("col_begin", C.c_int32), ("col_count", C.c_int32)]
 
 
 _lib = None
@@ -153,4 +154,105 @@ def mul_mat_vec_q(w_bytes, wtype: int, w_ne, x, ids=None, bias=None, gate_bytes=
         a.gate_w = C.pointer(g)
     a.glu_op, a.glu_alpha, a.glu_limit = glu_op, alpha, limit
     check(lib().b200_mul_mat_vec_q(C.byref(a), stream_ptr()), "mul_mat_vec_q")
+    return dst
+
+
+# ----------------------------------------------------------------------------- glue ops + flash attention
+class RopeParams(C.Structure):
+    _fields_ = [("n_dims", C.c_int32), ("mode", C.c_int32), ("n_ctx_orig", C.c_int32), ("freq_base", C.c_float),
+                ("freq_scale", C.c_float), ("ext_factor", C.c_float), ("attn_factor", C.c_float),
+                ("beta_fast", C.c_float), ("beta_slow", C.c_float)]
+
+
+class FattnArgs(C.Structure):
+    _fields_ = [("q", Tensor), ("k", Tensor), ("v", Tensor), ("dst", Tensor), ("mask", C.POINTER(Tensor)),
+                ("sinks", C.POINTER(Tensor)), ("scale", C.c_float), ("max_bias", C.c_float), ("logit_softcap", C.c_float),
+                ("scratch", C.c_void_p), ("scratch_size", C.c_size_t)]
+
+
+def _opt(t):
+    return C.byref(t) if t is not None else None
+
+
+def rms_norm(x, mul=None, add=None, eps=1e-5):
+    import torch
+    d = torch.empty_like(x)
+    tx, td = from_torch(x), from_torch(d)
+    tm = from_torch(mul) if mul is not None else None
+    ta = from_torch(add) if add is not None else None
+    L = lib()
+    L.b200_rms_norm.argtypes = [C.c_void_p] * 4 + [C.c_float, C.c_void_p]
+    check(L.b200_rms_norm(C.byref(tx), _opt(tm), _opt(ta), C.byref(td), eps, stream_ptr()), "rms_norm")
+    return d
+
+
+def glu(op, gate, up, alpha=1.702, limit=7.0):
+    import torch
+    d = torch.empty_like(up)
+    tg, tu, td = from_torch(gate), from_torch(up), from_torch(d)
+    L = lib()
+    L.b200_glu.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_void_p]
+    check(L.b200_glu(op, C.byref(tg), C.byref(tu), C.byref(td), 0, alpha, limit, stream_ptr()), "glu")
+    return d
+
+
+def rope(x, pos, n_dims, mode, freq_base=10000.0, freq_scale=1.0, freq_factors=None):
+    """x: [n_tok, n_head, head_dim] f32 CUDA; pos: [n_tok] int32."""
+    import torch
+    d = torch.empty_like(x)
+    rp = RopeParams(n_dims, mode, 0, freq_base, freq_scale, 0.0, 1.0, 32.0, 1.0)
+    tx, tp, td = from_torch(x), from_torch(pos), from_torch(d)
+    tf = from_torch(freq_factors) if freq_factors is not None else None
+    L = lib()
+    L.b200_rope.argtypes = [C.c_void_p] * 8
+    check(L.b200_rope(C.byref(tx), C.byref(tp), _opt(tf), C.byref(td), C.byref(rp), None, None, stream_ptr()), "rope")
+    return d
+
+
+def set_rows(src, idx, dst_bytes, dst_type, dst_ne):
+    """src f32 [n, ne0]; idx int64 [n]; dst: uint8/typed CUDA tensor of ggml shape dst_ne, updated in place."""
+    ts, ti = from_torch(src), from_torch(idx)
+    td = make_tensor(dst_bytes.data_ptr(), dst_type, dst_ne)
+    L = lib()
+    L.b200_set_rows.argtypes = [C.c_void_p] * 4
+    check(L.b200_set_rows(C.byref(ts), C.byref(ti), C.byref(td), stream_ptr()), "set_rows")
+
+
+def get_rows(src_bytes, src_type, src_ne, ids):
+    import torch
+    d = torch.empty(ids.numel(), src_ne[0], dtype=torch.float32, device=ids.device)
+    ts = make_tensor(src_bytes.data_ptr(), src_type, src_ne)
+    ti, td = from_torch(ids), from_torch(d)
+    L = lib()
+    L.b200_get_rows.argtypes = [C.c_void_p] * 4
+    check(L.b200_get_rows(C.byref(ts), C.byref(ti), C.byref(td), stream_ptr()), "get_rows")
+    return d
+
+
+def flash_attn(q, k_bytes, v_bytes, kv_type, n_kv, H_kv, mask=None, sinks=None, scale=1.0, max_bias=0.0, softcap=0.0):
+    """q: f32 [H, n_q, D] CUDA (ggml [D, n_q, H]); k/v: packed rows, ggml [D, n_kv, H_kv] contiguous;
+    mask: f16 [n_q, n_kv]; returns f32 [n_q, H, D]."""
+    import torch
+    H, n_q, D = q.shape
+    dst = torch.empty(n_q, H, D, dtype=torch.float32, device=q.device)
+    a = FattnArgs()
+    a.q = from_torch(q)
+    a.k = make_tensor(k_bytes.data_ptr(), kv_type, [D, n_kv, H_kv, 1])
+    a.v = make_tensor(v_bytes.data_ptr(), kv_type, [D, n_kv, H_kv, 1])
+    a.dst = from_torch(dst)
+    keep = []
+    if mask is not None:
+        tm = from_torch(mask); keep.append(tm); a.mask = C.pointer(tm)
+    if sinks is not None:
+        tk = from_torch(sinks); keep.append(tk); a.sinks = C.pointer(tk)
+    a.scale, a.max_bias, a.logit_softcap = scale, max_bias, softcap
+    L = lib()
+    L.b200_fattn_scratch_size.restype = C.c_size_t
+    L.b200_fattn_scratch_size.argtypes = [C.c_void_p]
+    L.b200_flash_attn_ext.argtypes = [C.c_void_p, C.c_void_p]
+    n = L.b200_fattn_scratch_size(C.byref(a))
+    assert n > 0, "flash_attn: unsupported shape"
+    scratch = torch.zeros(n, dtype=torch.uint8, device=q.device)
+    a.scratch, a.scratch_size = scratch.data_ptr(), n
+    check(L.b200_flash_attn_ext(C.byref(a), stream_ptr()), "flash_attn_ext")
     return dst

@@ -1,0 +1,90 @@
+// b200_plugin.h — internal declarations of the ggml backend plugin (libggml-b200.so).
+// Host side in C++ (the reference's language); compute goes through include/b200_kernels.h only.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "ggml.h"
+#include "ggml-backend.h"
+#include "ggml-impl.h"
+#include "ggml-backend-impl.h"
+
+#include "b200_backend.h"
+#include "b200_kernels.h"
+
+#define B200_MAX_DEVICES 16
+#define B200_MATRIX_ROW_PADDING 512   // q8_1 activation rows are padded to this many elements (reference MATRIX_ROW_PADDING)
+
+[[noreturn]] void b200_abort(const char * file, int line, const char * what, const char * detail);
+
+#define B200_CUDA_CHECK(expr)                                                              \
+    do {                                                                                   \
+        cudaError_t err_ = (expr);                                                         \
+        if (err_ != cudaSuccess) b200_abort(__FILE__, __LINE__, #expr, cudaGetErrorString(err_)); \
+    } while (0)
+
+#define B200_KCHECK(expr)                                                                  \
+    do {                                                                                   \
+        int rc_ = (expr);                                                                  \
+        if (rc_ != B200_OK) b200_abort(__FILE__, __LINE__, #expr, b200_last_error());      \
+    } while (0)
+
+struct b200_device_info {
+    int         id;
+    std::string name;         // "B200_0"
+    std::string description;  // cudaDeviceProp.name
+    std::string pci_bus_id;
+    size_t      total_mem;
+    int         cc_major, cc_minor, n_sm;
+};
+
+int                      b200_n_devices();
+const b200_device_info & b200_device(int id);
+void                     b200_set_device(int id);
+
+// ---- buffer types (buffer.cpp)
+ggml_backend_buffer_type_t b200_buffer_type(int device);
+bool                       b200_buft_is_b200(ggml_backend_buffer_type_t buft);
+bool                       b200_buft_is_split(ggml_backend_buffer_type_t buft);
+int                        b200_buft_device(ggml_backend_buffer_type_t buft);
+
+// ---- backend context (exec.cpp)
+struct b200_graph_cache;
+struct b200_context {
+    int          device = 0;
+    cudaStream_t stream = nullptr;
+    std::string  name;
+    // scratch arenas (stable addresses across CUDA-graph replays; growing one drops the graph cache)
+    char * q8_scratch = nullptr; size_t q8_size = 0;      // q8_1 activations
+    char * fa_scratch = nullptr; size_t fa_size = 0;      // flash-attn counters + partials
+    b200_graph_cache * cache = nullptr;
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+    bool timing = false, ev_pending = false;
+};
+
+ggml_status b200_graph_compute(b200_context * ctx, ggml_cgraph * cgraph);
+bool        b200_supports_op(int device, const ggml_tensor * op);
+void        b200_context_free(b200_context * ctx);
+void        b200_timing_collect(b200_context * ctx);
+
+// ---- tensor translation
+static inline b200_tensor b200_desc(const ggml_tensor * t) {
+    b200_tensor d;
+    d.data = t->data; d.type = (int32_t) t->type; d._pad = 0;
+    for (int i = 0; i < 4; ++i) { d.ne[i] = t->ne[i]; d.nb[i] = (int64_t) t->nb[i]; }
+    return d;
+}
+
+// ---- stats (device.cpp)
+struct b200_stats_t {
+    std::mutex mu;
+    ggml_b200_stats s{};
+};
+b200_stats_t & b200_stats();

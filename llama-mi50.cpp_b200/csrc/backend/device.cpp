@@ -1,0 +1,231 @@
+// device.cpp — registry, device and backend(stream) vtables + the exported loader symbols.
+// Implements ggml_backend_reg_i / ggml_backend_device_i / ggml_backend_i (reference interface:
+// ggml/src/ggml-backend-impl.h:87-210; reference CUDA implementation: ggml-cuda/ggml-cuda.cu
+// :2768-2860 backend, :4328-4939 device, :4943-5117 reg).
+#include "b200_plugin.h"
+
+#include <cstdarg>
+#include <cstring>
+
+[[noreturn]] void b200_abort(const char * file, int line, const char * what, const char * detail) {
+    int dev = -1;
+    cudaGetDevice(&dev);
+    GGML_LOG_ERROR("ggml-b200 error: %s\n  in %s:%d (current device %d)\n  %s\n", what, file, line, dev, detail ? detail : "");
+    GGML_ABORT("ggml-b200 error");
+}
+
+// ---------------------------------------------------------------- device table
+namespace {
+struct dev_table {
+    std::vector<b200_device_info> devs;
+    dev_table() {
+        int n = 0;
+        if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); n = 0; }
+        for (int i = 0; i < n && (int) devs.size() < B200_MAX_DEVICES; ++i) {
+            cudaDeviceProp p;
+            if (cudaGetDeviceProperties(&p, i) != cudaSuccess) { cudaGetLastError(); continue; }
+            if (p.major != 10) continue;   // kernels are sm_100a only: no other architecture is claimed
+            b200_device_info d;
+            d.id = i; d.name = "B200_" + std::to_string(devs.size()); d.description = p.name;
+            char bus[32]; snprintf(bus, sizeof(bus), "%04x:%02x:%02x.0", p.pciDomainID, p.pciBusID, p.pciDeviceID);
+            d.pci_bus_id = bus; d.total_mem = p.totalGlobalMem; d.cc_major = p.major; d.cc_minor = p.minor; d.n_sm = p.multiProcessorCount;
+            devs.push_back(d);
+        }
+    }
+};
+dev_table & table() { static dev_table t; return t; }
+}  // namespace
+
+int b200_n_devices() { return (int) table().devs.size(); }
+const b200_device_info & b200_device(int id) { return table().devs[id]; }
+void b200_set_device(int id) {
+    int cur = -1;
+    const int cuda_id = table().devs[id].id;
+    if (cudaGetDevice(&cur) == cudaSuccess && cur == cuda_id) return;
+    B200_CUDA_CHECK(cudaSetDevice(cuda_id));
+}
+
+b200_stats_t & b200_stats() { static b200_stats_t s; return s; }
+
+ggml_backend_dev_t b200_dev(int device);
+ggml_backend_reg_t b200_reg();
+
+// ---------------------------------------------------------------- backend (stream)
+namespace {
+
+ggml_guid_t backend_guid() {
+    static ggml_guid guid = {0xb2, 0x00, 0x51, 0x0a, 0x67, 0x67, 0x6d, 0x6c, 0x2d, 0x62, 0x32, 0x30, 0x30, 0x00, 0x00, 0x01};
+    return &guid;
+}
+
+const char * be_name(ggml_backend_t b) { return ((b200_context *) b->context)->name.c_str(); }
+void be_free(ggml_backend_t b) { b200_context_free((b200_context *) b->context); delete b; }
+
+bool tensor_on_b200(const ggml_tensor * t) {
+    ggml_backend_buffer_t buf = t->view_src ? t->view_src->buffer : t->buffer;
+    return buf && b200_buft_is_b200(buf->buft) && !b200_buft_is_split(buf->buft);
+}
+void be_set_async(ggml_backend_t b, ggml_tensor * t, const void * data, size_t off, size_t size) {
+    b200_context * c = (b200_context *) b->context;
+    GGML_ASSERT(tensor_on_b200(t));
+    b200_set_device(c->device);
+    B200_CUDA_CHECK(cudaMemcpyAsync((char *) t->data + off, data, size, cudaMemcpyHostToDevice, c->stream));
+}
+void be_get_async(ggml_backend_t b, const ggml_tensor * t, void * data, size_t off, size_t size) {
+    b200_context * c = (b200_context *) b->context;
+    GGML_ASSERT(tensor_on_b200(t));
+    b200_set_device(c->device);
+    B200_CUDA_CHECK(cudaMemcpyAsync(data, (const char *) t->data + off, size, cudaMemcpyDeviceToHost, c->stream));
+}
+void be_sync(ggml_backend_t b) {
+    b200_context * c = (b200_context *) b->context;
+    b200_set_device(c->device);
+    B200_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    b200_timing_collect(c);
+}
+ggml_status be_graph_compute(ggml_backend_t b, ggml_cgraph * g) { return b200_graph_compute((b200_context *) b->context, g); }
+
+void be_event_record(ggml_backend_t b, ggml_backend_event_t e) {
+    b200_context * c = (b200_context *) b->context;
+    B200_CUDA_CHECK(cudaEventRecord((cudaEvent_t) e->context, c->stream));
+}
+void be_event_wait(ggml_backend_t b, ggml_backend_event_t e) {
+    b200_context * c = (b200_context *) b->context;
+    B200_CUDA_CHECK(cudaStreamWaitEvent(c->stream, (cudaEvent_t) e->context, 0));
+}
+
+const ggml_backend_i kBackendIface = {
+    /* get_name           */ be_name,
+    /* free               */ be_free,
+    /* set_tensor_async   */ be_set_async,
+    /* get_tensor_async   */ be_get_async,
+    /* cpy_tensor_async   */ nullptr,
+    /* synchronize        */ be_sync,
+    /* graph_plan_create  */ nullptr,
+    /* graph_plan_free    */ nullptr,
+    /* graph_plan_update  */ nullptr,
+    /* graph_plan_compute */ nullptr,
+    /* graph_compute      */ be_graph_compute,
+    /* event_record       */ be_event_record,
+    /* event_wait         */ be_event_wait,
+    /* graph_optimize     */ nullptr,
+};
+
+// ---------------------------------------------------------------- device
+struct dev_ctx { int device; };
+
+const char * dev_name(ggml_backend_dev_t d) { return b200_device(((dev_ctx *) d->context)->device).name.c_str(); }
+const char * dev_desc(ggml_backend_dev_t d) { return b200_device(((dev_ctx *) d->context)->device).description.c_str(); }
+void dev_memory(ggml_backend_dev_t d, size_t * free, size_t * total) {
+    b200_set_device(((dev_ctx *) d->context)->device);
+    B200_CUDA_CHECK(cudaMemGetInfo(free, total));
+}
+enum ggml_backend_dev_type dev_type(ggml_backend_dev_t) { return GGML_BACKEND_DEVICE_TYPE_GPU; }
+void dev_props(ggml_backend_dev_t d, ggml_backend_dev_props * p) {
+    const b200_device_info & info = b200_device(((dev_ctx *) d->context)->device);
+    p->name = info.name.c_str(); p->description = info.description.c_str(); p->type = GGML_BACKEND_DEVICE_TYPE_GPU;
+    p->device_id = info.pci_bus_id.c_str();
+    dev_memory(d, &p->memory_free, &p->memory_total);
+    p->caps = { /* async */ true, /* host_buffer */ false, /* buffer_from_host_ptr */ false, /* events */ true };
+}
+ggml_backend_t dev_init_backend(ggml_backend_dev_t d, const char *) {
+    const int device = ((dev_ctx *) d->context)->device;
+    b200_set_device(device);
+    b200_context * c = new b200_context;
+    c->device = device; c->name = b200_device(device).name;
+    B200_CUDA_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    const char * t = getenv("GGML_B200_TIMING");
+    c->timing = t && atoi(t) != 0;
+    if (c->timing) { B200_CUDA_CHECK(cudaEventCreate(&c->ev_begin)); B200_CUDA_CHECK(cudaEventCreate(&c->ev_end)); }
+    return new ggml_backend{ backend_guid(), kBackendIface, d, c };
+}
+ggml_backend_buffer_type_t dev_buft(ggml_backend_dev_t d) { return b200_buffer_type(((dev_ctx *) d->context)->device); }
+bool dev_supports_op(ggml_backend_dev_t d, const ggml_tensor * op) { return b200_supports_op(((dev_ctx *) d->context)->device, op); }
+bool dev_supports_buft(ggml_backend_dev_t d, ggml_backend_buffer_type_t buft) {
+    if (b200_buft_is_split(buft)) return true;
+    return b200_buft_device(buft) == ((dev_ctx *) d->context)->device;
+}
+bool dev_offload_op(ggml_backend_dev_t, const ggml_tensor *) { return false; }
+ggml_backend_event_t dev_event_new(ggml_backend_dev_t d) {
+    b200_set_device(((dev_ctx *) d->context)->device);
+    cudaEvent_t e;
+    B200_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    return new ggml_backend_event{ d, e };
+}
+void dev_event_free(ggml_backend_dev_t, ggml_backend_event_t e) { cudaEventDestroy((cudaEvent_t) e->context); delete e; }
+void dev_event_sync(ggml_backend_dev_t, ggml_backend_event_t e) { B200_CUDA_CHECK(cudaEventSynchronize((cudaEvent_t) e->context)); }
+
+const ggml_backend_device_i kDevIface = {
+    /* get_name             */ dev_name,
+    /* get_description      */ dev_desc,
+    /* get_memory           */ dev_memory,
+    /* get_type             */ dev_type,
+    /* get_props            */ dev_props,
+    /* init_backend         */ dev_init_backend,
+    /* get_buffer_type      */ dev_buft,
+    /* get_host_buffer_type */ nullptr,
+    /* buffer_from_host_ptr */ nullptr,
+    /* supports_op          */ dev_supports_op,
+    /* supports_buft        */ dev_supports_buft,
+    /* offload_op           */ dev_offload_op,
+    /* event_new            */ dev_event_new,
+    /* event_free           */ dev_event_free,
+    /* event_synchronize    */ dev_event_sync,
+};
+
+// ---------------------------------------------------------------- registry
+const char * reg_name(ggml_backend_reg_t) { return "B200"; }
+size_t reg_dev_count(ggml_backend_reg_t) { return (size_t) b200_n_devices(); }
+ggml_backend_dev_t reg_get_dev(ggml_backend_reg_t, size_t i) { return b200_dev((int) i); }
+
+ggml_backend_feature * get_features(ggml_backend_reg_t) {
+    // BLACKWELL_NATIVE_FP4 is deliberately NOT advertised: MXFP4 weights multiply q8_1 activations,
+    // so the stricter 5e-4 NMSE gate of tests/test-backend-ops.cpp:3718-3728 applies.
+    static ggml_backend_feature f[] = { {"ARCH", "sm_100a"}, {"NO_CPU_FALLBACK", "1"}, {nullptr, nullptr} };
+    return f;
+}
+void * reg_proc(ggml_backend_reg_t, const char * name) {
+    if (!strcmp(name, "ggml_backend_split_buffer_type")) return (void *) ggml_backend_b200_split_buffer_type;
+    if (!strcmp(name, "ggml_backend_get_features"))      return (void *) get_features;
+    if (!strcmp(name, "ggml_backend_b200_get_stats"))    return (void *) ggml_backend_b200_get_stats;
+    if (!strcmp(name, "ggml_backend_b200_reset_stats"))  return (void *) ggml_backend_b200_reset_stats;
+    return nullptr;
+}
+const ggml_backend_reg_i kRegIface = { reg_name, reg_dev_count, reg_get_dev, reg_proc };
+
+}  // namespace
+
+ggml_backend_reg_t b200_reg() {
+    static ggml_backend_reg reg = { GGML_BACKEND_API_VERSION, kRegIface, nullptr };
+    return &reg;
+}
+
+ggml_backend_dev_t b200_dev(int device) {
+    static std::mutex mu;
+    static ggml_backend_device devs[B200_MAX_DEVICES];
+    static dev_ctx ctxs[B200_MAX_DEVICES];
+    static bool init[B200_MAX_DEVICES] = {};
+    std::lock_guard<std::mutex> lock(mu);
+    if (device < 0 || device >= b200_n_devices()) return nullptr;
+    if (!init[device]) {
+        ctxs[device].device = device;
+        devs[device] = ggml_backend_device{ kDevIface, b200_reg(), &ctxs[device] };
+        init[device] = true;
+    }
+    return &devs[device];
+}
+
+// ---------------------------------------------------------------- exported symbols
+#define B200_EXPORT extern "C" __attribute__((visibility("default")))
+
+B200_EXPORT ggml_backend_reg_t ggml_backend_init(void) { return b200_reg(); }
+B200_EXPORT int ggml_backend_score(void) { return b200_n_devices() > 0 ? 100 : 0; }
+
+B200_EXPORT void ggml_backend_b200_get_stats(ggml_b200_stats * out) {
+    std::lock_guard<std::mutex> lock(b200_stats().mu);
+    *out = b200_stats().s;
+}
+B200_EXPORT void ggml_backend_b200_reset_stats(void) {
+    std::lock_guard<std::mutex> lock(b200_stats().mu);
+    b200_stats().s = ggml_b200_stats{};
+}

@@ -1,0 +1,396 @@
+// exec.cpp — supports_op and graph_compute of the B200 backend.
+// Replaces the op dispatcher ggml_cuda_compute_forward (reference ggml-cuda/ggml-cuda.cu:2422-2762),
+// supports_op (:4440-4860) and the graph executor with fusion + CUDA-graph capture/replay
+// (:2862-3086, :3394-3922, :3941-3977).  Design differences:
+//   * one function translates a node into C-ABI calls; supports_op runs it in validation mode,
+//     so an op is claimed iff the very same code path would execute it;
+//   * the activation vector of consecutive MUL_MATs that share src1 (wq/wk/wv, gate/up) is
+//     quantized to q8_1 ONCE (the reference re-quantizes per matmul, mmvq.cu:700-706);
+//   * kernels are chained with programmatic dependent launch inside one captured CUDA graph.
+#include "b200_plugin.h"
+
+#include <cmath>
+#include <cstring>
+
+namespace {
+
+bool env_flag(const char * name) { const char * v = getenv(name); return v && atoi(v) != 0; }
+
+struct exec_state {
+    b200_context * ctx = nullptr;
+    void * stream = B200_STREAM_VALIDATE;
+    bool validate = true;
+    // q8_1 activation cache: the quantized form of `q8_src` currently held in ctx->q8_scratch
+    const ggml_tensor * q8_src = nullptr;
+    const void * q8_src_data = nullptr;
+    size_t need_q8 = 0, need_fa = 0;   // scratch high-water marks found during the sizing pass
+    bool sizing = false;               // sizing pass: compute need_*, launch nothing
+    uint64_t launches = 0;
+};
+
+int64_t pad_to(int64_t x, int64_t n) { return (x + n - 1) / n * n; }
+
+bool is_quant_weight(ggml_type t) {
+    return t == GGML_TYPE_Q4_0 || t == GGML_TYPE_Q8_0 || t == GGML_TYPE_Q4_K || t == GGML_TYPE_Q6_K || t == GGML_TYPE_MXFP4;
+}
+
+int map_unary(ggml_unary_op op) {
+    switch (op) {
+        case GGML_UNARY_OP_SILU: return B200_UNARY_SILU;
+        case GGML_UNARY_OP_GELU: return B200_UNARY_GELU;
+        case GGML_UNARY_OP_RELU: return B200_UNARY_RELU;
+        case GGML_UNARY_OP_SIGMOID: return B200_UNARY_SIGMOID;
+        case GGML_UNARY_OP_TANH: return B200_UNARY_TANH;
+        case GGML_UNARY_OP_GELU_QUICK: return B200_UNARY_GELU_QUICK;
+        case GGML_UNARY_OP_NEG: return B200_UNARY_NEG;
+        case GGML_UNARY_OP_EXP: return B200_UNARY_EXP;
+        default: return -1;
+    }
+}
+
+// ---- MUL_MAT / MUL_MAT_ID -------------------------------------------------------------------
+// quantize src1 into the q8_1 arena (unless it is already there) and run the GEMV in <= 8-column windows
+int run_mul_mat(exec_state & st, const ggml_tensor * dst, const ggml_tensor * bias, const ggml_tensor * gate,
+                const ggml_tensor * gate_bias, int glu_op, float alpha, float limit) {
+    const ggml_tensor * w = dst->src[0]; const ggml_tensor * x = dst->src[1];
+    const ggml_tensor * ids = dst->op == GGML_OP_MUL_MAT_ID ? dst->src[2] : nullptr;
+    if (!is_quant_weight(w->type) || x->type != GGML_TYPE_F32 || dst->type != GGML_TYPE_F32) return B200_ERR_UNSUPPORTED;
+    if (x->nb[0] != sizeof(float) || x->ne[0] != w->ne[0]) return B200_ERR_UNSUPPORTED;
+    if (x->ne[1] > 65535 || x->ne[2] * x->ne[3] > 65535) return B200_ERR_UNSUPPORTED;
+
+    b200_mmvq_args a{};
+    a.w = b200_desc(w);
+    a.xq_ne0_padded = pad_to(x->ne[0], B200_MATRIX_ROW_PADDING);
+    for (int i = 0; i < 4; ++i) a.x_ne[i] = x->ne[i];
+    a.dst = b200_desc(dst);
+    b200_tensor t_ids, t_bias, t_gate, t_gbias;
+    if (ids)       { t_ids = b200_desc(ids); a.ids = &t_ids; }
+    if (bias)      { t_bias = b200_desc(bias); a.bias = &t_bias; }
+    if (gate)      { t_gate = b200_desc(gate); a.gate_w = &t_gate; }
+    if (gate_bias) { t_gbias = b200_desc(gate_bias); a.gate_bias = &t_gbias; }
+    a.glu_op = gate ? glu_op : B200_GLU_NONE; a.glu_alpha = alpha; a.glu_limit = limit;
+
+    const int64_t ncols = ids ? 1 : x->ne[1];
+    const int nwin = (int) ((ncols + 7) / 8);
+    for (int wi = 0; wi < nwin; ++wi) {   // validate every window shape
+        if (nwin > 1) { a.col_begin = wi * 8; a.col_count = (int) std::min<int64_t>(8, ncols - wi * 8); }
+        if (!b200_mmvq_supported(&a)) return B200_ERR_UNSUPPORTED;
+        if (wi > 0 && wi < nwin - 1) wi = nwin - 2;   // interior windows are identical
+    }
+    if (st.validate) return B200_OK;
+
+    const b200_tensor tx = b200_desc(x);
+    const size_t q8_bytes = b200_q8_1_buffer_size(&tx, a.xq_ne0_padded);
+    if (st.sizing) { st.need_q8 = std::max(st.need_q8, q8_bytes); return B200_OK; }
+    GGML_ASSERT(q8_bytes <= st.ctx->q8_size);
+    if (st.q8_src != x || st.q8_src_data != x->data) {
+        B200_KCHECK(b200_quantize_q8_1(&tx, st.ctx->q8_scratch, a.xq_ne0_padded, st.stream));
+        st.q8_src = x; st.q8_src_data = x->data; st.launches++;
+    }
+    a.xq = st.ctx->q8_scratch;
+    for (int wi = 0; wi < nwin; ++wi) {
+        if (nwin > 1) { a.col_begin = wi * 8; a.col_count = (int) std::min<int64_t>(8, ncols - wi * 8); }
+        B200_KCHECK(b200_mul_mat_vec_q(&a, st.stream));
+        st.launches++;
+    }
+    return B200_OK;
+}
+
+int run_flash_attn(exec_state & st, const ggml_tensor * dst) {
+    const ggml_tensor * q = dst->src[0]; const ggml_tensor * k = dst->src[1]; const ggml_tensor * v = dst->src[2];
+    const ggml_tensor * mask = dst->src[3]; const ggml_tensor * sinks = dst->src[4];
+    b200_fattn_args a{};
+    a.q = b200_desc(q); a.k = b200_desc(k); a.v = b200_desc(v); a.dst = b200_desc(dst);
+    b200_tensor tm, ts;
+    if (mask)  { tm = b200_desc(mask); a.mask = &tm; }
+    if (sinks) { ts = b200_desc(sinks); a.sinks = &ts; }
+    memcpy(&a.scale, (const float *) dst->op_params + 0, sizeof(float));
+    memcpy(&a.max_bias, (const float *) dst->op_params + 1, sizeof(float));
+    memcpy(&a.logit_softcap, (const float *) dst->op_params + 2, sizeof(float));
+    if (st.validate) return b200_flash_attn_ext(&a, B200_STREAM_VALIDATE);
+    const size_t need = b200_fattn_scratch_size(&a);
+    if (st.sizing) { st.need_fa = std::max(st.need_fa, need); return B200_OK; }
+    GGML_ASSERT(need <= st.ctx->fa_size);
+    a.scratch = st.ctx->fa_scratch; a.scratch_size = st.ctx->fa_size;
+    B200_KCHECK(b200_flash_attn_ext(&a, st.stream));
+    st.launches++;
+    return B200_OK;
+}
+
+#define RUN(expr)                                                     \
+    do {                                                              \
+        const int rc__ = (expr);                                      \
+        if (st.validate || st.sizing) return rc__;                    \
+        if (rc__ != B200_OK) b200_abort(__FILE__, __LINE__, #expr, b200_last_error()); \
+        st.launches++;                                                \
+        return B200_OK;                                               \
+    } while (0)
+
+// Single (unfused) node. In validation/sizing mode nothing is launched.
+int run_node(exec_state & st, const ggml_tensor * n) {
+    void * s = (st.validate || st.sizing) ? B200_STREAM_VALIDATE : st.stream;
+    const ggml_tensor * s0 = n->src[0]; const ggml_tensor * s1 = n->src[1];
+    switch (n->op) {
+        case GGML_OP_NONE: case GGML_OP_VIEW: case GGML_OP_RESHAPE: case GGML_OP_PERMUTE: case GGML_OP_TRANSPOSE:
+            return B200_OK;
+        case GGML_OP_GET_ROWS: { b200_tensor a = b200_desc(s0), b = b200_desc(s1), d = b200_desc(n); RUN(b200_get_rows(&a, &b, &d, s)); }
+        case GGML_OP_RMS_NORM: {
+            b200_tensor a = b200_desc(s0), d = b200_desc(n); float eps; memcpy(&eps, n->op_params, sizeof(float));
+            RUN(b200_rms_norm(&a, nullptr, nullptr, &d, eps, s));
+        }
+        case GGML_OP_ADD: case GGML_OP_SUB: case GGML_OP_MUL: case GGML_OP_DIV: {
+            const int op = n->op == GGML_OP_ADD ? B200_BIN_ADD : n->op == GGML_OP_SUB ? B200_BIN_SUB : n->op == GGML_OP_MUL ? B200_BIN_MUL : B200_BIN_DIV;
+            b200_tensor a = b200_desc(s0), b = b200_desc(s1), d = b200_desc(n);
+            RUN(b200_bin_bcast(op, &a, &b, &d, s));
+        }
+        case GGML_OP_SCALE: {
+            b200_tensor a = b200_desc(s0), d = b200_desc(n); float sc, bi; memcpy(&sc, n->op_params, 4); memcpy(&bi, (const float *) n->op_params + 1, 4);
+            RUN(b200_scale(&a, &d, sc, bi, s));
+        }
+        case GGML_OP_UNARY: {
+            const int op = map_unary(ggml_get_unary_op(n));
+            if (op < 0) return B200_ERR_UNSUPPORTED;
+            b200_tensor a = b200_desc(s0), d = b200_desc(n);
+            RUN(b200_unary(op, &a, &d, s));
+        }
+        case GGML_OP_GLU: {
+            b200_tensor a = b200_desc(s0), d = b200_desc(n), b; if (s1) b = b200_desc(s1);
+            float alpha, limit; memcpy(&alpha, (const float *) n->op_params + 2, 4); memcpy(&limit, (const float *) n->op_params + 3, 4);
+            RUN(b200_glu((int) ggml_get_glu_op(n), &a, s1 ? &b : nullptr, &d, n->op_params[1], alpha, limit, s));
+        }
+        case GGML_OP_CPY: case GGML_OP_CONT: case GGML_OP_DUP: { b200_tensor a = b200_desc(s0), d = b200_desc(n); RUN(b200_cpy(&a, &d, s)); }
+        case GGML_OP_SET_ROWS: { b200_tensor a = b200_desc(s0), b = b200_desc(s1), d = b200_desc(n); RUN(b200_set_rows(&a, &b, &d, s)); }
+        case GGML_OP_ROPE: {
+            b200_rope_params rp{};
+            const int32_t * p = n->op_params;
+            rp.n_dims = p[1]; rp.mode = p[2]; rp.n_ctx_orig = p[4];
+            memcpy(&rp.freq_base, p + 5, 4); memcpy(&rp.freq_scale, p + 6, 4); memcpy(&rp.ext_factor, p + 7, 4);
+            memcpy(&rp.attn_factor, p + 8, 4); memcpy(&rp.beta_fast, p + 9, 4); memcpy(&rp.beta_slow, p + 10, 4);
+            b200_tensor a = b200_desc(s0), b = b200_desc(s1), d = b200_desc(n), f; if (n->src[2]) f = b200_desc(n->src[2]);
+            RUN(b200_rope(&a, &b, n->src[2] ? &f : nullptr, &d, &rp, nullptr, nullptr, s));
+        }
+        case GGML_OP_SOFT_MAX: {
+            b200_tensor a = b200_desc(s0), d = b200_desc(n), m, k; if (s1) m = b200_desc(s1); if (n->src[2]) k = b200_desc(n->src[2]);
+            float sc, mb; memcpy(&sc, n->op_params, 4); memcpy(&mb, (const float *) n->op_params + 1, 4);
+            RUN(b200_soft_max(&a, s1 ? &m : nullptr, n->src[2] ? &k : nullptr, &d, sc, mb, s));
+        }
+        case GGML_OP_FLASH_ATTN_EXT: return run_flash_attn(st, n);
+        case GGML_OP_MUL_MAT: case GGML_OP_MUL_MAT_ID: return run_mul_mat(st, n, nullptr, nullptr, nullptr, B200_GLU_NONE, 0.0f, 0.0f);
+        default: return B200_ERR_UNSUPPORTED;
+    }
+}
+#undef RUN
+
+}  // namespace
+
+bool b200_supports_op(int device, const ggml_tensor * op) {
+    // every source must live in (or be allocatable in) this device's buffers
+    for (int i = 0; i < GGML_MAX_SRC; ++i) {
+        const ggml_tensor * s = op->src[i];
+        if (!s) continue;
+        ggml_backend_buffer_t buf = s->view_src ? s->view_src->buffer : s->buffer;
+        if (buf && b200_buft_is_b200(buf->buft) && !b200_buft_is_split(buf->buft) && b200_buft_device(buf->buft) != device) return false;
+        if (buf && b200_buft_is_split(buf->buft) && op->op != GGML_OP_MUL_MAT) return false;
+    }
+    exec_state st;   // validation mode
+    return run_node(st, op) == B200_OK;
+}
+
+// =====================================================================================
+// graph executor: fusion matcher + CUDA-graph capture/replay
+// =====================================================================================
+namespace {
+
+struct node_key {
+    const void * node; const void * data; int op; int32_t flags;
+    int64_t ne[4]; size_t nb[4];
+    const void * src[GGML_MAX_SRC]; const void * src_data[GGML_MAX_SRC];
+    int32_t op_params[GGML_MAX_OP_PARAMS / sizeof(int32_t)];
+};
+
+void make_key(const ggml_tensor * n, node_key & k) {
+    memset(&k, 0, sizeof(k));
+    k.node = n; k.data = n->data; k.op = (int) n->op; k.flags = n->flags;
+    for (int i = 0; i < 4; ++i) { k.ne[i] = n->ne[i]; k.nb[i] = n->nb[i]; }
+    for (int i = 0; i < GGML_MAX_SRC; ++i) { k.src[i] = n->src[i]; k.src_data[i] = n->src[i] ? n->src[i]->data : nullptr; }
+    memcpy(k.op_params, n->op_params, sizeof(k.op_params));
+}
+
+}  // namespace
+
+struct b200_graph_cache {
+    std::vector<node_key> keys;        // properties of the graph last seen
+    cudaGraphExec_t exec = nullptr;    // instantiated capture of `keys` (or null)
+    uint64_t kernels = 0;              // kernel nodes in `exec`
+    int seen = 0;                      // consecutive identical submissions
+};
+
+namespace {
+
+bool same_shape(const ggml_tensor * a, const ggml_tensor * b) { return ggml_are_same_shape(a, b); }
+
+// returns the number of graph nodes consumed starting at i (>= 1)
+int run_fused(exec_state & st, ggml_cgraph * g, int i, bool fusion) {
+    ggml_tensor * n = g->nodes[i];
+    if (fusion && !st.validate) {
+        // {RMS_NORM, MUL[, ADD]}  (reference fusion: ggml-cuda.cu:3844-3854)
+        if (n->op == GGML_OP_RMS_NORM) {
+            const ggml_op ops3[] = {GGML_OP_RMS_NORM, GGML_OP_MUL, GGML_OP_ADD};
+            int cnt = ggml_can_fuse(g, i, ops3, 3) ? 3 : ggml_can_fuse(g, i, ops3, 2) ? 2 : 1;
+            while (cnt > 1) {
+                const ggml_tensor * mul = g->nodes[i + 1];
+                const ggml_tensor * w = mul->src[0] == n ? mul->src[1] : mul->src[0];
+                const ggml_tensor * add = cnt == 3 ? g->nodes[i + 2] : nullptr;
+                const ggml_tensor * b = add ? (add->src[0] == mul ? add->src[1] : add->src[0]) : nullptr;
+                const ggml_tensor * out = add ? add : mul;
+                b200_tensor tx = b200_desc(n->src[0]), tw = b200_desc(w), td = b200_desc(out), tb; if (b) tb = b200_desc(b);
+                float eps; memcpy(&eps, n->op_params, 4);
+                if (b200_rms_norm(&tx, &tw, b ? &tb : nullptr, &td, eps, B200_STREAM_VALIDATE) == B200_OK) {
+                    if (!st.sizing) { B200_KCHECK(b200_rms_norm(&tx, &tw, b ? &tb : nullptr, &td, eps, st.stream)); st.launches++; }
+                    return cnt;
+                }
+                --cnt;
+            }
+        }
+        // {MUL_MAT(gate), MUL_MAT(up), GLU} on one activation column (reference: ggml-cuda.cu:3737-3771)
+        if (n->op == GGML_OP_MUL_MAT && i + 2 < g->n_nodes && n->ne[1] == 1 && n->ne[2] == 1 && n->ne[3] == 1) {
+            ggml_tensor * m2 = g->nodes[i + 1]; ggml_tensor * glu = g->nodes[i + 2];
+            if (m2->op == GGML_OP_MUL_MAT && glu->op == GGML_OP_GLU && m2->src[1] == n->src[1] && glu->src[0] && glu->src[1] &&
+                ((glu->src[0] == n && glu->src[1] == m2) || (glu->src[0] == m2 && glu->src[1] == n)) &&
+                ggml_node_has_n_uses(g, i, 1) && ggml_node_has_n_uses(g, i + 1, 1) && glu->op_params[1] == 0 &&
+                same_shape(n, m2) && same_shape(n, glu) && n->src[0]->type == m2->src[0]->type) {
+                const ggml_tensor * gate_mm = glu->src[0]; const ggml_tensor * up_mm = glu->src[1];
+                float alpha, limit; memcpy(&alpha, (const float *) glu->op_params + 2, 4); memcpy(&limit, (const float *) glu->op_params + 3, 4);
+                // run as: dst(glu) = act(gate_w . x) * (up_w . x)
+                ggml_tensor tmp = *glu;            // shallow copy describing the fused output
+                tmp.op = GGML_OP_MUL_MAT; tmp.src[0] = up_mm->src[0]; tmp.src[1] = up_mm->src[1]; tmp.src[2] = nullptr;
+                exec_state probe = st; probe.validate = true;
+                if (run_mul_mat(probe, &tmp, nullptr, gate_mm->src[0], nullptr, (int) ggml_get_glu_op(glu), alpha, limit) == B200_OK) {
+                    run_mul_mat(st, &tmp, nullptr, gate_mm->src[0], nullptr, (int) ggml_get_glu_op(glu), alpha, limit);
+                    if (st.q8_src == &tmp) st.q8_src = nullptr;
+                    return 3;
+                }
+            }
+        }
+        // {MUL_MAT, ADD} with a single column: the addend (bias or residual stream) rides in the GEMV epilogue
+        if (n->op == GGML_OP_MUL_MAT && i + 1 < g->n_nodes && n->ne[1] == 1 && n->ne[2] == 1 && n->ne[3] == 1) {
+            ggml_tensor * add = g->nodes[i + 1];
+            if (add->op == GGML_OP_ADD && (add->src[0] == n || add->src[1] == n) && ggml_node_has_n_uses(g, i, 1) && same_shape(add, n)) {
+                const ggml_tensor * other = add->src[0] == n ? add->src[1] : add->src[0];
+                if (other->type == GGML_TYPE_F32 && other->ne[0] == n->ne[0] && ggml_nelements(other) == n->ne[0] && other->nb[0] == 4) {
+                    ggml_tensor tmp = *add;
+                    tmp.op = GGML_OP_MUL_MAT; tmp.src[0] = n->src[0]; tmp.src[1] = n->src[1]; tmp.src[2] = nullptr;
+                    exec_state probe = st; probe.validate = true;
+                    if (run_mul_mat(probe, &tmp, other, nullptr, nullptr, B200_GLU_NONE, 0, 0) == B200_OK) {
+                        run_mul_mat(st, &tmp, other, nullptr, nullptr, B200_GLU_NONE, 0, 0);
+                        return 2;
+                    }
+                }
+            }
+        }
+    }
+    const int rc = run_node(st, n);
+    if (rc != B200_OK) {
+        GGML_LOG_ERROR("ggml-b200: node %d (%s, %s) is not supported but reached graph_compute\n", i, ggml_op_name(n->op), n->name);
+        GGML_ABORT("ggml-b200: unsupported node in graph_compute (supports_op must have declined it)");
+    }
+    return 1;
+}
+
+void walk_graph(exec_state & st, ggml_cgraph * g, bool fusion) {
+    for (int i = 0; i < g->n_nodes;) {
+        ggml_tensor * n = g->nodes[i];
+        if (ggml_is_empty(n) || (n->flags & GGML_TENSOR_FLAG_COMPUTE) == 0) { ++i; continue; }
+        i += run_fused(st, g, i, fusion);
+    }
+}
+
+void grow(b200_context * ctx, char *& p, size_t & cur, size_t need, bool zero) {
+    if (need <= cur) return;
+    B200_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    if (p) B200_CUDA_CHECK(cudaFree(p));
+    cur = (need + (1u << 20)) & ~((size_t) (1u << 20) - 1);
+    B200_CUDA_CHECK(cudaMalloc((void **) &p, cur));
+    if (zero) B200_CUDA_CHECK(cudaMemset(p, 0, cur));
+    if (ctx->cache) {   // arena addresses are baked into captured graphs
+        if (ctx->cache->exec) { cudaGraphExecDestroy(ctx->cache->exec); ctx->cache->exec = nullptr; }
+        ctx->cache->seen = 0;
+    }
+}
+
+}  // namespace
+
+void b200_timing_collect(b200_context * ctx) {
+    if (!ctx->timing || !ctx->ev_pending) return;
+    float ms = 0.0f;
+    if (cudaEventElapsedTime(&ms, ctx->ev_begin, ctx->ev_end) == cudaSuccess) {
+        std::lock_guard<std::mutex> lock(b200_stats().mu);
+        b200_stats().s.device_ms_total += ms; b200_stats().s.device_ms_last = ms;
+    } else cudaGetLastError();
+    ctx->ev_pending = false;
+}
+
+ggml_status b200_graph_compute(b200_context * ctx, ggml_cgraph * g) {
+    b200_set_device(ctx->device);
+    static const bool no_graphs = env_flag("GGML_B200_DISABLE_GRAPHS"), no_fusion = env_flag("GGML_B200_DISABLE_FUSION");
+    if (!ctx->cache) ctx->cache = new b200_graph_cache;
+    b200_graph_cache & c = *ctx->cache;
+
+    // 1. has this exact graph been submitted before?
+    std::vector<node_key> keys((size_t) g->n_nodes);
+    for (int i = 0; i < g->n_nodes; ++i) make_key(g->nodes[i], keys[i]);
+    const bool same = keys.size() == c.keys.size() && (keys.empty() || memcmp(keys.data(), c.keys.data(), keys.size() * sizeof(node_key)) == 0);
+    if (!same) { c.keys.swap(keys); c.seen = 0; if (c.exec) { cudaGraphExecDestroy(c.exec); c.exec = nullptr; } }
+    c.seen++;
+
+    if (ctx->timing) {   // device time of the previous graph must be read before its events are re-recorded
+        if (ctx->ev_pending) { B200_CUDA_CHECK(cudaEventSynchronize(ctx->ev_end)); b200_timing_collect(ctx); }
+        B200_CUDA_CHECK(cudaEventRecord(ctx->ev_begin, ctx->stream));
+    }
+
+    uint64_t launched = 0; bool replay = false;
+    if (c.exec) {
+        B200_CUDA_CHECK(cudaGraphLaunch(c.exec, ctx->stream));
+        launched = c.kernels; replay = true;
+    } else {
+        // 2. size the scratch arenas (no launches)
+        exec_state sz; sz.ctx = ctx; sz.validate = false; sz.sizing = true;
+        walk_graph(sz, g, !no_fusion);
+        grow(ctx, ctx->q8_scratch, ctx->q8_size, sz.need_q8, false);
+        grow(ctx, ctx->fa_scratch, ctx->fa_size, sz.need_fa, true);
+
+        // 3. run, capturing into a CUDA graph from the second identical submission on
+        const bool capture = !no_graphs && c.seen >= 2;
+        exec_state st; st.ctx = ctx; st.validate = false; st.stream = ctx->stream;
+        if (capture) B200_CUDA_CHECK(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed));
+        walk_graph(st, g, !no_fusion);
+        launched = st.launches;
+        if (capture) {
+            cudaGraph_t graph = nullptr;
+            B200_CUDA_CHECK(cudaStreamEndCapture(ctx->stream, &graph));
+            B200_CUDA_CHECK(cudaGraphInstantiate(&c.exec, graph, 0));
+            B200_CUDA_CHECK(cudaGraphDestroy(graph));
+            c.kernels = launched;
+            B200_CUDA_CHECK(cudaGraphLaunch(c.exec, ctx->stream));
+        }
+    }
+    if (ctx->timing) { B200_CUDA_CHECK(cudaEventRecord(ctx->ev_end, ctx->stream)); ctx->ev_pending = true; }
+    {
+        std::lock_guard<std::mutex> lock(b200_stats().mu);
+        ggml_b200_stats & s = b200_stats().s;
+        s.graphs_computed++; s.graphs_replayed += replay; s.kernels_launched += launched; s.nodes_last_graph = launched;
+    }
+    return GGML_STATUS_SUCCESS;
+}
+
+void b200_context_free(b200_context * ctx) {
+    b200_set_device(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->cache) { if (ctx->cache->exec) cudaGraphExecDestroy(ctx->cache->exec); delete ctx->cache; }
+    if (ctx->q8_scratch) cudaFree(ctx->q8_scratch);
+    if (ctx->fa_scratch) cudaFree(ctx->fa_scratch);
+    if (ctx->ev_begin) cudaEventDestroy(ctx->ev_begin);
+    if (ctx->ev_end) cudaEventDestroy(ctx->ev_end);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}

@@ -161,9 +161,11 @@ extern "C" int b200_mmvq_supported(const b200_mmvq_args * a) {
         if (ids.type != B200_I32 || ids.nb[0] != 4 || ids.nb[1] % 4 != 0) return 0;
         if (d.ne[1] != ids.ne[0] || d.ne[2] != ids.ne[1] || d.ne[3] != 1 || w.ne[3] != 1) return 0;
         if (a->x_ne[2] != d.ne[2] || (a->x_ne[1] != 1 && a->x_ne[1] != d.ne[1]) || a->x_ne[3] != 1) return 0;
-        if (d.ne[1] > 65535 || d.ne[2] > 65535) return 0;
+        if (d.ne[1] > 65535 || d.ne[2] > 65535 || a->col_begin || a->col_count) return 0;
     } else {
-        if (a->x_ne[1] < 1 || a->x_ne[1] > 8 || d.ne[1] != a->x_ne[1]) return 0;
+        if (a->x_ne[1] < 1 || d.ne[1] != a->x_ne[1]) return 0;
+        if (a->col_begin < 0 || a->col_count < 0 || a->col_begin + a->col_count > a->x_ne[1]) return 0;
+        if ((a->col_count ? a->col_count : a->x_ne[1]) > 8) return 0;
         if (d.ne[2] != a->x_ne[2] || d.ne[3] != a->x_ne[3]) return 0;
         if (w.ne[2] < 1 || w.ne[3] < 1 || d.ne[2] % w.ne[2] != 0 || d.ne[3] % w.ne[3] != 0) return 0;
         if (d.ne[2] > 65535 || d.ne[3] > 65535) return 0;
@@ -213,7 +215,9 @@ extern "C" int b200_mul_mat_vec_q(const b200_mmvq_args * a, void * stream) {
         p.r2 = p.r3 = 1;
         g.y = (unsigned) d.ne[1]; g.z = (unsigned) d.ne[2];
     } else {
-        ncols = (int) a->x_ne[1];
+        ncols = a->col_count ? a->col_count : (int) a->x_ne[1];
+        p.xq += (int64_t) a->col_begin * x1;
+        p.dst += (int64_t) a->col_begin * (d.nb[1] / 4);
         p.xq_col = x1; p.xq_chan = x2; p.xq_samp = x3;
         p.dst_col = d.nb[1] / 4; p.dst_chan = d.nb[2] / 4; p.dst_samp = d.nb[3] / 4;
         p.r2 = (int32_t) (d.ne[2] / w.ne[2]); p.r3 = (int32_t) (d.ne[3] / w.ne[3]); p.ne11 = 1;

@@ -54,18 +54,23 @@ template <> struct fmt<B200_Q8_0> {
 // kvalues = {0,1,2,3,4,6,8,12, 0,-1,-2,-3,-4,-6,-8,-12} (ggml-common.h:1094): bit 3 is the sign.
 // PRMT looks up the 3-bit magnitude; a second PRMT in sign-replicate mode builds the 0xFF mask of
 // negative lanes from bit 3 of each nibble; negation is done on the integer (mag ^ m) - m.
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+    uint32_t d;   // raw PRMT: selector bit 3 = replicate the sign of the selected byte (not exposed by __byte_perm)
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+    return d;
+}
 __device__ __forceinline__ void mxfp4_expand(uint32_t q, int & lo, int & hi) {
     constexpr uint32_t T0 = 0x03020100u, T1 = 0x0c080604u;                 // magnitudes 0..7
     const uint32_t q4 = q << 4;
     // nibble order in q: n0=elem j, n1=elem j+16, n2=elem j+1, n3=elem j+17, ...
-    const uint32_t ma = __byte_perm(T0, T1, q & 0x7777u);                  // (j, j+16, j+1, j+17)
-    const uint32_t mb = __byte_perm(T0, T1, (q >> 16) & 0x7777u);          // (j+2, j+18, j+3, j+19)
-    const uint32_t sa = __byte_perm(q4, q, 0xD9C8u);                       // 0xFF where bit 3 set
-    const uint32_t sb = __byte_perm(q4, q, 0xFBEAu);
+    const uint32_t ma = prmt(T0, T1, q & 0x7777u);                  // (j, j+16, j+1, j+17)
+    const uint32_t mb = prmt(T0, T1, (q >> 16) & 0x7777u);          // (j+2, j+18, j+3, j+19)
+    const uint32_t sa = prmt(q4, q, 0xD9C8u);                       // 0xFF where bit 3 set
+    const uint32_t sb = prmt(q4, q, 0xFBEAu);
     const uint32_t va = __vsub4(ma ^ sa, sa);
     const uint32_t vb = __vsub4(mb ^ sb, sb);
-    lo = (int) __byte_perm(va, vb, 0x6420u);                               // elements j..j+3
-    hi = (int) __byte_perm(va, vb, 0x7531u);                               // elements j+16..j+19
+    lo = (int) prmt(va, vb, 0x6420u);                               // elements j..j+3
+    hi = (int) prmt(va, vb, 0x7531u);                               // elements j+16..j+19
 }
 template <> struct fmt<B200_MXFP4> {
     static constexpr int block_bytes = 17, units_per_block = 1; static constexpr bool has_min = false;

@@ -1,0 +1,153 @@
+"""GPU parity through the C ABI for the decode glue ops and flash attention
+(row A9) against the pinned C oracle.  Tolerances are written next to each check."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from conftest import ptr
+
+pytestmark = pytest.mark.gpu
+
+
+def _mods():
+    import torch
+    from llama_mi50_b200 import capi, gguf_synth
+    return torch, capi, gguf_synth
+
+
+@pytest.mark.parametrize("n,rows", [(64, 3), (4096, 1), (5120, 2), (14336, 1), (100, 5)])
+def test_rms_norm_mul_add(orc, n, rows):
+    torch, capi, _ = _mods()
+    rng = np.random.default_rng(n)
+    x = rng.standard_normal((rows, n)).astype(np.float32)
+    w = rng.standard_normal(n).astype(np.float32)
+    b = rng.standard_normal(n).astype(np.float32)
+    want = np.zeros_like(x)
+    orc.orc_rms_norm(ptr(x), ptr(want), C.c_int64(n), C.c_int64(rows), C.c_float(1e-5))
+    got = capi.rms_norm(torch.from_numpy(x).cuda(), eps=1e-5).cpu().numpy()
+    assert np.abs(got - want).max() <= 1e-5 * np.abs(want).max()          # f32 sum order only
+    got = capi.rms_norm(torch.from_numpy(x).cuda(), torch.from_numpy(w).cuda(), torch.from_numpy(b).cuda(), eps=1e-5).cpu().numpy()
+    want2 = want * w + b
+    assert np.abs(got - want2).max() <= 1e-5 * np.abs(want2).max() + 1e-6
+
+
+@pytest.mark.parametrize("op", [0, 1, 2, 3, 4, 5])
+def test_glu(orc, op):
+    torch, capi, _ = _mods()
+    rng = np.random.default_rng(op)
+    g = (rng.standard_normal((3, 1000)) * 3).astype(np.float32)
+    u = (rng.standard_normal((3, 1000)) * 3).astype(np.float32)
+    want = np.zeros_like(g)
+    orc.orc_glu(op, ptr(g), ptr(u), ptr(want), C.c_int64(g.size), C.c_float(1.702), C.c_float(7.0))
+    got = capi.glu(op, torch.from_numpy(g).cuda(), torch.from_numpy(u).cuda()).cpu().numpy()
+    assert np.abs(got - want).max() <= 2e-6 * np.abs(want).max() + 1e-6   # expf/tanhf ulp differences
+
+
+@pytest.mark.parametrize("mode", [0, 2])
+@pytest.mark.parametrize("hd,n_dims", [(64, 64), (128, 128), (128, 64)])
+def test_rope(orc, mode, hd, n_dims):
+    torch, capi, _ = _mods()
+    rng = np.random.default_rng(hd + mode)
+    n_tok, n_head = 5, 3
+    x = rng.standard_normal((n_tok, n_head, hd)).astype(np.float32)
+    pos = np.array([0, 1, 17, 511, 4095], np.int32)
+    want = np.zeros_like(x)
+    orc.orc_rope(ptr(x), ptr(want), C.c_int64(hd), C.c_int64(n_head), C.c_int64(n_tok), ptr(pos), n_dims, mode,
+                 C.c_float(10000.0), C.c_float(1.0), None)
+    got = capi.rope(torch.from_numpy(x).cuda(), torch.from_numpy(pos).cuda(), n_dims, mode).cpu().numpy()
+    # theta is pos*base^(-2i/n) via powf here vs repeated multiplication in the reference: ~1e-4 rad at pos 4095
+    assert np.abs(got - want).max() <= 2e-3
+
+
+def test_set_rows_q8_0_bit_exact_and_f16(orc):
+    """KV-cache writes: q8_0 blocks bit-exact vs quantize_row_q8_0_ref; f16 equals IEEE RNE conversion."""
+    torch, capi, _ = _mods()
+    rng = np.random.default_rng(3)
+    ne0, n, cache_rows = 1024, 4, 16
+    x = rng.standard_normal((n, ne0)).astype(np.float32)
+    idx = np.array([3, 0, 15, 7], np.int64)
+    dst = torch.zeros(cache_rows * (ne0 // 32) * 34, dtype=torch.uint8, device="cuda")
+    capi.set_rows(torch.from_numpy(x).cuda(), torch.from_numpy(idx).cuda(), dst, capi.Q8_0, [ne0, cache_rows, 1, 1])
+    got = dst.cpu().numpy().reshape(cache_rows, -1)
+    for i, r in enumerate(idx):
+        want = np.zeros(ne0 // 32 * 34, np.uint8)
+        orc.orc_quantize_row_q8_0(ptr(x[i]), ptr(want), C.c_int64(ne0))
+        assert np.array_equal(got[r], want)
+    assert not got[[1, 2, 4]].any()
+    dst16 = torch.zeros(cache_rows, ne0, dtype=torch.float16, device="cuda")
+    capi.set_rows(torch.from_numpy(x).cuda(), torch.from_numpy(idx).cuda(), dst16, capi.F16, [ne0, cache_rows, 1, 1])
+    got16 = dst16.cpu().numpy()
+    for i, r in enumerate(idx):
+        assert np.array_equal(got16[r].view(np.uint16), x[i].astype(np.float16).view(np.uint16))
+
+
+@pytest.mark.parametrize("name,t", [("q4_0", 2), ("q8_0", 8), ("q4_K", 12), ("q6_K", 14), ("mxfp4", 39)])
+def test_get_rows_dequant(orc, name, t):
+    torch, capi, gguf_synth = _mods()
+    rng = np.random.default_rng(t)
+    K, R = 512, 40
+    w = gguf_synth.make_tensor_bytes(rng, t, (K, R), sigma=0.5)
+    ids = np.array([0, 39, 7, 7, 21], np.int32)
+    got = capi.get_rows(torch.from_numpy(w).cuda(), t, [K, R, 1, 1], torch.from_numpy(ids).cuda()).cpu().numpy()
+    rb = gguf_synth.row_bytes(t, K)
+    for i, r in enumerate(ids):
+        want = np.zeros(K, np.float32)
+        orc.orc_dequantize_row(t, ptr(w[r * rb:(r + 1) * rb]), ptr(want), C.c_int64(K))
+        assert np.abs(got[i] - want).max() <= 1e-6 * np.abs(want).max()   # fma contraction only
+
+
+def _kv_bytes(orc, capi, x, kv_type):
+    """x f32 [H_kv, n_kv, D] -> packed bytes and the dequantized values the kernel sees."""
+    if kv_type == capi.F16:
+        h = x.astype(np.float16)
+        return h.view(np.uint8).reshape(-1), h.astype(np.float32)
+    flat = np.ascontiguousarray(x.reshape(-1))
+    out = np.zeros(flat.size // 32 * 34, np.uint8)
+    orc.orc_quantize_row_q8_0(ptr(flat), ptr(out), C.c_int64(flat.size))
+    deq = np.zeros(flat.size, np.float32)
+    orc.orc_dequantize_row(8, ptr(out), ptr(deq), C.c_int64(flat.size))
+    return out, deq.reshape(x.shape)
+
+
+@pytest.mark.parametrize("kv_type", ["f16", "q8_0"])
+@pytest.mark.parametrize("D,H,H_kv,n_q,n_kv", [(128, 32, 8, 1, 256), (64, 32, 4, 1, 300), (128, 40, 8, 1, 4096),
+                                                 (128, 8, 8, 2, 1000), (64, 16, 4, 35, 512), (256, 4, 1, 1, 700), (128, 64, 8, 1, 32768)])
+@pytest.mark.parametrize("extras", ["plain", "mask", "mask+sinks+softcap", "alibi"])
+def test_flash_attn_decode(orc, kv_type, D, H, H_kv, n_q, n_kv, extras):
+    torch, capi, _ = _mods()
+    if n_kv == 32768 and extras not in ("mask",):
+        pytest.skip("long-context case runs once")
+    rng = np.random.default_rng(D + H + n_kv)
+    t = capi.F16 if kv_type == "f16" else capi.Q8_0
+    q = rng.standard_normal((H, n_q, D)).astype(np.float32)
+    k = rng.standard_normal((H_kv, n_kv, D)).astype(np.float32)
+    v = rng.standard_normal((H_kv, n_kv, D)).astype(np.float32)
+    kb, kd = _kv_bytes(orc, capi, k, t)
+    vb, vd = _kv_bytes(orc, capi, v, t)
+    scale = 1.0 / np.sqrt(D)
+    mask = sinks = None
+    max_bias = softcap = 0.0
+    if "mask" in extras or extras == "alibi":
+        m = np.zeros((n_q, n_kv), np.float32)
+        for j in range(n_q):                       # causal-style tail plus a masked block
+            m[j, n_kv - (n_q - 1 - j) * 3:] = -np.inf if j < n_q - 1 else 0.0
+        m[:, n_kv // 3: n_kv // 3 + 40] = -np.inf
+        if extras == "alibi":
+            m = np.where(np.isinf(m), m, -np.abs(rng.standard_normal((n_q, n_kv))).astype(np.float32))
+            max_bias = 8.0
+        mask = m.astype(np.float16)
+    if "sinks" in extras:
+        sinks = rng.standard_normal(H).astype(np.float32)
+        softcap = 10.0
+    got = capi.flash_attn(torch.from_numpy(q).cuda(), torch.from_numpy(kb).cuda(), torch.from_numpy(vb).cuda(), t, n_kv, H_kv,
+                          mask=None if mask is None else torch.from_numpy(mask).cuda(),
+                          sinks=None if sinks is None else torch.from_numpy(sinks).cuda(),
+                          scale=scale, max_bias=max_bias, softcap=softcap).cpu().numpy()
+    want = np.zeros((n_q, H, D), np.float32)
+    mf = None if mask is None else np.ascontiguousarray(mask.astype(np.float32))
+    orc.orc_flash_attn(ptr(q), ptr(np.ascontiguousarray(kd)), ptr(np.ascontiguousarray(vd)), None if mf is None else ptr(mf),
+                       None if sinks is None else ptr(sinks), ptr(want), C.c_int64(D), C.c_int64(n_q), C.c_int64(H), C.c_int64(H_kv),
+                       C.c_int64(n_kv), C.c_float(scale), C.c_float(max_bias), C.c_float(softcap))
+    # reference gate: NMSE <= 5e-4 (tests/test-backend-ops.cpp:6082-6084); f32 math here is far tighter
+    assert orc.orc_nmse(ptr(want), ptr(np.ascontiguousarray(got)), C.c_size_t(want.size)) < 1e-8
