@@ -164,9 +164,9 @@ SHAPES = {
     "qwen2.5-32b-q8_0": ModelShape("qwen2.5-32b", "qwen2", 64, 5120, 27648, 40, 8, 128, 152064, "q8_0", 32768, 1000000.0, 1e-6, qkv_bias=True),
     "llama3-70b-q4_k_m": ModelShape("llama3-70b", "llama", 80, 8192, 28672, 64, 8, 128, 128256, "q4_k_m"),
     # test-size models (same graph topology, seconds on a CPU)
-    "tiny-q4_0": ModelShape("tiny", "llama", 2, 256, 512, 8, 2, 32, 512, "q4_0", 512, 10000.0),
+    "tiny-q4_0": ModelShape("tiny", "llama", 2, 256, 512, 4, 2, 64, 512, "q4_0", 512, 10000.0),
     "tiny-q4_k_m": ModelShape("tiny-k", "llama", 4, 512, 1024, 8, 2, 64, 1024, "q4_k_m", 512, 10000.0),
-    "tiny-q8_0": ModelShape("tiny-q8", "qwen2", 2, 256, 512, 8, 2, 32, 512, "q8_0", 512, 10000.0, 1e-6, qkv_bias=True),
+    "tiny-q8_0": ModelShape("tiny-q8", "qwen2", 2, 256, 512, 4, 2, 64, 512, "q8_0", 512, 10000.0, 1e-6, qkv_bias=True),
 }
 
 
