@@ -89,6 +89,42 @@ B200_API int b200_mmvq_supported(const b200_mmvq_args * a);
 B200_API int b200_mul_mat_vec_q(const b200_mmvq_args * a, void * stream);
 
 
+/* ---- K4s: streaming fused GEMV (the decode hot path) ---------------------------------------------
+ * One launch computes up to B200_GEMV_MAX_SEG matrix-vector products that share ONE activation
+ * column (wq/wk/wv of a layer, or ffn_gate/ffn_up), replacing the reference's sequence
+ *   rms_norm (norm.cu:476) -> mul -> quantize_q8_1 (quantize.cu:4-48) -> mul_mat_vec_q (mmvq.cu:140-356) x n
+ *   [-> add / glu (unary.cu:337)]
+ * with
+ *   prologue : x f32 [K] (optionally RMS-normalised and multiplied by norm_w) is quantised to q8_1 in
+ *              shared memory with the arithmetic of quantize_row_q8_1_ref (ggml-quants.c:225-258);
+ *   stream   : weight rows travel HBM -> shared memory as 1-D TMA bulk copies (cp.async.bulk) through
+ *              an mbarrier ring; consumer warps do the dp4a dot products out of shared memory;
+ *   epilogue : + bias / residual, or GLU pairing (segment 0 = gate, segment 1 = up, one dst).
+ * Weight tensors must be row-contiguous 2-D (nb[1] == row size) with a 16-byte aligned base, and the
+ * allocation must extend >= 16 bytes past the last row (the plugin's buffers and torch do).
+ * Kernels are chained with programmatic dependent launch: weight prefetch of launch N+1 overlaps
+ * the tail of launch N. */
+#define B200_GEMV_MAX_SEG 4
+typedef struct b200_gemv_seg {
+    b200_tensor w;              /* quantized [K, M] */
+    const b200_tensor * bias;   /* f32 [M] added to the product (bias or residual stream), or NULL */
+    b200_tensor dst;            /* f32 [M] (ignored for segment 0 of a GLU pair) */
+} b200_gemv_seg;
+typedef struct b200_gemv_fused_args {
+    b200_tensor x;                  /* f32 [K] activation column */
+    const b200_tensor * norm_w;     /* f32 [K]: x := rms_norm(x, eps) * norm_w before quantisation; NULL = none */
+    float   eps;
+    int32_t n_seg;
+    b200_gemv_seg seg[B200_GEMV_MAX_SEG];
+    int32_t glu_op;                 /* b200_glu_op; != NONE requires n_seg == 2: dst = glu(seg0) * seg1 -> seg[1].dst */
+    float   glu_alpha, glu_limit;
+    void *  xq_out;                 /* optional: the q8_1 blocks of the (normalised) activation, K/32 blocks (tests) */
+    int32_t n_sm;                   /* CTAs to launch; 0 = one per SM of the current device */
+    int32_t flags;                  /* 0. Tuning: bits 4-7 ring depth, bits 8-15 stage KiB, bit 0 bandwidth probe (no dot products) */
+} b200_gemv_fused_args;
+B200_API int b200_gemv_fused_supported(const b200_gemv_fused_args * a);
+B200_API int b200_gemv_fused(const b200_gemv_fused_args * a, void * stream);
+
 /* ---- validation mode ------------------------------------------------------------------
  * Passing B200_STREAM_VALIDATE as `stream` to any op below makes it check its arguments and
  * return B200_OK / B200_ERR_UNSUPPORTED without touching the GPU.  The plugin's supports_op uses

@@ -256,3 +256,46 @@ def flash_attn(q, k_bytes, v_bytes, kv_type, n_kv, H_kv, mask=None, sinks=None, 
     a.scratch, a.scratch_size = scratch.data_ptr(), n
     check(L.b200_flash_attn_ext(C.byref(a), stream_ptr()), "flash_attn_ext")
     return dst
+
+
+# ----------------------------------------------------------------------------- K4s: streaming fused GEMV
+class GemvSeg(C.Structure):
+    _fields_ = [("w", Tensor), ("bias", C.POINTER(Tensor)), ("dst", Tensor)]
+
+
+class GemvFusedArgs(C.Structure):
+    _fields_ = [("x", Tensor), ("norm_w", C.POINTER(Tensor)), ("eps", C.c_float), ("n_seg", C.c_int32),
+                ("seg", GemvSeg * 4), ("glu_op", C.c_int32), ("glu_alpha", C.c_float), ("glu_limit", C.c_float),
+                ("xq_out", C.c_void_p), ("n_sm", C.c_int32), ("flags", C.c_int32)]
+
+
+def gemv_fused_args(x, segs, norm_w=None, eps=0.0, glu_op=GLU_NONE, alpha=1.702, limit=7.0, xq_out=None, n_sm=0, flags=0, keep=None):
+    """Build a b200_gemv_fused_args. x: CUDA f32 [K]; segs: list of (w_bytes, wtype, M, bias|None, dst|None).
+    `keep` collects the descriptors that must stay alive while launches referencing them are captured."""
+    keep = keep if keep is not None else []
+    K = x.numel()
+    a = GemvFusedArgs()
+    a.x = make_tensor(x.data_ptr(), F32, [K, 1, 1, 1])
+    if norm_w is not None:
+        tn = make_tensor(norm_w.data_ptr(), F32, [K, 1, 1, 1]); keep.append(tn); a.norm_w = C.pointer(tn)
+    a.eps, a.n_seg = eps, len(segs)
+    for i, (wb, wt, M, bias, dst) in enumerate(segs):
+        a.seg[i].w = make_tensor(wb.data_ptr(), wt, [K, M, 1, 1])
+        if bias is not None:
+            tb = make_tensor(bias.data_ptr(), F32, [M, 1, 1, 1]); keep.append(tb); a.seg[i].bias = C.pointer(tb)
+        if dst is not None:
+            a.seg[i].dst = make_tensor(dst.data_ptr(), F32, [M, 1, 1, 1])
+    a.glu_op, a.glu_alpha, a.glu_limit = glu_op, alpha, limit
+    a.xq_out = xq_out.data_ptr() if xq_out is not None else None
+    a.n_sm, a.flags = n_sm, flags
+    keep.append(a)
+    return a
+
+
+def gemv_fused(x, segs, **kw):
+    L = lib()
+    L.b200_gemv_fused.argtypes = [C.c_void_p, C.c_void_p]
+    L.b200_gemv_fused_supported.argtypes = [C.c_void_p]
+    keep = []
+    a = gemv_fused_args(x, segs, keep=keep, **kw)
+    check(L.b200_gemv_fused(C.byref(a), stream_ptr()), "gemv_fused")

@@ -72,6 +72,7 @@ class DecodeSession:
         L.b200_fattn_scratch_size.restype = C.c_size_t
         L.b200_fattn_scratch_size.argtypes = [vp]
         L.b200_flash_attn_ext.argtypes = [vp, vp]
+        L.b200_gemv_fused.argtypes = [vp, vp]
 
     def _t(self, x, ttype=None, ne=None, nb=None):
         """descriptor of a torch CUDA tensor (kept alive)."""
@@ -96,9 +97,11 @@ class DecodeSession:
                 rb = gguf_synth.row_bytes(t, ne[0])
                 data = data[lo * rb:hi * rb]
                 ne = (ne[0], hi - lo)
-            dev = torch.from_numpy(np.ascontiguousarray(data)).to(self.dev)
             if t == F32:
-                dev = dev.view(torch.float32)
+                dev = torch.from_numpy(np.ascontiguousarray(data)).to(self.dev).view(torch.float32)
+            else:   # >= 16 B of slack after the last row: bulk copies round their end up to 16 B
+                dev = torch.zeros(data.nbytes + 64, dtype=torch.uint8, device=self.dev)
+                dev[:data.nbytes] = torch.from_numpy(np.ascontiguousarray(data)).to(self.dev)
             self.w[name] = (dev, t, ne)
             if is_mat and name != "token_embd.weight":
                 self.weight_bytes_local += data.nbytes
@@ -182,17 +185,43 @@ class DecodeSession:
             lo, hi = row_split(dst.shape[-1], self.world, self.rank)
             self.gather(out.view(-1), dst.view(-1), lo, hi)
 
+    def _gemv(self, x, segs, norm=None, glu=capi.GLU_NONE):
+        """streaming fused GEMV: segs = [(weight name, bias tensor|None, dst tensor|None)]; all share activation x.
+        Under row split every segment's local slice is gathered into its dst."""
+        split = self.world > 1
+        csegs, post, o = [], [], 0
+        for wname, bias, dst in segs:
+            wd, t, (K, M) = self.w[wname]
+            out = dst
+            if dst is not None and split:
+                lo, hi = row_split(dst.numel(), self.world, self.rank)
+                out = self.loc[o:o + M]; o += M
+                post.append((out, dst, lo, hi))
+                bias = bias.view(-1)[lo:hi] if bias is not None else None
+            csegs.append((wd, t, M, bias, out))
+        nw = self.w[norm][0] if norm else None
+        a = capi.gemv_fused_args(x.view(-1), csegs, norm_w=nw, eps=self.s.rms_eps, glu_op=glu, keep=self.keep)
+        self._chk(self.L.b200_gemv_fused(C.byref(a), self._st()), "gemv_fused")
+        for out, dst, lo, hi in post:
+            self.gather(out, dst.view(-1), lo, hi)
+
     def _norm(self, x, wname, dst):
         tx, tw, td = self._t(x), self._t(self.w[wname][0].view(1, -1)), self._t(dst)
         self._chk(self.L.b200_rms_norm(C.byref(tx), C.byref(tw), None, C.byref(td), self.s.rms_eps, self._st()), "rms_norm")
 
-    def _rope(self, x, dst, n_head):
+    def _rope(self, x, dst, n_head, cache=None):
+        """RoPE; with `cache` the rotated row goes straight into the KV cache slot (fused SET_ROWS, f16 cache)."""
         s = self.s
         mode = 2 if s.arch == "qwen2" else 0
         rp = capi.RopeParams(s.head_dim, mode, s.n_ctx_train, s.rope_base, 1.0, 0.0, 1.0, 32.0, 1.0)
         tx = self._t(x.view(1, n_head, s.head_dim)); td = self._t(dst.view(1, n_head, s.head_dim)); tp = self._t(self.pos)
         self.keep.append(rp)
-        self._chk(self.L.b200_rope(C.byref(tx), C.byref(tp), None, C.byref(td), C.byref(rp), None, None, self._st()), "rope")
+        ti = tc = None
+        if cache is not None:
+            ti = self._t(self.slot)
+            tc = self._t(cache, self.kv_type, [n_head * s.head_dim, self.n_ctx, 1, 1])
+        self._chk(self.L.b200_rope(C.byref(tx), C.byref(tp), None, C.byref(td), C.byref(rp),
+                                   C.byref(ti) if ti else None, C.byref(tc) if tc else None, self._st()), "rope")
 
     def _set_row(self, src, cache):
         KVD = self.s.n_head_kv * self.s.head_dim
@@ -235,6 +264,23 @@ class DecodeSession:
         x, x2 = self.x, self.x2
         for il in range(s.n_layer):
             p = f"blk.{il}."
+            if self.fused:
+                self._gemv(x, [(p + "attn_q.weight", self._full_bias(p + "attn_q.bias"), self.q),
+                               (p + "attn_k.weight", self._full_bias(p + "attn_k.bias"), self.k),
+                               (p + "attn_v.weight", self._full_bias(p + "attn_v.bias"), self.v)], norm=p + "attn_norm.weight")
+                self._rope(self.q, self.qr, s.n_head)
+                if self.kv_type == F16:
+                    self._rope(self.k, self.kr, s.n_head_kv, cache=self.kc[il])
+                else:
+                    self._rope(self.k, self.kr, s.n_head_kv)
+                    self._set_row(self.kr, self.kc[il])
+                self._set_row(self.v, self.vc[il])
+                self._attn(il, n_kv)
+                self._gemv(self.att, [(p + "attn_output.weight", x, x2)])
+                self._gemv(x2, [(p + "ffn_gate.weight", None, None), (p + "ffn_up.weight", None, self.ff)],
+                           norm=p + "ffn_norm.weight", glu=capi.GLU_SWIGLU)
+                self._gemv(self.ff, [(p + "ffn_down.weight", x2, x)])
+                continue
             self._norm(x, p + "attn_norm.weight", self.h)
             self._mm(p + "attn_q.weight", self.h, self.q, bias=self._full_bias(p + "attn_q.bias"))
             self._mm(p + "attn_k.weight", self.h, self.k, bias=self._full_bias(p + "attn_k.bias"), requant=False)
@@ -248,8 +294,11 @@ class DecodeSession:
             self._norm(x2, p + "ffn_norm.weight", self.h)
             self._mm(p + "ffn_up.weight", self.h, self.ff, gate=p + "ffn_gate.weight", glu=capi.GLU_SWIGLU)
             self._mm(p + "ffn_down.weight", self.ff, x, bias=x2)
-        self._norm(x, "output_norm.weight", self.h)
-        self._mm("output.weight", self.h, self.logits)
+        if self.fused:
+            self._gemv(x, [("output.weight", None, self.logits)], norm="output_norm.weight")
+        else:
+            self._norm(x, "output_norm.weight", self.h)
+            self._mm("output.weight", self.h, self.logits)
         self.pos.add_(1); self.slot.add_(1)
         return self._n
 
@@ -301,6 +350,17 @@ class DecodeSession:
 
         def issue():
             self._n = 0
+            for il in range(s.n_layer if self.fused else 0):
+                p = f"blk.{il}."
+                self._gemv(self.x, [(p + "attn_q.weight", None, self.q), (p + "attn_k.weight", None, self.k),
+                                    (p + "attn_v.weight", None, self.v)], norm=p + "attn_norm.weight")
+                self._gemv(self.att, [(p + "attn_output.weight", self.x, self.x2)])
+                self._gemv(self.x2, [(p + "ffn_gate.weight", None, None), (p + "ffn_up.weight", None, self.ff)],
+                           norm=p + "ffn_norm.weight", glu=capi.GLU_SWIGLU)
+                self._gemv(self.ff, [(p + "ffn_down.weight", self.x2, self.x)])
+            if self.fused:
+                self._gemv(self.x, [("output.weight", None, self.logits)], norm="output_norm.weight")
+                return self._n
             for il in range(s.n_layer):
                 p = f"blk.{il}."
                 self._mm(p + "attn_q.weight", self.h, self.q, requant=False)

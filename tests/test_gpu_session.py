@@ -80,13 +80,13 @@ def reference_decode(orc, gs, shape, weights, tokens):
 
 
 @pytest.mark.parametrize("key", ["tiny-q4_0", "tiny-q4_k_m", "tiny-q8_0"])
-@pytest.mark.parametrize("graph", [False, True])
-def test_decode_session_vs_numpy(orc, key, graph):
+@pytest.mark.parametrize("graph,fused", [(False, True), (True, True), (False, False)])
+def test_decode_session_vs_numpy(orc, key, graph, fused):
     import torch
     from llama_mi50_b200 import gguf_synth as gs
     from llama_mi50_b200.session import DecodeSession
     shape = gs.SHAPES[key]
-    sess = DecodeSession(shape, n_ctx=256)
+    sess = DecodeSession(shape, n_ctx=256, fused=fused)
     weights = {n: (d.cpu().numpy().view(np.uint8).reshape(-1), t, ne) for n, (d, t, ne) in sess.w.items()}
     tokens = [3, 77, 5, 130, 9, 250]
     want = reference_decode(orc, gs, shape, weights, tokens)
