@@ -185,7 +185,9 @@ def main_b200(a):
     if world > 1:
         from llama_mi50_b200.rowsplit import make_gather
         gather = make_gather(dist, world, rank)
-    sess = DecodeSession(shape, n_ctx=n_ctx, rank=rank, world=world, gather=gather)
+    mode = {"chain": "chain", "fused": True, "basic": False}[a.mode if world == 1 or a.mode != "chain" else "fused"]
+    sess = DecodeSession(shape, n_ctx=n_ctx, rank=rank, world=world, gather=gather, fused=mode)
+    sess.chain_flags = a.chain_flags
     sess.capture(sess.n_kv_for(N_GEN - 1))
     lib = capi.lib()
 
@@ -271,7 +273,7 @@ def main_b200(a):
             "warmup": a.warmup, "ms_per_step": round(ms_per_step, 3), "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "int8 x int4/6 dp4a, f32 accumulate", "data": "synthetic",
             "config": {"workload": key, "n_gen": N_GEN, "n_kv": n_ctx, "kv_type": "f16", "flash_attn": 1,
-                       "parallelism": f"row-split tp{world}" if world > 1 else "single GPU",
+                       "parallelism": f"row-split tp{world}" if world > 1 else "single GPU", "issue": a.mode,
                        "l2": "inputs larger than L2 (weights %.2f GB per token vs 126 MB L2)" % (wbytes / 1e9)},
             "roofline": roofline, "clocks": clocks, "gpu_launches": gpu_launches,
             "e2e": {"value": round(e2e_cabi, 2), "unit": "tok/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -315,6 +317,9 @@ if __name__ == "__main__":
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="llama3-8b", choices=sorted(WORKLOADS))
     ap.add_argument("--no-llama-bench", action="store_true", help="skip the llama-bench/plugin and CPU-baseline legs")
+    ap.add_argument("--mode", default="chain", choices=["chain", "fused", "basic"],
+                    help="chain: one cooperative launch per token; fused: one streaming-GEMV launch per matmul group; basic: unfused ops")
+    ap.add_argument("--chain-flags", type=lambda x: int(x, 0), default=0)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     sys.exit(main_reference(args) if args.impl == "reference" else main_b200(args))

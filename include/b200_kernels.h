@@ -125,6 +125,43 @@ typedef struct b200_gemv_fused_args {
 B200_API int b200_gemv_fused_supported(const b200_gemv_fused_args * a);
 B200_API int b200_gemv_fused(const b200_gemv_fused_args * a, void * stream);
 
+typedef struct b200_rope_params {
+    int32_t n_dims, mode, n_ctx_orig;
+    float freq_base, freq_scale, ext_factor, attn_factor, beta_fast, beta_slow;
+} b200_rope_params;
+
+/* ---- decode chain: every matmul of a token in ONE cooperative launch -------------------------------
+ * A chain is a list of phases run by the persistent streaming-GEMV kernel: GEMV phases (exactly the
+ * arguments of b200_gemv_fused) and attention phases (one query position: RoPE(q), RoPE(k), the KV-cache
+ * write and flash attention over an f16 cache — reference rope.cu:563, set-rows.cu:318,
+ * fattn-vec.cuh:19-507).  Phase i may read anything phase i-1 wrote: phases are separated by in-kernel grid
+ * barriers which only the consuming warps wait on, while the producer warp keeps streaming the next
+ * phase's weights, so HBM does not drain at matmul boundaries (the reference pays one launch + one
+ * quantize launch per matmul).  All pointers are captured at create time. */
+enum b200_phase_kind { B200_PHASE_GEMV = 0, B200_PHASE_ATTN = 1 };
+typedef struct b200_attn_phase {
+    b200_tensor q, k_new, v_new;     /* f32 raw projections of the current token: [D*H], [D*H_kv], [D*H_kv] */
+    b200_tensor k_cache, v_cache;    /* f16 [D, n_kv, H_kv] views of the layer's cache (nb[1] = position stride) */
+    const b200_tensor * pos;         /* i32 [1]: position of the token (RoPE) */
+    const b200_tensor * slot;        /* i64 [1]: cache row the token is written to */
+    const b200_tensor * mask;        /* f16 [n_kv] (0 / -inf) or NULL */
+    b200_rope_params rope;           /* modes NORMAL(0) / NEOX(2), no YaRN (ext_factor 0, attn_factor 1) */
+    float scale;
+    b200_tensor dst;                 /* f32 [D*H] */
+} b200_attn_phase;
+typedef struct b200_phase {
+    int32_t kind;                    /* b200_phase_kind */
+    int32_t _pad;
+    b200_gemv_fused_args gemv;
+    b200_attn_phase attn;
+} b200_phase;
+typedef struct b200_chain b200_chain;
+B200_API b200_chain * b200_chain_create(const b200_phase * phases, int n_phases, int flags);   /* NULL: see b200_last_error() */
+B200_API int          b200_chain_launch(b200_chain * chain, void * stream);
+B200_API void         b200_chain_destroy(b200_chain * chain);
+/* flags bit 2 at create time: per-phase globaltimer stamps of the first and last CTA (tools/timeline_chain.py) */
+B200_API int          b200_chain_debug_read(b200_chain * chain, unsigned long long * out, int n_phases);
+
 /* ---- validation mode ------------------------------------------------------------------
  * Passing B200_STREAM_VALIDATE as `stream` to any op below makes it check its arguments and
  * return B200_OK / B200_ERR_UNSUPPORTED without touching the GPU.  The plugin's supports_op uses
@@ -167,10 +204,7 @@ B200_API int b200_cpy(const b200_tensor * src, const b200_tensor * dst, void * s
 B200_API int b200_set_rows(const b200_tensor * src, const b200_tensor * idx, const b200_tensor * dst, void * stream);
 
 /* ROPE (rope.cu:563): modes NORMAL(0) and NEOX(2); YaRN parameters as in ggml_rope_ext */
-typedef struct b200_rope_params {
-    int32_t n_dims, mode, n_ctx_orig;
-    float freq_base, freq_scale, ext_factor, attn_factor, beta_fast, beta_slow;
-} b200_rope_params;
+/* b200_rope_params: declared above (decode chain section) */
 /* x f32 [head_dim, n_head, n_tok, 1]; pos i32 [n_tok]; freq_factors f32 [n_dims/2] or NULL.
  * Optional fused SET_ROWS (ggml-cuda.cu:3614-3621): when set_idx != NULL the rotated rows are written
  * to set_dst (f16/f32 rows of head_dim*n_head elements, row index from set_idx) instead of dst. */

@@ -299,3 +299,52 @@ def gemv_fused(x, segs, **kw):
     keep = []
     a = gemv_fused_args(x, segs, keep=keep, **kw)
     check(L.b200_gemv_fused(C.byref(a), stream_ptr()), "gemv_fused")
+
+
+# ----------------------------------------------------------------------------- decode chain
+class AttnPhase(C.Structure):
+    _fields_ = [("q", Tensor), ("k_new", Tensor), ("v_new", Tensor), ("k_cache", Tensor), ("v_cache", Tensor),
+                ("pos", C.POINTER(Tensor)), ("slot", C.POINTER(Tensor)), ("mask", C.POINTER(Tensor)),
+                ("rope", RopeParams), ("scale", C.c_float), ("dst", Tensor)]
+
+
+class Phase(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("_pad", C.c_int32), ("gemv", GemvFusedArgs), ("attn", AttnPhase)]
+
+
+PHASE_GEMV, PHASE_ATTN = 0, 1
+
+
+class Chain:
+    """Owns a b200_chain (device-side phase descriptors). launch() is capturable into a CUDA graph."""
+
+    def __init__(self, phases, flags=0, keep=None):
+        L = lib()
+        L.b200_chain_create.restype = C.c_void_p
+        L.b200_chain_create.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.b200_chain_launch.argtypes = [C.c_void_p, C.c_void_p]
+        L.b200_chain_destroy.argtypes = [C.c_void_p]
+        arr = (Phase * len(phases))(*phases)
+        self._keep = (arr, keep)
+        self.n = len(phases)
+        self.h = L.b200_chain_create(arr, len(phases), flags)
+        if not self.h:
+            raise RuntimeError("b200_chain_create: " + L.b200_last_error().decode())
+
+    def launch(self):
+        check(lib().b200_chain_launch(self.h, stream_ptr()), "chain_launch")
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib().b200_chain_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+
+def gemv_phase(x, segs, **kw):
+    ph = Phase()
+    ph.kind = PHASE_GEMV
+    ph.gemv = gemv_fused_args(x, segs, **kw)
+    return ph

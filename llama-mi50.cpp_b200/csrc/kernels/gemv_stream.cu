@@ -5,36 +5,43 @@
 // for up to 4 weight matrices that share one activation column.
 //
 // B200 design (see DESIGN.md "K4s"):
-//   * persistent CTAs, one (or two co-resident across consecutive launches) per SM; the rows of all
-//     segments are split across CTAs by BYTES, so every SM streams the same amount of HBM;
+//   * persistent CTAs, one per SM; the rows of all segments are split across CTAs by BYTES, so every SM
+//     streams the same amount of HBM;
 //   * a producer warp moves weight rows HBM -> shared memory with 1-D TMA bulk copies
-//     (cp.async.bulk ... mbarrier::complete_tx) into a 3-stage ring; alignment of the odd block formats
-//     (18/34/17/210-byte blocks) is paid on shared memory reads, never on HBM transactions;
-//   * 8 consumer warps do dp4a dot products out of shared memory against the q8_1 activation held in
-//     shared memory (quantised once per CTA in the prologue, bank-conflict-free padded layout);
+//     (cp.async.bulk ... mbarrier::complete_tx) into a ring of 3 x ~56 KB stages (measured: HBM efficiency of the
+//     bulk copies needs >= ~32 KB per copy); alignment of the odd block formats (18/34/17/210-byte blocks)
+//     is paid on shared memory reads, never on HBM transactions;
+//   * 16 consumer warps do dp4a dot products out of shared memory against the q8_1 activation
+//     (quantised once per CTA in the prologue; hoisted into registers per segment);
 //   * a finalizer warp reduces the per-lane partial sums and applies the epilogue (bias/residual, GLU)
 //     so consumers never wait on a shuffle chain or a CTA-wide barrier in the main loop;
 //   * programmatic dependent launch: the producer starts prefetching weights before the previous kernel
-//     in the stream has finished; only the activation read waits (griddepcontrol.wait).
+//     in the stream has finished; only the activation read waits (griddepcontrol.wait);
+//   * DECODE CHAIN (b200_chain_*): the same kernel runs a LIST of phases (every matmul of every layer plus an
+//     attention phase with RoPE and the KV-cache write fused in) in ONE cooperative launch; phases are separated
+//     by in-kernel grid barriers that only the consumers wait on — the producer keeps streaming the next phase's
+//     weights into the ring, so HBM never drains at a matmul boundary.
 #include <algorithm>
 #include <cstring>
+#include <vector>
 
 #include "quantize.cuh"
 #include "vecdot.cuh"
 
 namespace b200 {
 
-constexpr int GS_NW          = 8;                      // consumer warps
-constexpr int GS_THREADS     = (GS_NW + 2) * 32;       // + producer warp + finalizer warp
-constexpr int GS_PRO_THREADS = (GS_NW + 1) * 32;       // warps that run the prologue (all but the producer)
+constexpr int GS_NW          = 16;                     // consumer warps (4 per scheduler)
+constexpr int GS_THREADS     = (GS_NW + 1) * 32;       // + producer warp
+constexpr int GS_CON_THREADS = GS_NW * 32;
+constexpr int GS_PRO_THREADS = GS_CON_THREADS;         // warps that run the prologue (all but the producer)
 constexpr int GS_STAGES      = 3;                      // default ring depth
 constexpr int GS_MAX_STAGES  = 8;
-constexpr int GS_STAGE_BYTES = 24 * 1024;              // preferred payload capacity of a stage (runtime: gs_params::stage_stride)
+constexpr int GS_STAGE_BYTES = 56 * 1024;              // preferred stage payload: HBM efficiency needs >= ~32 KB per bulk copy
 constexpr int GS_STAGE_SLACK = 128;                    // slack for 16 B alignment of both ends / funnel over-read
-constexpr int GS_RED_FLOATS  = 1280;                   // per parity: rows * (KS*32 + 4) <= GS_RED_FLOATS
-constexpr int GS_SMEM_2CTA   = 112 * 1024;             // budget that still lets two CTAs share an SM (PDL overlap)
-constexpr int GS_SMEM_MAX    = 224 * 1024;
-constexpr int GS_RB          = 2;                      // rows per warp pass (activation registers reused across them)
+constexpr int GS_RED_FLOATS  = 2304;                   // per parity: rows * (KS*32 + 4) <= GS_RED_FLOATS
+constexpr int GS_SMEM_MAX    = 220 * 1024;             // dynamic; ~3 KB of static shared memory on top
+constexpr int GS_RB          = 2;                      // rows per warp pass (two independent dp4a chains)
+constexpr int GS_MAX_PHASES  = 1024;
 
 struct gs_seg {
     const uint8_t * w[2];     // [1] = paired "up" matrix of a GLU work segment (else null)
@@ -45,17 +52,36 @@ struct gs_seg {
     int32_t R, KS, spr, ipr;       // rows per chunk, warps along K, steps per row, items per row
     int32_t spw, _pad;             // K-steps per warp (1, 2 or 4): the per-step activation registers are hoisted
 };
-struct gs_params {
+// attention phase of the decode chain: one query position, f16 KV cache, RoPE + KV-cache write fused in
+struct gs_attn {
+    const float * q; const float * k_new; const float * v_new;   // raw projections of the current token
+    char * k_cache; char * v_cache; const __half * mask; float * dst;
+    const int32_t * pos; const int64_t * slot;
+    int64_t k_nb1, k_nb2, v_nb1, v_nb2;
+    int32_t D, H, H_kv, n_kv, rope_mode, n_dims;
+    float scale, theta_scale, freq_scale;
+};
+struct alignas(16) gs_phase {
+    int32_t kind;                  // 0 = GEMV, 1 = attention
+    int32_t n_ws;                  // work segments (GEMV)
     gs_seg seg[B200_GEMV_MAX_SEG];
-    int32_t n_ws;                  // work segments
     int32_t glu_op; float glu_alpha, glu_limit;
     const float * x; const float * norm_w; float eps; int32_t K;
     blk_q8_1 * xq_out;
     int64_t total_bytes;
-    int32_t act_qs_bytes;
+    gs_attn attn;
+};
+struct gs_params {
+    gs_phase inl;                  // the phase of a single-phase launch (b200_gemv_fused)
+    const gs_phase * phases;       // device array for a chain (null: use inl)
+    unsigned int * bar;            // one arrival counter per phase (zeroed before the launch)
+    int32_t n_phases;
+    int32_t act_qs_bytes;          // activation region sized for the largest K of the chain
     int32_t stage_stride;          // bytes between ring stages (payload + GS_STAGE_SLACK, multiple of 128)
     int32_t n_stages;              // ring depth
+    int32_t attn_floats;           // attention scratch (floats) after the activation scales
     int32_t flags;                 // tuning/debug: bit 0 = consumers skip the dot products (bandwidth probe)
+    unsigned long long * dbg;      // flags bit 2: globaltimer stamps [phase][cta 0 | last cta][4]
 };
 
 // ---------------------------------------------------------------- PTX helpers
@@ -319,170 +345,201 @@ __device__ __forceinline__ float gs_glu(int op, float g, float x, float alpha, f
     }
 }
 
-// ring / reduction-buffer position carried by every role across the segments of a launch
+// ring position carried by the producer and the consumers across the segments and phases of a launch
 struct gs_pos {
     int st = 0, full_par = 0;      // ring stage, parity of its "full" phase
-    int rp = 0, red_par = 0;       // reduction buffer, parity of its phase
     int ns = GS_STAGES;
-    int dbg = 0;
-    __device__ __forceinline__ void next() {
-        ++dbg;
-        if (++st == ns) { st = 0; full_par ^= 1; }
-        if (rp) red_par ^= 1;
-        rp ^= 1;
-    }
+    __device__ __forceinline__ void next() { if (++st == ns) { st = 0; full_par ^= 1; } }
 };
-
-// timeline probe (flags bit 2): CTA 0 records clock64() stamps per chunk into xq_out viewed as long long[3][4096][4]
-#define GS_STAMP(role, n, k) do { if ((p.flags & 4) && blockIdx.x == 0 && (n) < 4096) ((long long *) p.xq_out)[((role) * 4096 + (n)) * 4 + (k)] = clock64(); } while (0)
 
 struct gs_shared {
-    uint64_t full[GS_MAX_STAGES], empty[GS_MAX_STAGES], rfull[2], rempty[2];
-    float part[GS_NW + 1];
+    uint64_t full[GS_MAX_STAGES], empty[GS_MAX_STAGES];
+    float part[GS_NW];
+    float slots[2][GS_NW][GS_RB];  // per-warp row sums of a pass, combined across the KS warps of a row group
 };
 
-// consumer warps: all chunks of one work segment
-template <int TYPE, int SPW>
-__device__ __forceinline__ void consume_segment(const gs_params & p, const gs_seg & sg, int r0, int r1, gs_pos & pos, gs_shared & sh,
-                                                uint8_t * ring, float * red, const uint8_t * aq, const float2 * ads, int warp, int lane) {
+struct gs_ctx {                    // per-thread view of the launch-wide shared memory carve-up
+    uint8_t * ring; uint8_t * aq; float2 * ads; float * attn; gs_shared * sh;
+    int stage_stride, flags;
+};
+
+__device__ __forceinline__ void gs_row_range(const gs_seg & sg, int64_t lo, int64_t hi, int & r0, int & r1) {
+    const int64_t rbw = (int64_t) sg.rb * sg.nsub, tot = rbw * sg.M;
+    const int64_t a = min(max(lo - sg.byte_prefix, (int64_t) 0), tot), b = min(max(hi - sg.byte_prefix, (int64_t) 0), tot);
+    r0 = (int) ((a + rbw - 1) / rbw); r1 = (int) ((b + rbw - 1) / rbw);
+}
+
+// consumer warps: all chunks of one work segment.  A pass of a warp covers GS_RB rows (for a GLU pair: the gate row and the
+// up row of ONE output row); the KS warps of a row group each own a K slice, reduce their lanes by shuffles and meet at a
+// named barrier of their own; warp ks == 0 sums the KS values in fixed order, applies the epilogue and stores.
+template <int TYPE, int SPW, bool COHERENT>
+__device__ __forceinline__ void consume_segment(const gs_ctx & c, const gs_phase & ph, const gs_seg & sg, int r0, int r1, gs_pos & pos, int warp, int lane) {
     const int KS = sg.KS, ksl = 31 - __clz(KS), ks = warp & (KS - 1), rg = warp >> ksl, RG = GS_NW >> ksl;
     item<TYPE> itm[SPW];
 #pragma unroll
-    for (int s = 0; s < SPW; ++s) itm[s].init((ks + s * KS) * 32 + lane, sg.ipr, aq, ads);
-    const int rstride = KS * 32 + 4, rbase = ks * 32 + lane, vstep = RG * GS_RB, rb = sg.rb, R = sg.R;
+    for (int s = 0; s < SPW; ++s) itm[s].init((ks + s * KS) * 32 + lane, sg.ipr, c.aq, c.ads);
+    const int rb = sg.rb, R = sg.R;
     const bool pair = sg.nsub == 2;
+    const int rpp = pair ? 1 : GS_RB;                      // output rows per warp pass
+    const float * __restrict__ bias = sg.bias;
+    float * __restrict__ dst = sg.dst;
+    const int glu_op = ph.glu_op; const float glu_alpha = ph.glu_alpha, glu_limit = ph.glu_limit;
     uint32_t ga0 = (uint32_t) ((uintptr_t) (sg.w[0] + (int64_t) r0 * rb) & 15);
     uint32_t ga1 = pair ? (uint32_t) ((uintptr_t) (sg.w[1] + (int64_t) r0 * rb) & 15) : 0u;
     const uint32_t gstep = (uint32_t) R * (uint32_t) rb;
+    gs_shared & sh = *c.sh;
+    int par = 0;
     for (int row = r0; row < r1; row += R) {
-        const int nr = min(R, r1 - row), nv = pair ? 2 * nr : nr;
-        const uint8_t * sub0 = ring + pos.st * p.stage_stride + ga0;
+        const int nr = min(R, r1 - row);
+        const uint8_t * sub0 = c.ring + pos.st * c.stage_stride + ga0;
         const uint8_t * sub1 = sub0 - ga0 + ((ga0 + (uint32_t) nr * rb + 15u) & ~15u) + ga1;
-        float * r = red + pos.rp * GS_RED_FLOATS + rbase;
         mbar_wait(&sh.full[pos.st], pos.full_par);
-        if (warp == 0 && lane == 0) GS_STAMP(1, pos.dbg, 0);
-        bool red_free = false;
-        for (int vb = rg * GS_RB; vb < nv; vb += vstep) {
+        for (int jb = rg * rpp; jb < nr; jb += RG * rpp) {
             const uint8_t * rowp[GS_RB];
+            if (pair) { rowp[0] = sub0 + jb * rb; rowp[1] = sub1 + jb * rb; }
+            else {
+#pragma unroll
+                for (int j = 0; j < GS_RB; ++j) rowp[j] = sub0 + min(jb + j, nr - 1) * rb;     // clamp: a duplicate row is computed and dropped
+            }
+            float bv[GS_RB];                               // epilogue operand, requested before the dot products
 #pragma unroll
             for (int j = 0; j < GS_RB; ++j) {
-                const int v = min(vb + j, nv - 1);                   // clamp: a duplicate row is computed and dropped
-                rowp[j] = v < nr ? sub0 + v * rb : sub1 + (v - nr) * rb;
+                bv[j] = 0.0f;
+                if (bias && ks == 0 && lane == 0 && j < rpp && jb + j < nr) bv[j] = COHERENT ? __ldcg(bias + row + jb + j) : bias[row + jb + j];
             }
             float acc[GS_RB];
 #pragma unroll
             for (int j = 0; j < GS_RB; ++j) acc[j] = 0.0f;
-            if (!(p.flags & 1)) {
+            if (!(c.flags & 1)) {
 #pragma unroll
                 for (int s = 0; s < SPW; ++s)
                     if (itm[s].ok) itm[s].template dot<GS_RB>(rowp, acc);
             }
-            if (!red_free) { mbar_wait(&sh.rempty[pos.rp], pos.red_par ^ 1); red_free = true; }
 #pragma unroll
-            for (int j = 0; j < GS_RB; ++j)
-                if (vb + j < nv) r[(vb + j) * rstride] = acc[j];
+            for (int j = 0; j < GS_RB; ++j) acc[j] = warp_sum(acc[j]);
+            if (KS > 1) {
+                if (lane == 0) {
+#pragma unroll
+                    for (int j = 0; j < GS_RB; ++j) sh.slots[par][warp][j] = acc[j];
+                }
+                named_bar_sync(4 + rg, KS * 32);
+                if (ks == 0 && lane == 0) {
+#pragma unroll
+                    for (int j = 0; j < GS_RB; ++j) {
+                        float t = 0.0f;
+                        for (int k = 0; k < KS; ++k) t += sh.slots[par][warp + k][j];
+                        acc[j] = t;
+                    }
+                }
+                par ^= 1;
+            }
+            if (ks == 0 && lane == 0) {
+                if (pair) {
+                    dst[row + jb] = gs_glu(glu_op, acc[0], acc[1], glu_alpha, glu_limit) + bv[0];
+                } else {
+#pragma unroll
+                    for (int j = 0; j < GS_RB; ++j)
+                        if (jb + j < nr) dst[row + jb + j] = acc[j] + bv[j];
+                }
+            }
         }
-        // every warp must observe the reduction buffer being released, even one without rows in this chunk:
-        // its arrival below must not land in the buffer's previous phase
-        if (!red_free) mbar_wait(&sh.rempty[pos.rp], pos.red_par ^ 1);
         __syncwarp();
-        if (warp == 0 && lane == 0) GS_STAMP(1, pos.dbg, 1);
-        if (lane == 0) { mbar_arrive(&sh.empty[pos.st]); mbar_arrive(&sh.rfull[pos.rp]); }
-        if (warp == 0 && lane == 0) GS_STAMP(1, pos.dbg, 2);
+        if (lane == 0) mbar_arrive(&sh.empty[pos.st]);
         pos.next();
         ga0 = (ga0 + gstep) & 15u; ga1 = (ga1 + gstep) & 15u;
     }
 }
 
-template <int TYPE>
-__device__ __forceinline__ void consume_dispatch(const gs_params & p, const gs_seg & sg, int r0, int r1, gs_pos & pos, gs_shared & sh,
-                                                 uint8_t * ring, float * red, const uint8_t * aq, const float2 * ads, int warp, int lane) {
-    if (sg.spw == 1)      consume_segment<TYPE, 1>(p, sg, r0, r1, pos, sh, ring, red, aq, ads, warp, lane);
-    else if (sg.spw == 2) consume_segment<TYPE, 2>(p, sg, r0, r1, pos, sh, ring, red, aq, ads, warp, lane);
+template <int TYPE, bool COHERENT>
+__device__ __forceinline__ void consume_dispatch(const gs_ctx & c, const gs_phase & ph, const gs_seg & sg, int r0, int r1, gs_pos & pos, int warp, int lane) {
+    if (sg.spw == 1)      consume_segment<TYPE, 1, COHERENT>(c, ph, sg, r0, r1, pos, warp, lane);
+    else if (sg.spw == 2) consume_segment<TYPE, 2, COHERENT>(c, ph, sg, r0, r1, pos, warp, lane);
     else if (item<TYPE>::max_spw >= 4)
-        consume_segment<TYPE, (item<TYPE>::max_spw >= 4 ? 4 : 1)>(p, sg, r0, r1, pos, sh, ring, red, aq, ads, warp, lane);
+        consume_segment<TYPE, (item<TYPE>::max_spw >= 4 ? 4 : 1), COHERENT>(c, ph, sg, r0, r1, pos, warp, lane);
 }
 
-template <int T0, int T1>
-__global__ void __launch_bounds__(GS_THREADS, 2) gemv_stream_kernel(const __grid_constant__ gs_params p) {
-    extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t *  ring = smem;                                                    // GS_STAGES x stage_stride
-    float *    red  = (float *) (smem + p.n_stages * p.stage_stride);          // 2 x GS_RED_FLOATS
-    uint8_t *  aq   = (uint8_t *) (red + 2 * GS_RED_FLOATS);                   // activation int8, padded layout
-    float2 *   ads  = (float2 *) (aq + p.act_qs_bytes);                        // (d, d*sum) per unit
-    __shared__ gs_shared sh;
+// ---------------------------------------------------------------- phase pieces
+// prologue of a GEMV phase (consumers + finalizer): x -> [rms norm * w] -> q8_1 in shared memory.
+// COHERENT selects L2-coherent loads: inside a chain x was written by other SMs during this launch.
+template <bool COHERENT>
+__device__ __forceinline__ float4 gs_ld4(const float * p) {
+    return COHERENT ? __ldcg((const float4 *) p) : *(const float4 *) p;
+}
+template <bool COHERENT>
+__device__ __forceinline__ void gs_prologue(const gs_ctx & c, const gs_phase & ph, int warp, int lane) {
+    const int K = ph.K, nblk = K >> 5;
+    const float * __restrict__ x = ph.x;
+    const float * __restrict__ nw = ph.norm_w;
+    blk_q8_1 * xq_out = blockIdx.x == 0 ? ph.xq_out : nullptr;
+    const int pw = warp;                                        // prologue warps = the consumer warps
+    gs_shared & sh = *c.sh;
+    const int sub = lane & 7, bw = lane >> 3;                   // 8 lanes per 32-element block, 4 blocks per warp pass
+    constexpr int BPP = GS_NW * 4;                              // blocks per pass of the prologue warps
+    constexpr int NV = 8;                                       // passes whose x values stay in registers
 
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    if (tid == 0) {
-#pragma unroll
-        for (int s = 0; s < p.n_stages; ++s) { mbar_init(&sh.full[s], 1); mbar_init(&sh.empty[s], GS_NW); }
-        mbar_init(&sh.rfull[0], GS_NW); mbar_init(&sh.rfull[1], GS_NW);
-        mbar_init(&sh.rempty[0], 1);    mbar_init(&sh.rempty[1], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    }
-    __syncthreads();
-    pdl_launch_dependents();          // the next kernel in the stream may begin its own weight prefetch
-
-    // ---- this CTA's share of every work segment, split by bytes
-    const int64_t lo = p.total_bytes * (int64_t) blockIdx.x / gridDim.x;
-    const int64_t hi = p.total_bytes * (int64_t) (blockIdx.x + 1) / gridDim.x;
-    auto row_range = [&](const gs_seg & sg, int & r0, int & r1) {
-        const int64_t rbw = (int64_t) sg.rb * sg.nsub, tot = rbw * sg.M;
-        const int64_t a = min(max(lo - sg.byte_prefix, (int64_t) 0), tot), b = min(max(hi - sg.byte_prefix, (int64_t) 0), tot);
-        r0 = (int) ((a + rbw - 1) / rbw); r1 = (int) ((b + rbw - 1) / rbw);
-    };
-
-    if (warp == GS_NW) {
-        // ================= producer: TMA bulk copies into the ring
-        if (lane == 0) {
-            const uint64_t pol = policy_evict_first();
-            gs_pos pos; pos.ns = p.n_stages;
-            int dbg_n = 0;
-            for (int s = 0; s < p.n_ws; ++s) {
-                const gs_seg & sg = p.seg[s];
-                int r0, r1; row_range(sg, r0, r1);
-                for (int row = r0; row < r1; row += sg.R) {
-                    const int nr = min(sg.R, r1 - row);
-                    mbar_wait(&sh.empty[pos.st], pos.full_par ^ 1);
-                    GS_STAMP(0, dbg_n, 0);
-                    uint8_t * dstp = ring + pos.st * p.stage_stride;
-                    const uintptr_t g0 = (uintptr_t) (sg.w[0] + (int64_t) row * sg.rb);
-                    const uint32_t o0 = (uint32_t) (g0 & 15), b0 = (o0 + (uint32_t) nr * sg.rb + 15u) & ~15u;
-                    if (sg.nsub == 2) {
-                        const uintptr_t g1 = (uintptr_t) (sg.w[1] + (int64_t) row * sg.rb);
-                        const uint32_t o1 = (uint32_t) (g1 & 15), b1 = (o1 + (uint32_t) nr * sg.rb + 15u) & ~15u;
-                        mbar_expect_tx(&sh.full[pos.st], b0 + b1);
-                        bulk_g2s(dstp, (const void *) (g0 - o0), b0, &sh.full[pos.st], pol);
-                        bulk_g2s(dstp + b0, (const void *) (g1 - o1), b1, &sh.full[pos.st], pol);
-                    } else if (p.flags & 2) {     // experiment: the same bytes as 4 concurrent copies
-                        mbar_expect_tx(&sh.full[pos.st], b0);
-                        const uint32_t q4 = (b0 / 4 + 15u) & ~15u;
-                        for (uint32_t o = 0; o < b0; o += q4)
-                            bulk_g2s(dstp + o, (const void *) (g0 - o0 + o), min(q4, b0 - o), &sh.full[pos.st], pol);
-                    } else {
-                        mbar_expect_tx(&sh.full[pos.st], b0);
-                        bulk_g2s(dstp, (const void *) (g0 - o0), b0, &sh.full[pos.st], pol);
-                    }
-                    GS_STAMP(0, dbg_n, 1);
-                    ++dbg_n;
-                    pos.next();
-                }
+    auto quant_store = [&](int blk, bool act, float4 t, float4 w, float scale) {
+        float v[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        if (act) {
+            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+            if (nw) {                                           // same op order as rms_norm then mul: (x*scale)*w
+                v[0] = __fmul_rn(__fmul_rn(v[0], scale), w.x); v[1] = __fmul_rn(__fmul_rn(v[1], scale), w.y);
+                v[2] = __fmul_rn(__fmul_rn(v[2], scale), w.z); v[3] = __fmul_rn(__fmul_rn(v[3], scale), w.w);
             }
         }
-        return;
-    }
+        float d; int sum;
+        const int q = quantize_block32_quad<8>(v, d, sum);
+        if (act) {
+            *(int *) (c.aq + act_off(blk) + sub * 4) = q;
+            if (sub == 0) {
+                const float dh = __half2float(__float2half_rn(d));          // the value a q8_1 block stores
+                c.ads[blk] = make_float2(dh, dh * (float) sum);
+            }
+            if (xq_out) {
+                int * out = (int *) (xq_out + blk);
+                out[1 + sub] = q;
+                if (sub == 0) *(__half2 *) out = q8_1_scales(d, sum);
+            }
+        }
+    };
 
-    // ================= prologue (consumers + finalizer): x -> [rms norm * w] -> q8_1 in shared memory
-    pdl_wait();                       // x, bias and dst belong to earlier kernels in the stream
-    {
-        const int K = p.K, nblk = K >> 5;
-        const int pw = warp < GS_NW ? warp : GS_NW, ptid = pw * 32 + lane;      // prologue warp / thread index (producer excluded)
+    if (nblk <= BPP * NV) {
+        // ---- all loads first (one L2 round trip), values stay in registers for both passes
+        float4 xv[NV], wv[NV];
+#pragma unroll
+        for (int it = 0; it < NV; ++it) {
+            const int blk = pw * 4 + bw + it * BPP;
+            xv[it] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); wv[it] = xv[it];
+            if (blk < nblk) {
+                xv[it] = gs_ld4<COHERENT>(x + blk * 32 + sub * 4);
+                if (nw) wv[it] = *(const float4 *) (nw + blk * 32 + sub * 4);
+            }
+        }
         float scale = 1.0f;
-        if (p.norm_w) {
+        if (nw) {
+            float ss = 0.0f;
+#pragma unroll
+            for (int it = 0; it < NV; ++it) ss += xv[it].x * xv[it].x + xv[it].y * xv[it].y + xv[it].z * xv[it].z + xv[it].w * xv[it].w;
+            ss = warp_sum(ss);
+            if (lane == 0) sh.part[pw] = ss;
+            named_bar_sync(1, GS_PRO_THREADS);
+            float tot = 0.0f;
+#pragma unroll
+            for (int i = 0; i < GS_NW; ++i) tot += sh.part[i];
+            scale = rsqrtf(tot / (float) K + ph.eps);
+        }
+#pragma unroll
+        for (int it = 0; it < NV; ++it) {
+            const int b0 = pw * 4 + it * BPP;                   // warp-uniform
+            if (b0 < nblk) quant_store(b0 + bw, b0 + bw < nblk, xv[it], wv[it], scale);
+        }
+    } else {
+        // ---- long rows: two passes over x
+        const int ptid = pw * 32 + lane;
+        float scale = 1.0f;
+        if (nw) {
             float ss = 0.0f;
             for (int i = ptid * 4; i < K; i += GS_PRO_THREADS * 4) {
-                const float4 v = *(const float4 *) (p.x + i);
+                const float4 v = gs_ld4<COHERENT>(x + i);
                 ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
             }
             ss = warp_sum(ss);
@@ -490,123 +547,272 @@ __global__ void __launch_bounds__(GS_THREADS, 2) gemv_stream_kernel(const __grid
             named_bar_sync(1, GS_PRO_THREADS);
             float tot = 0.0f;
 #pragma unroll
-            for (int i = 0; i <= GS_NW; ++i) tot += sh.part[i];
-            scale = rsqrtf(tot / (float) K + p.eps);
+            for (int i = 0; i < GS_NW; ++i) tot += sh.part[i];
+            scale = rsqrtf(tot / (float) K + ph.eps);
         }
-        const int sub = lane & 7, bw = lane >> 3;                 // 8 lanes per 32-element block, 4 blocks per warp pass
-        for (int b0 = pw * 4; b0 < nblk; b0 += (GS_NW + 1) * 4) {
+        for (int b0 = pw * 4; b0 < nblk; b0 += BPP) {
             const int blk = b0 + bw;
             const bool act = blk < nblk;
-            float v[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-            if (act) {
-                const float4 t = *(const float4 *) (p.x + blk * 32 + sub * 4);
-                v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-                if (p.norm_w) {                                    // same op order as rms_norm then mul: (x*scale)*w
-                    const float4 w = *(const float4 *) (p.norm_w + blk * 32 + sub * 4);
-                    v[0] = __fmul_rn(__fmul_rn(v[0], scale), w.x); v[1] = __fmul_rn(__fmul_rn(v[1], scale), w.y);
-                    v[2] = __fmul_rn(__fmul_rn(v[2], scale), w.z); v[3] = __fmul_rn(__fmul_rn(v[3], scale), w.w);
-                }
+            float4 t = make_float4(0.0f, 0.0f, 0.0f, 0.0f), w = t;
+            if (act) { t = gs_ld4<COHERENT>(x + blk * 32 + sub * 4); if (nw) w = *(const float4 *) (nw + blk * 32 + sub * 4); }
+            quant_store(blk, act, t, w, scale);
+        }
+    }
+    named_bar_sync(1, GS_PRO_THREADS);
+}
+
+// ---------------------------------------------------------------- attention phase (decode, one query position)
+// Item = one query head.  Replaces, for n_q = 1 and an f16 cache, the reference's ROPE(q), ROPE(k) (+SET_ROWS k, v) and
+// FLASH_ATTN_EXT nodes (rope.cu:563, set-rows.cu:318, fattn-vec.cuh:19-507).  The current token's K/V rows are taken
+// from the raw projections (RoPE applied, rounded to f16 exactly as the cache stores them) and written to the cache by
+// the first query head of each KV group; all other positions are read from the cache.
+template <int D>
+__device__ __forceinline__ void gs_attn_item(const gs_attn & a, int h, float * sm, int warp, int lane) {
+    constexpr int LPP = D / 32, PPB = 32 / LPP, DPL = D / 32;     // lanes per position, positions per batch, dims per lane (V)
+    const int tid = warp * 32 + lane;
+    const int gqa = a.H / a.H_kv, g = h / gqa;
+    const int pos = __ldcg(a.pos), slot = (int) __ldcg(a.slot);
+    float * s_q = sm, * s_k = sm + D, * s_v = sm + 2 * D, * s_part = sm + 3 * D;      // s_part: [GS_NW][D + 2]
+    // ---- 1. RoPE(q[h]) * scale, RoPE(k_new[g]) and v_new[g] rounded to f16
+    {
+        const int half_d = a.n_dims / 2;
+        if (tid < D) {                                            // threads 0..D/2-1: q pairs, D/2..D-1: k pairs
+            const bool isk = tid >= D / 2;
+            const int i = isk ? tid - D / 2 : tid;
+            const float * src = isk ? a.k_new + (int64_t) g * D : a.q + (int64_t) h * D;
+            float * dst = isk ? s_k : s_q;
+            if (i < half_d) {
+                const int i0 = a.rope_mode == 2 ? i : 2 * i, i1 = a.rope_mode == 2 ? i + half_d : 2 * i + 1;
+                const float theta = (float) pos * powf(a.theta_scale, (float) i) * a.freq_scale;
+                float sn, cs; sincosf(theta, &sn, &cs);
+                const float x0 = __ldcg(src + i0), x1 = __ldcg(src + i1);
+                float y0 = x0 * cs - x1 * sn, y1 = x0 * sn + x1 * cs;
+                if (isk) { y0 = __half2float(__float2half_rn(y0)); y1 = __half2float(__float2half_rn(y1)); }
+                else     { y0 *= a.scale; y1 *= a.scale; }
+                dst[i0] = y0; dst[i1] = y1;
             }
-            float d; int sum;
-            const int q = quantize_block32_quad<8>(v, d, sum);
-            if (act) {
-                *(int *) (aq + act_off(blk) + sub * 4) = q;
-                if (sub == 0) {
-                    const float dh = __half2float(__float2half_rn(d));          // the value a q8_1 block stores
-                    ads[blk] = make_float2(dh, dh * (float) sum);
-                }
-                if (p.xq_out && blockIdx.x == 0) {
-                    int * out = (int *) (p.xq_out + blk);
-                    out[1 + sub] = q;
-                    if (sub == 0) *(__half2 *) out = q8_1_scales(d, sum);
+            for (int d = a.n_dims + i; d < D; d += D / 2) {       // dims beyond n_dims pass through
+                const float y = __ldcg(src + d);
+                dst[d] = isk ? __half2float(__float2half_rn(y)) : y * a.scale;
+            }
+        } else if (tid < 2 * D) {
+            const int d = tid - D;
+            s_v[d] = __half2float(__float2half_rn(__ldcg(a.v_new + (int64_t) g * D + d)));
+        }
+    }
+    named_bar_sync(3, GS_CON_THREADS);
+    if (h % gqa == 0 && tid < 2 * D) {                            // KV-cache write of the current token (one writer per group)
+        const int d = tid < D ? tid : tid - D;
+        char * row = tid < D ? a.k_cache + (int64_t) slot * a.k_nb1 + (int64_t) g * a.k_nb2
+                             : a.v_cache + (int64_t) slot * a.v_nb1 + (int64_t) g * a.v_nb2;
+        ((__half *) row)[d] = __float2half_rn(tid < D ? s_k[d] : s_v[d]);
+    }
+    // ---- 2. scores + online softmax + V accumulation, KV positions strided over the warps
+    float qreg[32];
+    const int qsub = lane % LPP;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) qreg[i] = s_q[qsub * 32 + i];
+    float m = -INFINITY, l = 0.0f, acc[DPL];
+#pragma unroll
+    for (int i = 0; i < DPL; ++i) acc[i] = 0.0f;
+    const char * kb = a.k_cache + (int64_t) g * a.k_nb2;
+    const char * vb = a.v_cache + (int64_t) g * a.v_nb2;
+    for (int base = warp * PPB; base < a.n_kv; base += GS_NW * PPB) {
+        const int p = base + lane / LPP;
+        const float mk = p < a.n_kv ? (a.mask ? __half2float(a.mask[p]) : 0.0f) : -INFINITY;
+        float s = 0.0f;
+        if (mk != -INFINITY) {
+            if (p == slot) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) s += qreg[i] * s_k[qsub * 32 + i];
+            } else {
+                const uint4 * kr = (const uint4 *) (kb + (int64_t) p * a.k_nb1 + qsub * 64);
+#pragma unroll
+                for (int c4 = 0; c4 < 4; ++c4) {
+                    const uint4 t = kr[c4];
+                    const __half2 * hp = (const __half2 *) &t;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) { const float2 f = __half22float2(hp[i]); s += qreg[c4 * 8 + 2 * i] * f.x + qreg[c4 * 8 + 2 * i + 1] * f.y; }
                 }
             }
         }
-        named_bar_sync(1, GS_PRO_THREADS);
+#pragma unroll
+        for (int o = 1; o < LPP; o <<= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        s = mk == -INFINITY ? -INFINITY : s + mk;
+        float bm = s;
+#pragma unroll
+        for (int o = LPP; o < 32; o <<= 1) bm = fmaxf(bm, __shfl_xor_sync(0xffffffffu, bm, o));
+        const float mn = fmaxf(m, bm);
+        if (mn == -INFINITY) continue;                            // whole batch masked (warp-uniform)
+        const float corr = __expf(m - mn);
+        const float pr = s == -INFINITY ? 0.0f : __expf(s - mn);
+        float psum = pr;
+#pragma unroll
+        for (int o = LPP; o < 32; o <<= 1) psum += __shfl_xor_sync(0xffffffffu, psum, o);
+        l = l * corr + psum; m = mn;
+#pragma unroll
+        for (int i = 0; i < DPL; ++i) acc[i] *= corr;
+#pragma unroll
+        for (int j = 0; j < PPB; ++j) {
+            const float pj = __shfl_sync(0xffffffffu, pr, j * LPP);
+            const int pp = base + j;
+            if (pj != 0.0f) {                                     // warp-uniform
+                if (pp == slot) {
+#pragma unroll
+                    for (int i = 0; i < DPL; ++i) acc[i] += pj * s_v[lane * DPL + i];
+                } else {
+                    const __half * vr = (const __half *) (vb + (int64_t) pp * a.v_nb1) + lane * DPL;
+                    if (DPL == 4) { const uint2 t = *(const uint2 *) vr; const __half2 * hp = (const __half2 *) &t;
+                                    const float2 f0 = __half22float2(hp[0]), f1 = __half22float2(hp[1]);
+                                    acc[0] += pj * f0.x; acc[1] += pj * f0.y; acc[2] += pj * f1.x; acc[3] += pj * f1.y; }
+                    else          { const float2 f0 = __half22float2(*(const __half2 *) vr); acc[0] += pj * f0.x; acc[1] += pj * f0.y; }
+                }
+            }
+        }
     }
+    // ---- 3. combine the warps' states
+    float * mine = s_part + warp * (D + 2);
+#pragma unroll
+    for (int i = 0; i < DPL; ++i) mine[lane * DPL + i] = acc[i];
+    if (lane == 0) { mine[D] = m; mine[D + 1] = l; }
+    named_bar_sync(3, GS_CON_THREADS);
+    if (tid < D) {
+        float M = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < GS_NW; ++w) M = fmaxf(M, s_part[w * (D + 2) + D]);
+        float A = 0.0f, L = 0.0f;
+#pragma unroll
+        for (int w = 0; w < GS_NW; ++w) {
+            const float mw = s_part[w * (D + 2) + D];
+            const float wgt = mw == -INFINITY ? 0.0f : __expf(mw - M);
+            A += wgt * s_part[w * (D + 2) + tid]; L += wgt * s_part[w * (D + 2) + D + 1];
+        }
+        a.dst[(int64_t) h * D + tid] = A / L;
+    }
+    named_bar_sync(3, GS_CON_THREADS);                            // scratch is reused by the next item
+}
 
-    if (warp < GS_NW) {
-        // ================= consumers
-        gs_pos pos; pos.ns = p.n_stages;
-        for (int s = 0; s < p.n_ws; ++s) {
-            const gs_seg & sg = p.seg[s];
-            int r0, r1; row_range(sg, r0, r1);
-            if (r0 >= r1) continue;
-            if (sg.type == T0) consume_dispatch<T0>(p, sg, r0, r1, pos, sh, ring, red, aq, ads, warp, lane);
-            else               consume_dispatch<T1>(p, sg, r0, r1, pos, sh, ring, red, aq, ads, warp, lane);
+__device__ __forceinline__ unsigned long long gs_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define GS_STAMP(ip, k) do { if (p.dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) \
+    p.dbg[((ip) * 2 + (blockIdx.x ? 1 : 0)) * 8 + (k)] = gs_now(); } while (0)
+#define GS_STAMP_MAX(ip, k) do { if (p.dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) \
+    atomicMax(p.dbg + ((ip) * 2 + (blockIdx.x ? 1 : 0)) * 8 + (k), gs_now()); } while (0)
+
+__device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int * p) {
+    unsigned int v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// ---------------------------------------------------------------- the kernel
+template <int T0, int T1, bool CHAIN>
+__global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid_constant__ gs_params p) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ gs_shared sh;
+    // phase descriptors are staged in shared memory: read from global inside the chunk loops they cost an L2 round
+    // trip per field per chunk (measured: 1.3 us per chunk in the finalizer)
+    __shared__ gs_phase s_ph[2];       // consumers + finalizer (double-buffered: the finalizer may trail by a phase)
+    __shared__ gs_phase s_pp;          // producer (runs ahead)
+    gs_ctx c;
+    c.ring = smem;                                                            // n_stages x stage_stride
+    c.aq   = smem + p.n_stages * p.stage_stride;                              // activation int8, padded layout
+    c.ads  = (float2 *) (c.aq + p.act_qs_bytes);                              // (d, d*sum) per unit; sized with act_qs_bytes/4
+    c.attn = (float *) ((uint8_t *) c.ads + (p.act_qs_bytes >> 2) + 64);      // attention scratch
+    c.sh = &sh; c.stage_stride = p.stage_stride; c.flags = p.flags;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid == 0) {
+        for (int s = 0; s < p.n_stages; ++s) { mbar_init(&sh.full[s], 1); mbar_init(&sh.empty[s], GS_NW); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+    if (!CHAIN) pdl_launch_dependents();      // the next kernel in the stream may begin its own weight prefetch
+
+    const gs_phase * phases = CHAIN ? p.phases : &p.inl;
+    const int n_phases = CHAIN ? p.n_phases : 1;
+    gs_pos pos; pos.ns = p.n_stages;
+    constexpr int PH_VEC = (int) (sizeof(gs_phase) / 16);
+    static_assert(sizeof(gs_phase) % 16 == 0, "gs_phase is copied as uint4");
+
+    if (warp == GS_NW) {
+        // ================= producer: TMA bulk copies into the ring, straight through all phases
+        const uint64_t pol = policy_evict_first();
+        for (int ip = 0; ip < n_phases; ++ip) {
+            __syncwarp();
+            for (int i = lane; i < PH_VEC; i += 32) ((uint4 *) &s_pp)[i] = ((const uint4 *) (phases + ip))[i];
+            __syncwarp();
+            if (lane == 0) {
+                const gs_phase & ph = s_pp;
+                if (ph.kind != 0) continue;
+                const int64_t lo = ph.total_bytes * (int64_t) blockIdx.x / gridDim.x, hi = ph.total_bytes * (int64_t) (blockIdx.x + 1) / gridDim.x;
+                for (int s = 0; s < ph.n_ws; ++s) {
+                    const gs_seg & sg = ph.seg[s];
+                    int r0, r1; gs_row_range(sg, lo, hi, r0, r1);
+                    for (int row = r0; row < r1; row += sg.R) {
+                        const int nr = min(sg.R, r1 - row);
+                        mbar_wait(&sh.empty[pos.st], pos.full_par ^ 1);
+                        uint8_t * dstp = c.ring + pos.st * p.stage_stride;
+                        const uintptr_t g0 = (uintptr_t) (sg.w[0] + (int64_t) row * sg.rb);
+                        const uint32_t o0 = (uint32_t) (g0 & 15), b0 = (o0 + (uint32_t) nr * sg.rb + 15u) & ~15u;
+                        if (sg.nsub == 2) {
+                            const uintptr_t g1 = (uintptr_t) (sg.w[1] + (int64_t) row * sg.rb);
+                            const uint32_t o1 = (uint32_t) (g1 & 15), b1 = (o1 + (uint32_t) nr * sg.rb + 15u) & ~15u;
+                            mbar_expect_tx(&sh.full[pos.st], b0 + b1);
+                            bulk_g2s(dstp, (const void *) (g0 - o0), b0, &sh.full[pos.st], pol);
+                            bulk_g2s(dstp + b0, (const void *) (g1 - o1), b1, &sh.full[pos.st], pol);
+                        } else {
+                            mbar_expect_tx(&sh.full[pos.st], b0);
+                            bulk_g2s(dstp, (const void *) (g0 - o0), b0, &sh.full[pos.st], pol);
+                        }
+                        pos.next();
+                    }
+                }
+            }
         }
         return;
     }
 
-    // ================= finalizer: reduce partials, epilogue, store (4 lanes per row, 8 rows per pass)
-    {
-        gs_pos pos; pos.ns = p.n_stages;
-        const int part = lane & 3, rsel = lane >> 2;
-        for (int s = 0; s < p.n_ws; ++s) {
-            const gs_seg & sg = p.seg[s];
-            int r0, r1; row_range(sg, r0, r1);
-            const int nvals = sg.KS * 32, rstride = nvals + 4, per = nvals >> 2;      // floats per lane: KS*8
-            for (int row = r0; row < r1; row += sg.R) {
-                const int nr = min(sg.R, r1 - row);
-                float bias0 = 0.0f;                                   // prefetch the epilogue operand of the first pass
-                if (sg.bias && rsel < nr && part == 0) bias0 = sg.bias[row + rsel];
-                mbar_wait(&sh.rfull[pos.rp], pos.red_par);
-                if (lane == 0) GS_STAMP(2, pos.dbg, 0);
-                const float * r = red + pos.rp * GS_RED_FLOATS;
-                // The buffer is released as soon as its values sit in registers, and by a lane that never stores to
-                // global memory: mbarrier.arrive is a release, and a release issued by a storing thread waits for that
-                // thread's outstanding global stores (~1 us per chunk when it sat behind the dst store).
-                if (nr <= 8) {
-                    const int j = rsel;
-                    float v0 = 0.0f, v1 = 0.0f;
-                    if (j < nr) {
-                        const float4 * src = (const float4 *) (r + j * rstride + part * per);
-                        for (int i = 0; i < per / 4; ++i) { const float4 t = src[i]; v0 += (t.x + t.y) + (t.z + t.w); }
-                        if (sg.nsub == 2) {
-                            src = (const float4 *) (r + (nr + j) * rstride + part * per);
-                            for (int i = 0; i < per / 4; ++i) { const float4 t = src[i]; v1 += (t.x + t.y) + (t.z + t.w); }
-                        }
-                    }
-                    v0 += __shfl_xor_sync(0xffffffffu, v0, 1); v1 += __shfl_xor_sync(0xffffffffu, v1, 1);
-                    v0 += __shfl_xor_sync(0xffffffffu, v0, 2); v1 += __shfl_xor_sync(0xffffffffu, v1, 2);
-                    if (lane == 1) mbar_arrive(&sh.rempty[pos.rp]);
-                    if (j < nr && part == 0) {
-                        float out = sg.nsub == 2 ? gs_glu(p.glu_op, v0, v1, p.glu_alpha, p.glu_limit) : v0;
-                        if (sg.bias) out += bias0;
-                        sg.dst[row + j] = out;
-                    }
-                } else {
-                    float keep0[4], keep1[4];                       // up to 32 rows: 4 passes held in registers
-#pragma unroll
-                    for (int ps = 0; ps < 4; ++ps) {
-                        const int j = ps * 8 + rsel;
-                        float v0 = 0.0f, v1 = 0.0f;
-                        if (j < nr) {
-                            const float4 * src = (const float4 *) (r + j * rstride + part * per);
-                            for (int i = 0; i < per / 4; ++i) { const float4 t = src[i]; v0 += (t.x + t.y) + (t.z + t.w); }
-                            if (sg.nsub == 2) {
-                                src = (const float4 *) (r + (nr + j) * rstride + part * per);
-                                for (int i = 0; i < per / 4; ++i) { const float4 t = src[i]; v1 += (t.x + t.y) + (t.z + t.w); }
-                            }
-                        }
-                        v0 += __shfl_xor_sync(0xffffffffu, v0, 1); v1 += __shfl_xor_sync(0xffffffffu, v1, 1);
-                        v0 += __shfl_xor_sync(0xffffffffu, v0, 2); v1 += __shfl_xor_sync(0xffffffffu, v1, 2);
-                        keep0[ps] = v0; keep1[ps] = v1;
-                    }
-                    if (lane == 1) mbar_arrive(&sh.rempty[pos.rp]);
-#pragma unroll
-                    for (int ps = 0; ps < 4; ++ps) {
-                        const int j = ps * 8 + rsel;
-                        if (j < nr && part == 0) {
-                            float out = sg.nsub == 2 ? gs_glu(p.glu_op, keep0[ps], keep1[ps], p.glu_alpha, p.glu_limit) : keep0[ps];
-                            if (sg.bias) out += ps == 0 ? bias0 : sg.bias[row + j];
-                            sg.dst[row + j] = out;
-                        }
-                    }
-                }
-                if (lane == 0) GS_STAMP(2, pos.dbg, 1);
-                pos.next();
+    // ================= consumers (warps 0..GS_NW-1)
+    for (int ip = 0; ip < n_phases; ++ip) {
+        const gs_phase & ph = s_ph[ip & 1];
+        // static data: staged (and the norm weights requested into L2) before the dependency wait
+        for (int i = tid; i < PH_VEC; i += GS_CON_THREADS) ((uint4 *) &s_ph[ip & 1])[i] = ((const uint4 *) (phases + ip))[i];
+        // ---- dependency: everything this phase reads was produced by the previous phase (or earlier kernels)
+        if (ip == 0) {
+            pdl_wait();
+        } else if (tid == 0) {
+            while (ld_acquire_gpu(p.bar + ip - 1) < gridDim.x) { }
+        }
+        named_bar_sync(1, GS_CON_THREADS);
+        if (CHAIN && tid == 0) GS_STAMP(ip, 0);
+        if (ph.kind == 0) {
+            gs_prologue<CHAIN>(c, ph, warp, lane);
+            if (CHAIN && tid == 0) GS_STAMP(ip, 1);
+            const int64_t lo = ph.total_bytes * (int64_t) blockIdx.x / gridDim.x, hi = ph.total_bytes * (int64_t) (blockIdx.x + 1) / gridDim.x;
+            for (int s = 0; s < ph.n_ws; ++s) {
+                const gs_seg & sg = ph.seg[s];
+                int r0, r1; gs_row_range(sg, lo, hi, r0, r1);
+                if (r0 >= r1) continue;
+                if (sg.type == T0) consume_dispatch<T0, CHAIN>(c, ph, sg, r0, r1, pos, warp, lane);
+                else               consume_dispatch<T1, CHAIN>(c, ph, sg, r0, r1, pos, warp, lane);
             }
+        } else if (CHAIN) {
+            for (int h = blockIdx.x; h < ph.attn.H; h += gridDim.x) {
+                if (ph.attn.D == 128) gs_attn_item<128>(ph.attn, h, c.attn, warp, lane);
+                else                  gs_attn_item<64>(ph.attn, h, c.attn, warp, lane);
+            }
+        }
+        if (CHAIN) {
+            if (tid == 0) GS_STAMP(ip, 2);
+            // ---- publish: this CTA's stores of the phase are visible device-wide, then count it in
+            __threadfence();
+            named_bar_sync(1, GS_CON_THREADS);
+            if (tid == 0) { GS_STAMP(ip, 4); atomicAdd(p.bar + ip, 1u); GS_STAMP(ip, 3); }
         }
     }
 }
@@ -615,7 +821,8 @@ __global__ void __launch_bounds__(GS_THREADS, 2) gemv_stream_kernel(const __grid
 static bool gs_type_ok(int t) { return t == B200_Q4_0 || t == B200_Q8_0 || t == B200_MXFP4 || t == B200_Q4_K || t == B200_Q6_K; }
 static int  gs_wpi(int t) { return (t == B200_Q4_K || t == B200_Q6_K) ? 64 : 32; }
 
-static bool gs_build(const b200_gemv_fused_args * a, gs_params & p) {
+// validate one GEMV phase and fill everything that does not depend on the ring configuration
+static bool gs_build_phase(const b200_gemv_fused_args * a, gs_phase & ph, int64_t & need, int & act_qs, int types[2]) {
     if (!a || a->n_seg < 1 || a->n_seg > B200_GEMV_MAX_SEG) return false;
     const b200_tensor & x = a->x;
     const int64_t K = x.ne[0];
@@ -625,7 +832,6 @@ static bool gs_build(const b200_gemv_fused_args * a, gs_params & p) {
                       nelements(*a->norm_w) != K || ((uintptr_t) a->norm_w->data) % 16 != 0)) return false;
     const bool glu = a->glu_op != B200_GLU_NONE;
     if (glu && (a->n_seg != 2 || a->glu_op < B200_GLU_REGLU || a->glu_op > B200_GLU_GEGLU_QUICK)) return false;
-    int types[2] = {-1, -1};
     for (int s = 0; s < a->n_seg; ++s) {
         const b200_gemv_seg & g = a->seg[s];
         const b200_tensor & w = g.w;
@@ -641,38 +847,22 @@ static bool gs_build(const b200_gemv_fused_args * a, gs_params & p) {
         if (types[0] < 0 || types[0] == w.type) types[0] = w.type;
         else if (types[1] < 0 || types[1] == w.type) types[1] = w.type;
         else return false;
+        need = std::max<int64_t>(need, w.nb[1] * (glu ? 2 : 1) + 64);
     }
     if (glu) {
         const b200_tensor & g = a->seg[0].w; const b200_tensor & u = a->seg[1].w;
         if (g.type != u.type || g.ne[1] != u.ne[1] || a->seg[0].bias) return false;
     }
-    // shared-memory budget: ring + reduction buffers + activation
-    const int act_qs = (int) ((K + (K / 128 + 1) * 16 + 15) & ~15);
-    const int act_ds = (int) (K / 32 * 8);
-    int64_t need = 0;                                   // smallest stage payload that holds one row (pair)
-    for (int s = 0; s < a->n_seg; ++s) need = std::max<int64_t>(need, a->seg[s].w.nb[1] * (glu ? 2 : 1) + 64);
-    const int fixed = 2 * GS_RED_FLOATS * 4 + act_qs + act_ds + 16;
-    const int flags = a->flags;
-    const int n_stages = ((flags >> 4) & 0xF) ? std::min((flags >> 4) & 0xF, GS_MAX_STAGES) : GS_STAGES;
-    const int64_t want = ((flags >> 8) & 0xFF) ? (int64_t) ((flags >> 8) & 0xFF) * 1024 : GS_STAGE_BYTES;
-    int64_t payload = std::max<int64_t>(want, need);
-    auto total_for = [&](int64_t pl) { return (int64_t) n_stages * (((pl + 127) & ~127) + GS_STAGE_SLACK) + fixed; };
-    if (!((flags >> 8) & 0xFF) && total_for(payload) > GS_SMEM_2CTA && need < payload) {          // shrink the stages if that keeps two CTAs per SM
-        const int64_t fit = (GS_SMEM_2CTA - fixed) / n_stages - GS_STAGE_SLACK - 128;
-        if (fit >= need && fit >= 12 * 1024) payload = fit & ~127;
-    }
-    if (total_for(payload) > GS_SMEM_MAX) return false;
-    const int stage_payload = (int) ((payload + 127) & ~127);
+    act_qs = std::max(act_qs, (int) ((K + (K / 128 + 1) * 16 + 15) & ~15));
 
-    memset(&p, 0, sizeof(p));
-    p.K = (int32_t) K; p.x = (const float *) x.data; p.norm_w = a->norm_w ? (const float *) a->norm_w->data : nullptr; p.eps = a->eps;
-    p.glu_op = a->glu_op; p.glu_alpha = a->glu_alpha; p.glu_limit = a->glu_limit;
-    p.xq_out = (blk_q8_1 *) a->xq_out; p.act_qs_bytes = act_qs; p.stage_stride = stage_payload + GS_STAGE_SLACK;
-    p.n_stages = n_stages; p.flags = flags;
-    int64_t prefix = 0;
-    p.n_ws = glu ? 1 : a->n_seg;
-    for (int s = 0; s < p.n_ws; ++s) {
-        gs_seg & g = p.seg[s];
+    memset(&ph, 0, sizeof(ph));
+    ph.kind = 0;
+    ph.K = (int32_t) K; ph.x = (const float *) x.data; ph.norm_w = a->norm_w ? (const float *) a->norm_w->data : nullptr; ph.eps = a->eps;
+    ph.glu_op = a->glu_op; ph.glu_alpha = a->glu_alpha; ph.glu_limit = a->glu_limit;
+    ph.xq_out = (blk_q8_1 *) a->xq_out;
+    ph.n_ws = glu ? 1 : a->n_seg;
+    for (int s = 0; s < ph.n_ws; ++s) {
+        gs_seg & g = ph.seg[s];
         const b200_gemv_seg & src = glu ? a->seg[1] : a->seg[s];
         g.nsub = glu ? 2 : 1;
         g.w[0] = (const uint8_t *) (glu ? a->seg[0].w.data : src.w.data);
@@ -682,52 +872,92 @@ static bool gs_build(const b200_gemv_fused_args * a, gs_params & p) {
         g.M = (int32_t) src.w.ne[1]; g.rb = (int32_t) src.w.nb[1]; g.type = src.w.type;
         g.ipr = (int32_t) (K / gs_wpi(g.type)); g.spr = (g.ipr + 31) / 32;
         int KS = 1; while (KS * 2 <= GS_NW && KS * 2 <= g.spr) KS *= 2;
-        g.KS = KS;
         int spw = (g.spr + KS - 1) / KS;
         if (spw == 3) spw = 4;
         if (spw > (gs_wpi(g.type) == 64 ? 2 : 4)) return false;        // row too long for the register-resident activation
-        g.spw = spw;
-        const int RG = GS_NW / KS;
-        // rows per chunk: fit the stage (both sub-blocks + alignment slack), the reduction buffer, one pass granularity
+        g.KS = KS; g.spw = spw;
+    }
+    return true;
+}
+
+// rows per chunk once the stage payload is known
+static bool gs_finish_phase(gs_phase & ph, int stage_payload) {
+    int64_t prefix = 0;
+    for (int s = 0; s < ph.n_ws; ++s) {
+        gs_seg & g = ph.seg[s];
+        const int RG = GS_NW / g.KS;
         int R = (stage_payload - 64) / (g.rb * g.nsub);
-        const int red_rows = GS_RED_FLOATS / (KS * 32 + 4) / g.nsub;
-        if (R > red_rows) R = red_rows;
-        if (R > 32) R = 32;
-        if (R < 1) return false;                       // a single row does not fit a stage
-        const int pass = RG * GS_RB / g.nsub > 0 ? RG * GS_RB / g.nsub : 1;
+        if (R > 64) R = 64;
+        if (R < 1) return false;
+        const int pass = g.nsub == 2 ? RG : RG * GS_RB;  // output rows per CTA pass
         if (R > pass) R -= R % pass;
         g.R = R;
         g.byte_prefix = prefix;
         prefix += (int64_t) g.rb * g.nsub * g.M;
     }
-    p.total_bytes = prefix;
+    ph.total_bytes = prefix;
     return true;
 }
 
-static size_t gs_smem(const gs_params & p) {
-    return (size_t) p.n_stages * p.stage_stride + 2 * GS_RED_FLOATS * 4 + p.act_qs_bytes + (size_t) p.K / 32 * 8 + 16;
+struct gs_config { int n_stages, stage_payload, act_qs, attn_floats; size_t smem; };
+
+static bool gs_make_config(int flags, int64_t need, int act_qs, int attn_floats, gs_config & cfg) {
+    cfg.n_stages = ((flags >> 4) & 0xF) ? std::min((flags >> 4) & 0xF, GS_MAX_STAGES) : GS_STAGES;
+    const int64_t want = ((flags >> 8) & 0xFF) ? (int64_t) ((flags >> 8) & 0xFF) * 1024 : GS_STAGE_BYTES;
+    const int64_t fixed = act_qs + act_qs / 4 + 64 + (int64_t) attn_floats * 4 + 64;
+    int64_t payload = std::max<int64_t>(want, need);
+    auto total_for = [&](int64_t pl) { return (int64_t) cfg.n_stages * (((pl + 127) & ~127) + GS_STAGE_SLACK) + fixed; };
+    if (total_for(payload) > GS_SMEM_MAX) {            // shrink the stages (never below one row) to fit
+        const int64_t fit = ((GS_SMEM_MAX - fixed) / cfg.n_stages - GS_STAGE_SLACK) & ~127;
+        if (fit < need) return false;
+        payload = fit;
+    }
+    cfg.stage_payload = (int) ((payload + 127) & ~127);
+    cfg.act_qs = act_qs; cfg.attn_floats = attn_floats;
+    cfg.smem = (size_t) total_for(cfg.stage_payload);
+    return true;
 }
 
-template <int T0, int T1>
-static int gs_launch(const gs_params & p, int grid, cudaStream_t st) {
+template <int T0, int T1, bool CHAIN>
+static int gs_launch(const gs_params & p, size_t smem, int grid, cudaStream_t st) {
     static bool attr_set[64] = {};
-    const size_t smem = gs_smem(p);
     int dev = 0;
     B200_CUDA_TRY(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64) return B200_ERR_ARG;
     if (!attr_set[dev]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(gemv_stream_kernel<T0, T1>, cudaFuncAttributeMaxDynamicSharedMemorySize, GS_SMEM_MAX));
+        B200_CUDA_TRY(cudaFuncSetAttribute(gemv_stream_kernel<T0, T1, CHAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, GS_SMEM_MAX));
         attr_set[dev] = true;
     }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned) grid); cfg.blockDim = dim3(GS_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
     cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = 1;
+    if (CHAIN) { at[0].id = cudaLaunchAttributeCooperative; at[0].val.cooperative = 1; }     // all CTAs co-resident: the grid barriers need it
+    else       { at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[0].val.programmaticStreamSerializationAllowed = 1; }
     cfg.attrs = at; cfg.numAttrs = 1;
-    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, gemv_stream_kernel<T0, T1>, p));
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, gemv_stream_kernel<T0, T1, CHAIN>, p));
     count_launch();
     return B200_OK;
+}
+
+template <bool CHAIN>
+static int gs_launch_types(const gs_params & p, size_t smem, int grid, cudaStream_t st, int t0, int t1) {
+    if (t1 < 0) t1 = t0;
+    if (t0 == t1) {
+        switch (t0) {
+            case B200_Q4_K:  return gs_launch<B200_Q4_K, B200_Q4_K, CHAIN>(p, smem, grid, st);
+            case B200_Q6_K:  return gs_launch<B200_Q6_K, B200_Q6_K, CHAIN>(p, smem, grid, st);
+            case B200_Q4_0:  return gs_launch<B200_Q4_0, B200_Q4_0, CHAIN>(p, smem, grid, st);
+            case B200_Q8_0:  return gs_launch<B200_Q8_0, B200_Q8_0, CHAIN>(p, smem, grid, st);
+            case B200_MXFP4: return gs_launch<B200_MXFP4, B200_MXFP4, CHAIN>(p, smem, grid, st);
+        }
+    }
+    const int lo = t0 < t1 ? t0 : t1, hi = t0 < t1 ? t1 : t0;
+    if (lo == B200_Q4_K && hi == B200_Q6_K)  return gs_launch<B200_Q4_K, B200_Q6_K, CHAIN>(p, smem, grid, st);
+    if (lo == B200_Q4_0 && hi == B200_Q6_K)  return gs_launch<B200_Q4_0, B200_Q6_K, CHAIN>(p, smem, grid, st);
+    if (lo == B200_Q4_0 && hi == B200_Q8_0)  return gs_launch<B200_Q4_0, B200_Q8_0, CHAIN>(p, smem, grid, st);
+    if (lo == B200_Q8_0 && hi == B200_MXFP4) return gs_launch<B200_Q8_0, B200_MXFP4, CHAIN>(p, smem, grid, st);
+    set_error("b200 streaming GEMV: unsupported type pair (%d, %d)", t0, t1);
+    return B200_ERR_UNSUPPORTED;
 }
 
 static int gs_sm_count() {
@@ -738,40 +968,134 @@ static int gs_sm_count() {
     return n[dev];
 }
 
+static bool gs_build_single(const b200_gemv_fused_args * a, gs_params & p, size_t & smem, int types[2]) {
+    int64_t need = 0; int act_qs = 0;
+    types[0] = types[1] = -1;
+    memset(&p, 0, sizeof(p));
+    if (!gs_build_phase(a, p.inl, need, act_qs, types)) return false;
+    gs_config cfg;
+    if (!gs_make_config(a->flags, need, act_qs, 0, cfg)) return false;
+    if (!gs_finish_phase(p.inl, cfg.stage_payload)) return false;
+    p.n_phases = 1; p.act_qs_bytes = cfg.act_qs; p.stage_stride = cfg.stage_payload + GS_STAGE_SLACK;
+    p.n_stages = cfg.n_stages; p.flags = a->flags; p.attn_floats = 0;
+    smem = cfg.smem;
+    return true;
+}
+
 }  // namespace b200
 
 using namespace b200;
 
 extern "C" int b200_gemv_fused_supported(const b200_gemv_fused_args * a) {
-    gs_params p;
-    return gs_build(a, p) ? 1 : 0;
+    gs_params p; size_t smem; int types[2];
+    return gs_build_single(a, p, smem, types) ? 1 : 0;
 }
 
 extern "C" int b200_gemv_fused(const b200_gemv_fused_args * a, void * stream) {
-    gs_params p;
-    if (!gs_build(a, p)) { set_error("b200_gemv_fused: unsupported arguments"); return B200_ERR_UNSUPPORTED; }
+    gs_params p; size_t smem; int types[2];
+    if (!gs_build_single(a, p, smem, types)) { set_error("b200_gemv_fused: unsupported arguments"); return B200_ERR_UNSUPPORTED; }
     if (stream == B200_STREAM_VALIDATE) return B200_OK;
-    int t0 = p.seg[0].type, t1 = t0;
-    for (int s = 1; s < p.n_ws; ++s) if (p.seg[s].type != t0) t1 = p.seg[s].type;
-    // chunks available: never launch more CTAs than there are rows
     int64_t rows = 0;
-    for (int s = 0; s < p.n_ws; ++s) rows += p.seg[s].M;
+    for (int s = 0; s < p.inl.n_ws; ++s) rows += p.inl.seg[s].M;
     int grid = a->n_sm > 0 ? a->n_sm : gs_sm_count();
-    if (grid > rows) grid = (int) rows;
-    cudaStream_t st = (cudaStream_t) stream;
-    if (t0 == t1) {
-        switch (t0) {
-            case B200_Q4_K:  return gs_launch<B200_Q4_K, B200_Q4_K>(p, grid, st);
-            case B200_Q6_K:  return gs_launch<B200_Q6_K, B200_Q6_K>(p, grid, st);
-            case B200_Q4_0:  return gs_launch<B200_Q4_0, B200_Q4_0>(p, grid, st);
-            case B200_Q8_0:  return gs_launch<B200_Q8_0, B200_Q8_0>(p, grid, st);
-            case B200_MXFP4: return gs_launch<B200_MXFP4, B200_MXFP4>(p, grid, st);
-        }
+    if (grid > rows) grid = (int) rows;                // never launch more CTAs than there are rows
+    return gs_launch_types<false>(p, smem, grid, (cudaStream_t) stream, types[0], types[1]);
+}
+
+// ---------------------------------------------------------------- decode chain
+struct b200_chain {
+    gs_params p;
+    size_t smem = 0;
+    int grid = 0, t0 = -1, t1 = -1, device = 0;
+    gs_phase * d_phases = nullptr;
+    unsigned int * d_bar = nullptr;
+    int n_gemv = 0, n_attn = 0;
+    unsigned long long * d_dbg = nullptr;
+};
+
+static bool gs_build_attn(const b200_attn_phase * a, gs_phase & ph, int & attn_floats) {
+    const b200_tensor & q = a->q; const b200_tensor & k = a->k_cache; const b200_tensor & v = a->v_cache;
+    const int64_t D = k.ne[0], n_kv = k.ne[1], H_kv = k.ne[2];
+    if (D != 64 && D != 128) return false;
+    if (k.type != B200_F16 || v.type != B200_F16 || k.nb[0] != 2 || v.nb[0] != 2 || k.ne[3] != 1 || v.ne[3] != 1) return false;
+    if (v.ne[0] != D || v.ne[1] != n_kv || v.ne[2] != H_kv || n_kv < 1 || H_kv < 1) return false;
+    if (((uintptr_t) k.data | (uintptr_t) v.data) % 16 || k.nb[1] % 16 || k.nb[2] % 16 || v.nb[1] % 16 || v.nb[2] % 16) return false;
+    if (q.type != B200_F32 || q.nb[0] != 4 || nelements(q) % D != 0) return false;
+    const int64_t H = nelements(q) / D;
+    if (H < 1 || H % H_kv != 0) return false;
+    if (a->k_new.type != B200_F32 || a->v_new.type != B200_F32 || nelements(a->k_new) != D * H_kv || nelements(a->v_new) != D * H_kv) return false;
+    if (a->dst.type != B200_F32 || nelements(a->dst) != D * H) return false;
+    if (!a->pos || a->pos->type != B200_I32 || !a->slot || a->slot->type != B200_I64) return false;
+    if (a->mask && (a->mask->type != B200_F16 || a->mask->nb[0] != 2 || a->mask->ne[0] < n_kv)) return false;
+    const b200_rope_params & r = a->rope;
+    if ((r.mode != 0 && r.mode != 2) || r.n_dims <= 0 || r.n_dims % 2 || r.n_dims > D || r.ext_factor != 0.0f || r.attn_factor != 1.0f) return false;
+    memset(&ph, 0, sizeof(ph));
+    ph.kind = 1;
+    gs_attn & g = ph.attn;
+    g.q = (const float *) q.data; g.k_new = (const float *) a->k_new.data; g.v_new = (const float *) a->v_new.data;
+    g.k_cache = (char *) k.data; g.v_cache = (char *) v.data; g.mask = a->mask ? (const __half *) a->mask->data : nullptr;
+    g.dst = (float *) a->dst.data; g.pos = (const int32_t *) a->pos->data; g.slot = (const int64_t *) a->slot->data;
+    g.k_nb1 = k.nb[1]; g.k_nb2 = k.nb[2]; g.v_nb1 = v.nb[1]; g.v_nb2 = v.nb[2];
+    g.D = (int32_t) D; g.H = (int32_t) H; g.H_kv = (int32_t) H_kv; g.n_kv = (int32_t) n_kv;
+    g.rope_mode = r.mode; g.n_dims = r.n_dims; g.scale = a->scale;
+    g.theta_scale = powf(r.freq_base, -2.0f / (float) r.n_dims); g.freq_scale = r.freq_scale;
+    attn_floats = std::max(attn_floats, (int) (3 * D + GS_NW * (D + 2)));
+    return true;
+}
+
+extern "C" b200_chain * b200_chain_create(const b200_phase * phases, int n_phases, int flags) {
+    if (!phases || n_phases < 1 || n_phases > GS_MAX_PHASES) { set_error("b200_chain_create: bad phase count"); return nullptr; }
+    std::vector<gs_phase> ph((size_t) n_phases);
+    int64_t need = 0; int act_qs = 64, attn_floats = 0; int types[2] = {-1, -1};
+    b200_chain * ch = new b200_chain;
+    for (int i = 0; i < n_phases; ++i) {
+        bool ok;
+        if (phases[i].kind == B200_PHASE_GEMV) { ok = gs_build_phase(&phases[i].gemv, ph[i], need, act_qs, types); ch->n_gemv++; }
+        else if (phases[i].kind == B200_PHASE_ATTN) { ok = gs_build_attn(&phases[i].attn, ph[i], attn_floats); ch->n_attn++; }
+        else ok = false;
+        if (!ok) { set_error("b200_chain_create: phase %d is not supported", i); delete ch; return nullptr; }
     }
-    const int lo = t0 < t1 ? t0 : t1, hi = t0 < t1 ? t1 : t0;
-    if (lo == B200_Q4_K && hi == B200_Q6_K) return gs_launch<B200_Q4_K, B200_Q6_K>(p, grid, st);
-    if (lo == B200_Q4_0 && hi == B200_Q6_K) return gs_launch<B200_Q4_0, B200_Q6_K>(p, grid, st);
-    if (lo == B200_Q4_0 && hi == B200_Q8_0) return gs_launch<B200_Q4_0, B200_Q8_0>(p, grid, st);
-    set_error("b200_gemv_fused: unsupported type pair (%d, %d)", t0, t1);
-    return B200_ERR_UNSUPPORTED;
+    gs_config cfg;
+    if (types[0] < 0 || !gs_make_config(flags, need, act_qs, attn_floats, cfg)) { set_error("b200_chain_create: no ring configuration fits"); delete ch; return nullptr; }
+    for (int i = 0; i < n_phases; ++i)
+        if (ph[i].kind == 0 && !gs_finish_phase(ph[i], cfg.stage_payload)) { set_error("b200_chain_create: phase %d: row does not fit a stage", i); delete ch; return nullptr; }
+    cudaGetDevice(&ch->device);
+    if (cudaMalloc((void **) &ch->d_phases, sizeof(gs_phase) * (size_t) n_phases) != cudaSuccess ||
+        cudaMalloc((void **) &ch->d_bar, sizeof(unsigned int) * (size_t) n_phases) != cudaSuccess ||
+        cudaMemcpy(ch->d_phases, ph.data(), sizeof(gs_phase) * (size_t) n_phases, cudaMemcpyHostToDevice) != cudaSuccess) {
+        set_error("b200_chain_create: device allocation failed"); cudaGetLastError();
+        if (ch->d_phases) cudaFree(ch->d_phases); if (ch->d_bar) cudaFree(ch->d_bar);
+        delete ch; return nullptr;
+    }
+    memset(&ch->p, 0, sizeof(ch->p));
+    ch->p.phases = ch->d_phases; ch->p.bar = ch->d_bar; ch->p.n_phases = n_phases;
+    ch->p.act_qs_bytes = cfg.act_qs; ch->p.stage_stride = cfg.stage_payload + GS_STAGE_SLACK; ch->p.n_stages = cfg.n_stages;
+    ch->p.attn_floats = cfg.attn_floats; ch->p.flags = flags;
+    if (flags & 4) {
+        if (cudaMalloc((void **) &ch->d_dbg, sizeof(unsigned long long) * 8 * (size_t) n_phases) == cudaSuccess)
+            cudaMemset(ch->d_dbg, 0, sizeof(unsigned long long) * 8 * (size_t) n_phases);
+        ch->p.dbg = ch->d_dbg;
+    }
+    ch->smem = cfg.smem; ch->grid = gs_sm_count(); ch->t0 = types[0]; ch->t1 = types[1];
+    return ch;
+}
+
+extern "C" int b200_chain_launch(b200_chain * ch, void * stream) {
+    if (!ch) return B200_ERR_ARG;
+    cudaStream_t st = (cudaStream_t) stream;
+    B200_CUDA_TRY(cudaMemsetAsync(ch->d_bar, 0, sizeof(unsigned int) * (size_t) ch->p.n_phases, st));
+    return gs_launch_types<true>(ch->p, ch->smem, ch->grid, st, ch->t0, ch->t1);
+}
+
+// debug (flags bit 2): copies the globaltimer stamps [phase][cta 0 | last cta][barrier passed, prologue done, consumed, published]
+extern "C" int b200_chain_debug_read(b200_chain * ch, unsigned long long * out, int n_phases) {
+    if (!ch || !ch->d_dbg || n_phases > ch->p.n_phases) return B200_ERR_ARG;
+    B200_CUDA_TRY(cudaMemcpy(out, ch->d_dbg, sizeof(unsigned long long) * 8 * (size_t) n_phases, cudaMemcpyDeviceToHost));
+    return B200_OK;
+}
+
+extern "C" void b200_chain_destroy(b200_chain * ch) {
+    if (!ch) return;
+    cudaFree(ch->d_phases); cudaFree(ch->d_bar); if (ch->d_dbg) cudaFree(ch->d_dbg);
+    delete ch;
 }

@@ -59,6 +59,7 @@ class DecodeSession:
         self._alloc_state()
         self.graph = None
         self.launches_per_token = 0
+        self.chain, self.chain_n_kv, self.chain_keep, self.chain_flags = None, -1, [], 0
 
     # ------------------------------------------------------------------ ctypes plumbing
     def _bind(self):
@@ -250,8 +251,70 @@ class DecodeSession:
         self._chk(self.L.b200_flash_attn_ext(C.byref(a), self._st()), "flash_attn_ext")
 
     # ------------------------------------------------------------------ one token
+    def _build_chain(self, n_kv):
+        """The whole token as ONE cooperative launch: per layer [QKV | attention | wo | gate/up | down], then the logits."""
+        s = self.s
+        D, H, Hkv = s.head_dim, s.n_head, s.n_head_kv
+        assert self.world == 1 and self.kv_type == F16, "decode chain: single GPU, f16 KV"
+        keep, phases = self.chain_keep, []
+        x, x2 = self.x, self.x2
+
+        def seg(name, bias, dst):
+            wd, t, (K, M) = self.w[name]
+            return (wd, t, M, bias, dst)
+
+        hb = gguf_synth.row_bytes(self.kv_type, D)
+        mode = 2 if s.arch == "qwen2" else 0
+        for il in range(s.n_layer):
+            p = f"blk.{il}."
+            phases.append(capi.gemv_phase(x.view(-1), [seg(p + "attn_q.weight", self._full_bias(p + "attn_q.bias"), self.q.view(-1)),
+                                                       seg(p + "attn_k.weight", self._full_bias(p + "attn_k.bias"), self.k.view(-1)),
+                                                       seg(p + "attn_v.weight", self._full_bias(p + "attn_v.bias"), self.v.view(-1))],
+                                          norm_w=self.w[p + "attn_norm.weight"][0], eps=s.rms_eps, keep=keep))
+            ph = capi.Phase(); ph.kind = capi.PHASE_ATTN
+            a = ph.attn
+            a.q = capi.make_tensor(self.q.data_ptr(), F32, [D * H, 1, 1, 1])
+            a.k_new = capi.make_tensor(self.k.data_ptr(), F32, [D * Hkv, 1, 1, 1])
+            a.v_new = capi.make_tensor(self.v.data_ptr(), F32, [D * Hkv, 1, 1, 1])
+            nb = [2, self.kv_row_bytes, hb, self.kv_row_bytes * self.n_ctx]
+            a.k_cache = capi.make_tensor(self.kc[il].data_ptr(), F16, [D, n_kv, Hkv, 1], nb)
+            a.v_cache = capi.make_tensor(self.vc[il].data_ptr(), F16, [D, n_kv, Hkv, 1], nb)
+            tp, ts = capi.from_torch(self.pos), capi.from_torch(self.slot)
+            tm = capi.make_tensor(self.mask.data_ptr(), F16, [n_kv, 1, 1, 1], [2, 2 * self.n_ctx, 2 * self.n_ctx, 2 * self.n_ctx])
+            keep += [tp, ts, tm]
+            a.pos, a.slot, a.mask = C.pointer(tp), C.pointer(ts), C.pointer(tm)
+            a.rope = capi.RopeParams(D, mode, s.n_ctx_train, s.rope_base, 1.0, 0.0, 1.0, 32.0, 1.0)
+            a.scale = 1.0 / math.sqrt(D)
+            a.dst = capi.make_tensor(self.att.data_ptr(), F32, [D * H, 1, 1, 1])
+            phases.append(ph)
+            phases.append(capi.gemv_phase(self.att.view(-1), [seg(p + "attn_output.weight", x.view(-1), x2.view(-1))], keep=keep))
+            phases.append(capi.gemv_phase(x2.view(-1), [seg(p + "ffn_gate.weight", None, None), seg(p + "ffn_up.weight", None, self.ff.view(-1))],
+                                          norm_w=self.w[p + "ffn_norm.weight"][0], eps=s.rms_eps, glu_op=capi.GLU_SWIGLU, keep=keep))
+            phases.append(capi.gemv_phase(self.ff.view(-1), [seg(p + "ffn_down.weight", x2.view(-1), x.view(-1))], keep=keep))
+        phases.append(capi.gemv_phase(x.view(-1), [seg("output.weight", None, self.logits.view(-1))],
+                                      norm_w=self.w["output_norm.weight"][0], eps=s.rms_eps, keep=keep))
+        return capi.Chain(phases, flags=self.chain_flags, keep=keep)
+
+    def _issue_token_chain(self, n_kv):
+        torch = self.torch
+        self._n = 0
+        self.mask.view(-1).index_copy_(0, self.slot, self.zero16.view(-1))
+        if self.resident_tokens:
+            torch.index_select(self.tokens, 0, self.slot, out=self.tok)
+        emb, et, ene = self.w["token_embd.weight"]
+        te, tt, tx = self._t(emb, et, [ene[0], ene[1], 1, 1]), self._t(self.tok), self._t(self.x)
+        self._chk(self.L.b200_get_rows(C.byref(te), C.byref(tt), C.byref(tx), self._st()), "get_rows")
+        if self.chain is None or self.chain_n_kv != n_kv:
+            self.chain, self.chain_n_kv = self._build_chain(n_kv), n_kv
+        self.chain.launch()
+        self._n += 1
+        self.pos.add_(1); self.slot.add_(1)
+        return self._n
+
     def _issue_token(self, n_kv):
         """Issue every kernel of one decode step on the current stream. Returns the launch count."""
+        if self.fused == "chain":
+            return self._issue_token_chain(n_kv)
         s, torch = self.s, self.torch
         self._n = 0
         # bookkeeping on device: open the mask at the slot being written (integer/f16 plumbing)
@@ -347,6 +410,7 @@ class DecodeSession:
         pass (GBs) exceed L2, so every launch streams from HBM."""
         torch, s = self.torch, self.s
         gather, self.gather = self.gather, (lambda *a: None)
+        mode, self.fused = self.fused, (True if self.fused == "chain" else self.fused)
 
         def issue():
             self._n = 0
@@ -391,5 +455,5 @@ class DecodeSession:
             g.replay()
         e1.record()
         torch.cuda.synchronize()
-        self.gather = gather
+        self.gather, self.fused = gather, mode
         return e0.elapsed_time(e1) / reps, n

@@ -80,7 +80,7 @@ def reference_decode(orc, gs, shape, weights, tokens):
 
 
 @pytest.mark.parametrize("key", ["tiny-q4_0", "tiny-q4_k_m", "tiny-q8_0"])
-@pytest.mark.parametrize("graph,fused", [(False, True), (True, True), (False, False)])
+@pytest.mark.parametrize("graph,fused", [(False, True), (True, True), (False, False), (False, "chain"), (True, "chain")])
 def test_decode_session_vs_numpy(orc, key, graph, fused):
     import torch
     from llama_mi50_b200 import gguf_synth as gs
