@@ -148,6 +148,7 @@ typedef struct b200_attn_phase {
     b200_rope_params rope;           /* modes NORMAL(0) / NEOX(2), no YaRN (ext_factor 0, attn_factor 1) */
     float scale;
     b200_tensor dst;                 /* f32 [D*H] */
+    const b200_tensor * slot_v;      /* i64 [1]: cache row of V (NULL: same as slot; ggml passes k_idxs / v_idxs separately) */
 } b200_attn_phase;
 typedef struct b200_phase {
     int32_t kind;                    /* b200_phase_kind */

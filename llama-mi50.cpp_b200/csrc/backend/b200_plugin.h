@@ -7,6 +7,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <deque>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -73,6 +74,24 @@ ggml_status b200_graph_compute(b200_context * ctx, ggml_cgraph * cgraph);
 bool        b200_supports_op(int device, const ggml_tensor * op);
 void        b200_context_free(b200_context * ctx);
 void        b200_timing_collect(b200_context * ctx);
+
+// ---- decode-chain plan (chain_plan.cpp): the graph as a list of chain phases and plain nodes
+enum b200_item_kind { B200_ITEM_NODE = 0, B200_ITEM_PHASE = 1 };
+struct b200_plan_item {
+    int        kind = B200_ITEM_NODE;
+    int        first_node = 0;      // index into the graph
+    int        n_nodes = 0;
+    bool       scratch_rel = false; // phase tensors whose data pointer is an offset into the chain's private scratch
+    bool       hoisted = false;     // plain node moved out of an attention block: runs alone, out of index order
+    b200_phase phase;
+};
+struct b200_plan {
+    std::vector<b200_plan_item> items;
+    std::deque<b200_tensor>     pool;            // descriptors the phases point to (norm weights, biases, positions, masks)
+    int64_t                     scratch_floats = 0;
+};
+void b200_plan_build(ggml_cgraph * g, b200_plan & plan);
+bool b200_gemv_fused_supported_rel(const b200_gemv_fused_args & a);
 
 // ---- tensor translation
 static inline b200_tensor b200_desc(const ggml_tensor * t) {

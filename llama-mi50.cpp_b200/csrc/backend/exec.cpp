@@ -25,7 +25,7 @@ struct exec_state {
     const void * q8_src_data = nullptr;
     size_t need_q8 = 0, need_fa = 0;   // scratch high-water marks found during the sizing pass
     bool sizing = false;               // sizing pass: compute need_*, launch nothing
-    uint64_t launches = 0;
+    uint64_t launches = 0, chain_phases = 0;
 };
 
 int64_t pad_to(int64_t x, int64_t n) { return (x + n - 1) / n * n; }
@@ -218,7 +218,16 @@ void make_key(const ggml_tensor * n, node_key & k) {
 
 }  // namespace
 
+struct b200_chain_entry { b200_chain * chain = nullptr; float * scratch = nullptr; int n_phases = 0; };
+
 struct b200_graph_cache {
+    b200_plan plan;                    // the graph `keys` describes, compiled into chain phases + plain nodes
+    bool plan_built = false;
+    std::vector<b200_chain_entry> chains;
+    void drop_chains() {
+        for (b200_chain_entry & e : chains) { b200_chain_destroy(e.chain); if (e.scratch) cudaFree(e.scratch); }
+        chains.clear(); plan_built = false;
+    }
     std::vector<node_key> keys;        // properties of the graph last seen
     cudaGraphExec_t exec = nullptr;    // instantiated capture of `keys` (or null)
     uint64_t kernels = 0;              // kernel nodes in `exec`
@@ -230,13 +239,13 @@ namespace {
 bool same_shape(const ggml_tensor * a, const ggml_tensor * b) { return ggml_are_same_shape(a, b); }
 
 // returns the number of graph nodes consumed starting at i (>= 1)
-int run_fused(exec_state & st, ggml_cgraph * g, int i, bool fusion) {
+int run_fused(exec_state & st, ggml_cgraph * g, int i, bool fusion, int node_limit) {
     ggml_tensor * n = g->nodes[i];
     if (fusion && !st.validate) {
         // {RMS_NORM, MUL[, ADD]}  (reference fusion: ggml-cuda.cu:3844-3854)
         if (n->op == GGML_OP_RMS_NORM) {
             const ggml_op ops3[] = {GGML_OP_RMS_NORM, GGML_OP_MUL, GGML_OP_ADD};
-            int cnt = ggml_can_fuse(g, i, ops3, 3) ? 3 : ggml_can_fuse(g, i, ops3, 2) ? 2 : 1;
+            int cnt = (i + 3 <= node_limit && ggml_can_fuse(g, i, ops3, 3)) ? 3 : (i + 2 <= node_limit && ggml_can_fuse(g, i, ops3, 2)) ? 2 : 1;
             while (cnt > 1) {
                 const ggml_tensor * mul = g->nodes[i + 1];
                 const ggml_tensor * w = mul->src[0] == n ? mul->src[1] : mul->src[0];
@@ -253,7 +262,7 @@ int run_fused(exec_state & st, ggml_cgraph * g, int i, bool fusion) {
             }
         }
         // {MUL_MAT(gate), MUL_MAT(up), GLU} on one activation column (reference: ggml-cuda.cu:3737-3771)
-        if (n->op == GGML_OP_MUL_MAT && i + 2 < g->n_nodes && n->ne[1] == 1 && n->ne[2] == 1 && n->ne[3] == 1) {
+        if (n->op == GGML_OP_MUL_MAT && i + 2 < node_limit && n->ne[1] == 1 && n->ne[2] == 1 && n->ne[3] == 1) {
             ggml_tensor * m2 = g->nodes[i + 1]; ggml_tensor * glu = g->nodes[i + 2];
             if (m2->op == GGML_OP_MUL_MAT && glu->op == GGML_OP_GLU && m2->src[1] == n->src[1] && glu->src[0] && glu->src[1] &&
                 ((glu->src[0] == n && glu->src[1] == m2) || (glu->src[0] == m2 && glu->src[1] == n)) &&
@@ -273,7 +282,7 @@ int run_fused(exec_state & st, ggml_cgraph * g, int i, bool fusion) {
             }
         }
         // {MUL_MAT, ADD} with a single column: the addend (bias or residual stream) rides in the GEMV epilogue
-        if (n->op == GGML_OP_MUL_MAT && i + 1 < g->n_nodes && n->ne[1] == 1 && n->ne[2] == 1 && n->ne[3] == 1) {
+        if (n->op == GGML_OP_MUL_MAT && i + 1 < node_limit && n->ne[1] == 1 && n->ne[2] == 1 && n->ne[3] == 1) {
             ggml_tensor * add = g->nodes[i + 1];
             if (add->op == GGML_OP_ADD && (add->src[0] == n || add->src[1] == n) && ggml_node_has_n_uses(g, i, 1) && same_shape(add, n)) {
                 const ggml_tensor * other = add->src[0] == n ? add->src[1] : add->src[0];
@@ -301,8 +310,55 @@ void walk_graph(exec_state & st, ggml_cgraph * g, bool fusion) {
     for (int i = 0; i < g->n_nodes;) {
         ggml_tensor * n = g->nodes[i];
         if (ggml_is_empty(n) || (n->flags & GGML_TENSOR_FLAG_COMPUTE) == 0) { ++i; continue; }
-        i += run_fused(st, g, i, fusion);
+        i += run_fused(st, g, i, fusion, g->n_nodes);
     }
+}
+
+// one chain = a maximal run of consecutive phases of the plan; built on first use, replayed afterwards
+void flush_chain(exec_state & st, b200_graph_cache & c, std::vector<b200_plan_item *> & pending, size_t & seq) {
+    if (pending.empty()) return;
+    if (!st.sizing) {
+        if (seq >= c.chains.size()) {
+            b200_chain_entry e;
+            if (c.plan.scratch_floats > 0) B200_CUDA_CHECK(cudaMalloc((void **) &e.scratch, (size_t) c.plan.scratch_floats * sizeof(float)));
+            std::vector<b200_phase> ph;
+            for (b200_plan_item * it : pending) {
+                b200_phase p = it->phase;
+                if (it->scratch_rel) {
+                    char * base = (char *) e.scratch;
+                    if (p.kind == B200_PHASE_GEMV) { for (int s = 0; s < p.gemv.n_seg; ++s) p.gemv.seg[s].dst.data = base + (intptr_t) p.gemv.seg[s].dst.data; }
+                    else { p.attn.q.data = base + (intptr_t) p.attn.q.data; p.attn.k_new.data = base + (intptr_t) p.attn.k_new.data; p.attn.v_new.data = base + (intptr_t) p.attn.v_new.data; }
+                }
+                ph.push_back(p);
+            }
+            e.chain = b200_chain_create(ph.data(), (int) ph.size(), 0);
+            if (!e.chain) b200_abort(__FILE__, __LINE__, "b200_chain_create", b200_last_error());
+            e.n_phases = (int) ph.size();
+            c.chains.push_back(e);
+        }
+        B200_KCHECK(b200_chain_launch(c.chains[seq].chain, st.stream));
+        st.launches++; st.chain_phases += (uint64_t) c.chains[seq].n_phases;
+    }
+    ++seq;
+    pending.clear();
+}
+
+void walk_plan(exec_state & st, ggml_cgraph * g, b200_graph_cache & c, bool fusion) {
+    std::vector<b200_plan_item *> pending;
+    size_t seq = 0;
+    int next_node = 0;
+    std::vector<b200_plan_item> & items = c.plan.items;
+    for (size_t k = 0; k < items.size(); ++k) {
+        b200_plan_item & it = items[k];
+        if (it.kind == B200_ITEM_PHASE) { pending.push_back(&it); continue; }
+        if (it.hoisted) { flush_chain(st, c, pending, seq); run_fused(st, g, it.first_node, false, it.first_node + 1); continue; }
+        if (it.first_node < next_node) continue;                  // consumed by a fusion of the previous plain node
+        flush_chain(st, c, pending, seq);
+        int limit = g->n_nodes;                                   // plain-node fusions stop where the next phase begins
+        for (size_t j = k + 1; j < items.size(); ++j) if (items[j].kind == B200_ITEM_PHASE || items[j].hoisted) { limit = items[j].first_node; break; }
+        next_node = it.first_node + run_fused(st, g, it.first_node, fusion, std::max(limit, it.first_node + 1));
+    }
+    flush_chain(st, c, pending, seq);
 }
 
 void grow(b200_context * ctx, char *& p, size_t & cur, size_t need, bool zero) {
@@ -333,6 +389,7 @@ void b200_timing_collect(b200_context * ctx) {
 ggml_status b200_graph_compute(b200_context * ctx, ggml_cgraph * g) {
     b200_set_device(ctx->device);
     static const bool no_graphs = env_flag("GGML_B200_DISABLE_GRAPHS"), no_fusion = env_flag("GGML_B200_DISABLE_FUSION");
+    static const bool no_chain = env_flag("GGML_B200_DISABLE_CHAIN") || no_fusion;
     if (!ctx->cache) ctx->cache = new b200_graph_cache;
     b200_graph_cache & c = *ctx->cache;
 
@@ -340,7 +397,12 @@ ggml_status b200_graph_compute(b200_context * ctx, ggml_cgraph * g) {
     std::vector<node_key> keys((size_t) g->n_nodes);
     for (int i = 0; i < g->n_nodes; ++i) make_key(g->nodes[i], keys[i]);
     const bool same = keys.size() == c.keys.size() && (keys.empty() || memcmp(keys.data(), c.keys.data(), keys.size() * sizeof(node_key)) == 0);
-    if (!same) { c.keys.swap(keys); c.seen = 0; if (c.exec) { cudaGraphExecDestroy(c.exec); c.exec = nullptr; } }
+    if (!same) {
+        c.keys.swap(keys); c.seen = 0;
+        if (c.exec) { cudaGraphExecDestroy(c.exec); c.exec = nullptr; }
+        if (!c.chains.empty()) B200_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));   // a chain of the previous graph may still be running
+        c.drop_chains();
+    }
     c.seen++;
 
     if (ctx->timing) {   // device time of the previous graph must be read before its events are re-recorded
@@ -354,8 +416,10 @@ ggml_status b200_graph_compute(b200_context * ctx, ggml_cgraph * g) {
         launched = c.kernels; replay = true;
     } else {
         // 2. size the scratch arenas (no launches)
+        if (!no_chain && !c.plan_built) { b200_plan_build(g, c.plan); c.plan_built = true; }
+        auto walk = [&](exec_state & s) { if (no_chain) walk_graph(s, g, !no_fusion); else walk_plan(s, g, c, true); };
         exec_state sz; sz.ctx = ctx; sz.validate = false; sz.sizing = true;
-        walk_graph(sz, g, !no_fusion);
+        walk(sz);
         grow(ctx, ctx->q8_scratch, ctx->q8_size, sz.need_q8, false);
         grow(ctx, ctx->fa_scratch, ctx->fa_size, sz.need_fa, true);
 
@@ -363,7 +427,7 @@ ggml_status b200_graph_compute(b200_context * ctx, ggml_cgraph * g) {
         const bool capture = !no_graphs && c.seen >= 2;
         exec_state st; st.ctx = ctx; st.validate = false; st.stream = ctx->stream;
         if (capture) B200_CUDA_CHECK(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed));
-        walk_graph(st, g, !no_fusion);
+        walk(st);
         launched = st.launches;
         if (capture) {
             cudaGraph_t graph = nullptr;
@@ -386,7 +450,7 @@ ggml_status b200_graph_compute(b200_context * ctx, ggml_cgraph * g) {
 void b200_context_free(b200_context * ctx) {
     b200_set_device(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    if (ctx->cache) { if (ctx->cache->exec) cudaGraphExecDestroy(ctx->cache->exec); delete ctx->cache; }
+    if (ctx->cache) { if (ctx->cache->exec) cudaGraphExecDestroy(ctx->cache->exec); ctx->cache->drop_chains(); delete ctx->cache; }
     if (ctx->q8_scratch) cudaFree(ctx->q8_scratch);
     if (ctx->fa_scratch) cudaFree(ctx->fa_scratch);
     if (ctx->ev_begin) cudaEventDestroy(ctx->ev_begin);

@@ -56,7 +56,7 @@ struct gs_seg {
 struct gs_attn {
     const float * q; const float * k_new; const float * v_new;   // raw projections of the current token
     char * k_cache; char * v_cache; const __half * mask; float * dst;
-    const int32_t * pos; const int64_t * slot;
+    const int32_t * pos; const int64_t * slot; const int64_t * slot_v;
     int64_t k_nb1, k_nb2, v_nb1, v_nb2;
     int32_t D, H, H_kv, n_kv, rope_mode, n_dims;
     float scale, theta_scale, freq_scale;
@@ -380,7 +380,10 @@ __device__ __forceinline__ void consume_segment(const gs_ctx & c, const gs_phase
     for (int s = 0; s < SPW; ++s) itm[s].init((ks + s * KS) * 32 + lane, sg.ipr, c.aq, c.ads);
     const int rb = sg.rb, R = sg.R;
     const bool pair = sg.nsub == 2;
-    const int rpp = pair ? 1 : GS_RB;                      // output rows per warp pass
+    const int rpp = pair ? 1 : (R >= GS_RB ? GS_RB : 1);   // output rows per warp pass
+    const int RGP = RG * rpp;                              // output rows per CTA pass
+    int off = 0;                                           // (row - r0) mod RGP: row groups rotate through the chunks, so a
+                                                           // chunk shorter than a CTA pass does not leave the same warps idle
     const float * __restrict__ bias = sg.bias;
     float * __restrict__ dst = sg.dst;
     const int glu_op = ph.glu_op; const float glu_alpha = ph.glu_alpha, glu_limit = ph.glu_limit;
@@ -394,7 +397,9 @@ __device__ __forceinline__ void consume_segment(const gs_ctx & c, const gs_phase
         const uint8_t * sub0 = c.ring + pos.st * c.stage_stride + ga0;
         const uint8_t * sub1 = sub0 - ga0 + ((ga0 + (uint32_t) nr * rb + 15u) & ~15u) + ga1;
         mbar_wait(&sh.full[pos.st], pos.full_par);
-        for (int jb = rg * rpp; jb < nr; jb += RG * rpp) {
+        int jb0 = rg * rpp - off; if (jb0 < 0) jb0 += RGP;
+        off += R; while (off >= RGP) off -= RGP;
+        for (int jb = jb0; jb < nr; jb += RGP) {
             const uint8_t * rowp[GS_RB];
             if (pair) { rowp[0] = sub0 + jb * rb; rowp[1] = sub1 + jb * rb; }
             else {
@@ -439,7 +444,7 @@ __device__ __forceinline__ void consume_segment(const gs_ctx & c, const gs_phase
                 } else {
 #pragma unroll
                     for (int j = 0; j < GS_RB; ++j)
-                        if (jb + j < nr) dst[row + jb + j] = acc[j] + bv[j];
+                        if (j < rpp && jb + j < nr) dst[row + jb + j] = acc[j] + bv[j];
                 }
             }
         }
@@ -571,7 +576,7 @@ __device__ __forceinline__ void gs_attn_item(const gs_attn & a, int h, float * s
     constexpr int LPP = D / 32, PPB = 32 / LPP, DPL = D / 32;     // lanes per position, positions per batch, dims per lane (V)
     const int tid = warp * 32 + lane;
     const int gqa = a.H / a.H_kv, g = h / gqa;
-    const int pos = __ldcg(a.pos), slot = (int) __ldcg(a.slot);
+    const int pos = __ldcg(a.pos), slot = (int) __ldcg(a.slot), slot_v = (int) __ldcg(a.slot_v);
     float * s_q = sm, * s_k = sm + D, * s_v = sm + 2 * D, * s_part = sm + 3 * D;      // s_part: [GS_NW][D + 2]
     // ---- 1. RoPE(q[h]) * scale, RoPE(k_new[g]) and v_new[g] rounded to f16
     {
@@ -604,7 +609,7 @@ __device__ __forceinline__ void gs_attn_item(const gs_attn & a, int h, float * s
     if (h % gqa == 0 && tid < 2 * D) {                            // KV-cache write of the current token (one writer per group)
         const int d = tid < D ? tid : tid - D;
         char * row = tid < D ? a.k_cache + (int64_t) slot * a.k_nb1 + (int64_t) g * a.k_nb2
-                             : a.v_cache + (int64_t) slot * a.v_nb1 + (int64_t) g * a.v_nb2;
+                             : a.v_cache + (int64_t) slot_v * a.v_nb1 + (int64_t) g * a.v_nb2;
         ((__half *) row)[d] = __float2half_rn(tid < D ? s_k[d] : s_v[d]);
     }
     // ---- 2. scores + online softmax + V accumulation, KV positions strided over the warps
@@ -657,7 +662,7 @@ __device__ __forceinline__ void gs_attn_item(const gs_attn & a, int h, float * s
             const float pj = __shfl_sync(0xffffffffu, pr, j * LPP);
             const int pp = base + j;
             if (pj != 0.0f) {                                     // warp-uniform
-                if (pp == slot) {
+                if (pp == slot_v) {
 #pragma unroll
                     for (int i = 0; i < DPL; ++i) acc[i] += pj * s_v[lane * DPL + i];
                 } else {
@@ -871,10 +876,15 @@ static bool gs_build_phase(const b200_gemv_fused_args * a, gs_phase & ph, int64_
         g.dst = (float *) src.dst.data;
         g.M = (int32_t) src.w.ne[1]; g.rb = (int32_t) src.w.nb[1]; g.type = src.w.type;
         g.ipr = (int32_t) (K / gs_wpi(g.type)); g.spr = (g.ipr + 31) / 32;
-        int KS = 1; while (KS * 2 <= GS_NW && KS * 2 <= g.spr) KS *= 2;
+        // the fewest warps per row whose lanes can hold the activations of their K slice in registers: every extra
+        // K split costs a cross-warp reduction per pass
+        const int max_spw = gs_wpi(g.type) == 64 ? 2 : 4;
+        int KS = 1; while (KS < GS_NW && (g.spr + KS - 1) / KS > max_spw) KS *= 2;
+        const int force = (a->flags >> 16) & 0xF;                       // tuning: log2(KS) + 1
+        if (force) KS = std::max(KS, std::min(1 << (force - 1), GS_NW));
         int spw = (g.spr + KS - 1) / KS;
         if (spw == 3) spw = 4;
-        if (spw > (gs_wpi(g.type) == 64 ? 2 : 4)) return false;        // row too long for the register-resident activation
+        if (spw > max_spw) return false;                                // row too long for the register-resident activation
         g.KS = KS; g.spw = spw;
     }
     return true;
@@ -885,12 +895,10 @@ static bool gs_finish_phase(gs_phase & ph, int stage_payload) {
     int64_t prefix = 0;
     for (int s = 0; s < ph.n_ws; ++s) {
         gs_seg & g = ph.seg[s];
-        const int RG = GS_NW / g.KS;
         int R = (stage_payload - 64) / (g.rb * g.nsub);
         if (R > 64) R = 64;
         if (R < 1) return false;
-        const int pass = g.nsub == 2 ? RG : RG * GS_RB;  // output rows per CTA pass
-        if (R > pass) R -= R % pass;
+        if (g.nsub == 1 && R > GS_RB) R -= R % GS_RB;    // whole warp passes per chunk
         g.R = R;
         g.byte_prefix = prefix;
         prefix += (int64_t) g.rb * g.nsub * g.M;
@@ -1025,7 +1033,7 @@ static bool gs_build_attn(const b200_attn_phase * a, gs_phase & ph, int & attn_f
     if (H < 1 || H % H_kv != 0) return false;
     if (a->k_new.type != B200_F32 || a->v_new.type != B200_F32 || nelements(a->k_new) != D * H_kv || nelements(a->v_new) != D * H_kv) return false;
     if (a->dst.type != B200_F32 || nelements(a->dst) != D * H) return false;
-    if (!a->pos || a->pos->type != B200_I32 || !a->slot || a->slot->type != B200_I64) return false;
+    if (!a->pos || a->pos->type != B200_I32 || !a->slot || a->slot->type != B200_I64 || (a->slot_v && a->slot_v->type != B200_I64)) return false;
     if (a->mask && (a->mask->type != B200_F16 || a->mask->nb[0] != 2 || a->mask->ne[0] < n_kv)) return false;
     const b200_rope_params & r = a->rope;
     if ((r.mode != 0 && r.mode != 2) || r.n_dims <= 0 || r.n_dims % 2 || r.n_dims > D || r.ext_factor != 0.0f || r.attn_factor != 1.0f) return false;
@@ -1035,6 +1043,7 @@ static bool gs_build_attn(const b200_attn_phase * a, gs_phase & ph, int & attn_f
     g.q = (const float *) q.data; g.k_new = (const float *) a->k_new.data; g.v_new = (const float *) a->v_new.data;
     g.k_cache = (char *) k.data; g.v_cache = (char *) v.data; g.mask = a->mask ? (const __half *) a->mask->data : nullptr;
     g.dst = (float *) a->dst.data; g.pos = (const int32_t *) a->pos->data; g.slot = (const int64_t *) a->slot->data;
+    g.slot_v = a->slot_v ? (const int64_t *) a->slot_v->data : g.slot;
     g.k_nb1 = k.nb[1]; g.k_nb2 = k.nb[2]; g.v_nb1 = v.nb[1]; g.v_nb2 = v.nb[2];
     g.D = (int32_t) D; g.H = (int32_t) H; g.H_kv = (int32_t) H_kv; g.n_kv = (int32_t) n_kv;
     g.rope_mode = r.mode; g.n_dims = r.n_dims; g.scale = a->scale;
@@ -1072,8 +1081,8 @@ extern "C" b200_chain * b200_chain_create(const b200_phase * phases, int n_phase
     ch->p.act_qs_bytes = cfg.act_qs; ch->p.stage_stride = cfg.stage_payload + GS_STAGE_SLACK; ch->p.n_stages = cfg.n_stages;
     ch->p.attn_floats = cfg.attn_floats; ch->p.flags = flags;
     if (flags & 4) {
-        if (cudaMalloc((void **) &ch->d_dbg, sizeof(unsigned long long) * 8 * (size_t) n_phases) == cudaSuccess)
-            cudaMemset(ch->d_dbg, 0, sizeof(unsigned long long) * 8 * (size_t) n_phases);
+        if (cudaMalloc((void **) &ch->d_dbg, sizeof(unsigned long long) * 16 * (size_t) n_phases) == cudaSuccess)
+            cudaMemset(ch->d_dbg, 0, sizeof(unsigned long long) * 16 * (size_t) n_phases);
         ch->p.dbg = ch->d_dbg;
     }
     ch->smem = cfg.smem; ch->grid = gs_sm_count(); ch->t0 = types[0]; ch->t1 = types[1];
@@ -1090,7 +1099,7 @@ extern "C" int b200_chain_launch(b200_chain * ch, void * stream) {
 // debug (flags bit 2): copies the globaltimer stamps [phase][cta 0 | last cta][barrier passed, prologue done, consumed, published]
 extern "C" int b200_chain_debug_read(b200_chain * ch, unsigned long long * out, int n_phases) {
     if (!ch || !ch->d_dbg || n_phases > ch->p.n_phases) return B200_ERR_ARG;
-    B200_CUDA_TRY(cudaMemcpy(out, ch->d_dbg, sizeof(unsigned long long) * 8 * (size_t) n_phases, cudaMemcpyDeviceToHost));
+    B200_CUDA_TRY(cudaMemcpy(out, ch->d_dbg, sizeof(unsigned long long) * 16 * (size_t) n_phases, cudaMemcpyDeviceToHost));
     return B200_OK;
 }
 

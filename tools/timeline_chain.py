@@ -23,19 +23,25 @@ L = capi.lib()
 L.b200_chain_debug_read.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
 assert L.b200_chain_debug_read(sess.chain.h, out.ctypes.data_as(C.c_void_p), n) == 0
 d = out.reshape(n, 2, 8).astype(np.int64)
-t0 = d[0, 0, 0]
+# stamps per phase and CTA (0 = CTA 0, 1 = last CTA): [0] dependency satisfied, [1] prologue done, [2] rows consumed
+# (warp 0), [4] fence + CTA barrier done, [3] arrival counted
 names = ["qkv", "attn", "wo", "gateup", "down"]
-print("phase      | cta0: barrier-passed  +prologue  +consume  +publish | last cta: same      (ns; deltas within phase)   phase period")
-prev = t0
-tot = {}
-for i in range(n):
-    nm = names[i % 5] if i < n - 1 else "logits"
-    a, b = d[i, 0], d[i, 1]
-    period = a[0] - prev; prev = a[0]
-    tot.setdefault(nm, []).append((period, a[1] - a[0], a[2] - a[1], a[3] - a[2], b[3] - a[3], a[6] - a[2], a[4] - a[6], a[5] - a[4], a[3] - a[5]))
-    if i < 12 or i > n - 4:
-        print(f"{i:3d} {nm:7s}| {a[0]-t0:9d} {a[1]-a[0]:8d} {a[2]-a[1]:8d} {a[3]-a[2]:8d} | {b[0]-t0:9d} {b[1]-b[0]:8d} {b[2]-b[1]:8d} {b[3]-b[2]:8d}   {period:8d}")
-print("total ns", d[n - 1, 0, 3] - t0)
-for nm, v in tot.items():
-    v = np.array(v[1:] if len(v) > 1 else v)
-    print(f"{nm:7s} mean: wait-for-barrier-since-prev-phase-start {v[:,0].mean():8.0f}  prologue {v[:,1].mean():7.0f}  consume {v[:,2].mean():7.0f}  publish {v[:,3].mean():7.0f}  last-vs-first cta publish skew {v[:,4].mean():7.0f} | last consumer warp after warp0 {v[:,5].mean():6.0f}  finalizer done after that {v[:,6].mean():6.0f}  fence {v[:,7].mean():6.0f}  atomic {v[:,8].mean():6.0f}")
+for cta in (0, 1):
+    t0 = d[0, cta, 0]
+    rows = {}
+    prev_pub = t0
+    for i in range(n):
+        nm = names[i % 5] if i < n - 1 else "logits"
+        a = d[i, cta]
+        a1 = a[1] if a[1] else a[0]
+        rows.setdefault(nm, []).append((a[0] - prev_pub, a1 - a[0], a[2] - a1, a[4] - a[2], a[3] - a[4]))
+        prev_pub = a[3]
+    print(f"== CTA {'0' if cta == 0 else 'last'}: token {(d[n-1, cta, 3] - t0) / 1e3:.1f} us; mean ns per phase kind (first layer skipped)")
+    print("phase    wait-dep  prologue   consume  fence+bar    atomic     total")
+    layer = 0.0
+    for nm, v in rows.items():
+        v = np.array(v[1:] if len(v) > 1 else v, dtype=np.float64)
+        m = v.mean(axis=0)
+        if nm != "logits": layer += m.sum()
+        print(f"{nm:7s} {m[0]:9.0f} {m[1]:9.0f} {m[2]:9.0f} {m[3]:10.0f} {m[4]:9.0f} {m.sum():9.0f}")
+    print(f"per layer {layer / 1e3:.2f} us")
