@@ -303,9 +303,14 @@ def main_b200(a):
             line["llama_bench_error"] = str(e)[-400:]
             line.setdefault("cpu_baseline", {"value": None, "unit": "tok/s", "cores": 0, "kind": "reference", "sample": "failed: " + str(e)[-200:]})
     if rank == 0:
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # tearing the NCCL communicator down while captured graphs still hold its kernels was observed to hang
+        # (2 x B200, torch 2.11): leave together and skip the teardown
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush(); sys.stderr.flush()
+        os._exit(0)
     return 0
 
 

@@ -181,7 +181,8 @@ class DecodeSession:
             tg = capi.make_tensor(gd.data_ptr(), gt, [K, M, 1, 1]); self.keep.append(tg); a.gate_w = C.pointer(tg)
         a.glu_op, a.glu_alpha, a.glu_limit = glu, 1.702, 7.0
         self.keep.append(a)
-        self._chk(self.L.b200_mul_mat_vec_q(C.byref(a), self._st()), "mmvq " + wname)
+        if M > 0:        # a rank may own no rows of a small matrix (boundaries round down to 128 rows)
+            self._chk(self.L.b200_mul_mat_vec_q(C.byref(a), self._st()), "mmvq " + wname)
         if split:
             lo, hi = row_split(dst.shape[-1], self.world, self.rank)
             self.gather(out.view(-1), dst.view(-1), lo, hi)
@@ -199,10 +200,12 @@ class DecodeSession:
                 out = self.loc[o:o + M]; o += M
                 post.append((out, dst, lo, hi))
                 bias = bias.view(-1)[lo:hi] if bias is not None else None
-            csegs.append((wd, t, M, bias, out))
+            if M > 0:    # a rank may own no rows of a small matrix (boundaries round down to 128 rows)
+                csegs.append((wd, t, M, bias, out))
         nw = self.w[norm][0] if norm else None
-        a = capi.gemv_fused_args(x.view(-1), csegs, norm_w=nw, eps=self.s.rms_eps, glu_op=glu, keep=self.keep)
-        self._chk(self.L.b200_gemv_fused(C.byref(a), self._st()), "gemv_fused")
+        if csegs:
+            a = capi.gemv_fused_args(x.view(-1), csegs, norm_w=nw, eps=self.s.rms_eps, glu_op=glu, keep=self.keep)
+            self._chk(self.L.b200_gemv_fused(C.byref(a), self._st()), "gemv_fused")
         for out, dst, lo, hi in post:
             self.gather(out, dst.view(-1), lo, hi)
 
