@@ -163,6 +163,28 @@ B200_API void         b200_chain_destroy(b200_chain * chain);
 /* flags bit 2 at create time: per-phase globaltimer stamps of the first and last CTA (tools/timeline_chain.py) */
 B200_API int          b200_chain_debug_read(b200_chain * chain, unsigned long long * out, int n_phases);
 
+/* ---- K5: prefill GEMM on the tensor cores (tcgen05 + TMEM) ------------------------------------------
+ * dst[M, N] = W[M, K] . x[K, N] for N > 8 columns.  Replaces ggml_cuda_mul_mat_q (reference ggml-cuda/mmq.cu:71-218,
+ * mmq.cuh:3459-3698): the raw GGUF blocks travel by TMA, are expanded to f16 in shared memory by dequant warps and
+ * multiplied with 16-bit activations by tcgen05.mma (f32 accumulation in TMEM).  Two steps so that matmuls sharing an
+ * activation (q/k/v, gate/up) convert it once:
+ *   b200_mmq_convert_act : x f32 [K, N] -> pre-swizzled 16-bit tiles in `xb` (b200_mmq_act_size bytes, 1024 B aligned);
+ *                          act_fmt 0 = f16 (clamped to +-65504); 1 = bf16 tiles can be produced, but the GEMM only takes 0
+ *                          (tcgen05 kind::f16 traps on an f16 A with a bf16 B)
+ *   b200_mul_mat_q       : the GEMM; weights Q4_K / Q6_K / Q4_0, K % 256 == 0, 2-D, 16 B aligned rows */
+typedef struct b200_mmq_args {
+    b200_tensor w;        /* quantized [K, M] */
+    b200_tensor x;        /* f32 [K, N] (shape / validation; the kernel reads xb) */
+    b200_tensor dst;      /* f32 [M, N] */
+    const void * xb;      /* output of b200_mmq_convert_act for x */
+    int32_t act_fmt;      /* must match the conversion */
+    int32_t _pad;
+} b200_mmq_args;
+B200_API size_t b200_mmq_act_size(int64_t K, int64_t N);
+B200_API int    b200_mmq_supported(const b200_mmq_args * a);
+B200_API int    b200_mmq_convert_act(const b200_tensor * x, void * xb, int act_fmt, void * stream);
+B200_API int    b200_mul_mat_q(const b200_mmq_args * a, void * stream);
+
 /* ---- validation mode ------------------------------------------------------------------
  * Passing B200_STREAM_VALIDATE as `stream` to any op below makes it check its arguments and
  * return B200_OK / B200_ERR_UNSUPPORTED without touching the GPU.  The plugin's supports_op uses

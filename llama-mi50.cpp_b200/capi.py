@@ -27,6 +27,10 @@ class MmvqArgs(C.Structure):
                 ("col_begin", C.c_int32), ("col_count", C.c_int32)]
 
 
+class MmqArgs(C.Structure):
+    _fields_ = [("w", Tensor), ("x", Tensor), ("dst", Tensor), ("xb", C.c_void_p), ("act_fmt", C.c_int32), ("_pad", C.c_int32)]
+
+
 _lib = None
 
 
@@ -348,3 +352,27 @@ def gemv_phase(x, segs, **kw):
     ph.kind = PHASE_GEMV
     ph.gemv = gemv_fused_args(x, segs, **kw)
     return ph
+
+
+def mul_mat_q(w, wtype: int, K: int, M: int, x, dst, act_fmt: int = 1, xb=None):
+    """dst[N, M] (torch, ggml [M, N]) = W . x for x [N, K] f32 through the tensor-core prefill path.
+    Returns the converted activation buffer so callers can reuse it for matmuls sharing x."""
+    import torch
+    L = lib()
+    L.b200_mmq_act_size.restype = C.c_size_t
+    L.b200_mmq_act_size.argtypes = [C.c_int64, C.c_int64]
+    N = x.shape[0]
+    tx = from_torch(x)
+    if xb is None:
+        xb = torch.empty(L.b200_mmq_act_size(K, N) + 1024, dtype=torch.uint8, device=x.device)
+        off = (-xb.data_ptr()) % 1024
+        xb = xb[off:]
+        check(L.b200_mmq_convert_act(C.byref(tx), C.c_void_p(xb.data_ptr()), act_fmt, C.c_void_p(stream_ptr())), "mmq_convert_act")
+    a = MmqArgs()
+    a.w = make_tensor(w.data_ptr(), wtype, [K, M, 1, 1])
+    a.x = tx
+    a.dst = from_torch(dst)
+    a.xb = xb.data_ptr()
+    a.act_fmt = act_fmt
+    check(L.b200_mul_mat_q(C.byref(a), C.c_void_p(stream_ptr())), "mul_mat_q")
+    return xb

@@ -65,6 +65,7 @@ struct b200_context {
     // scratch arenas (stable addresses across CUDA-graph replays; growing one drops the graph cache)
     char * q8_scratch = nullptr; size_t q8_size = 0;      // q8_1 activations
     char * fa_scratch = nullptr; size_t fa_size = 0;      // flash-attn counters + partials
+    char * xb_scratch = nullptr; size_t xb_size = 0;      // 16-bit activation tiles of the tensor-core prefill GEMM
     b200_graph_cache * cache = nullptr;
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
     bool timing = false, ev_pending = false;

@@ -23,7 +23,10 @@ struct exec_state {
     // q8_1 activation cache: the quantized form of `q8_src` currently held in ctx->q8_scratch
     const ggml_tensor * q8_src = nullptr;
     const void * q8_src_data = nullptr;
-    size_t need_q8 = 0, need_fa = 0;   // scratch high-water marks found during the sizing pass
+    const ggml_tensor * xb_src = nullptr;     // same for the 16-bit activation tiles of the tensor-core GEMM
+    const void * xb_src_data = nullptr;
+    bool no_tc = env_flag("GGML_B200_DISABLE_TC");
+    size_t need_q8 = 0, need_fa = 0, need_xb = 0;   // scratch high-water marks found during the sizing pass
     bool sizing = false;               // sizing pass: compute need_*, launch nothing
     uint64_t launches = 0, chain_phases = 0;
 };
@@ -71,6 +74,26 @@ int run_mul_mat(exec_state & st, const ggml_tensor * dst, const ggml_tensor * bi
     a.glu_op = gate ? glu_op : B200_GLU_NONE; a.glu_alpha = alpha; a.glu_limit = limit;
 
     const int64_t ncols = ids ? 1 : x->ne[1];
+    // ---- prefill: more than 8 columns go to the tensor cores (reference router: ggml_cuda_mul_mat, ggml-cuda.cu:2183-2266)
+    if (!ids && !bias && !gate && ncols > 8 && !st.no_tc) {
+        b200_mmq_args m{};
+        m.w = b200_desc(w); m.x = b200_desc(x); m.dst = b200_desc(dst); m.act_fmt = 0;
+        if (b200_mmq_supported(&m)) {
+            if (st.validate) return B200_OK;
+            const size_t need = b200_mmq_act_size(x->ne[0], x->ne[1]) + 1024;
+            if (st.sizing) { st.need_xb = std::max(st.need_xb, need); return B200_OK; }
+            GGML_ASSERT(need <= st.ctx->xb_size);
+            char * xb = (char *) (((uintptr_t) st.ctx->xb_scratch + 1023) & ~(uintptr_t) 1023);
+            if (st.xb_src != x || st.xb_src_data != x->data) {      // q/k/v and gate/up share one conversion
+                B200_KCHECK(b200_mmq_convert_act(&m.x, xb, 0, st.stream));
+                st.xb_src = x; st.xb_src_data = x->data; st.launches++;
+            }
+            m.xb = xb;
+            B200_KCHECK(b200_mul_mat_q(&m, st.stream));
+            st.launches++;
+            return B200_OK;
+        }
+    }
     const int nwin = (int) ((ncols + 7) / 8);
     for (int wi = 0; wi < nwin; ++wi) {   // validate every window shape
         if (nwin > 1) { a.col_begin = wi * 8; a.col_count = (int) std::min<int64_t>(8, ncols - wi * 8); }
@@ -422,6 +445,7 @@ ggml_status b200_graph_compute(b200_context * ctx, ggml_cgraph * g) {
         walk(sz);
         grow(ctx, ctx->q8_scratch, ctx->q8_size, sz.need_q8, false);
         grow(ctx, ctx->fa_scratch, ctx->fa_size, sz.need_fa, true);
+        grow(ctx, ctx->xb_scratch, ctx->xb_size, sz.need_xb, false);
 
         // 3. run, capturing into a CUDA graph from the second identical submission on
         const bool capture = !no_graphs && c.seen >= 2;
@@ -453,6 +477,7 @@ void b200_context_free(b200_context * ctx) {
     if (ctx->cache) { if (ctx->cache->exec) cudaGraphExecDestroy(ctx->cache->exec); ctx->cache->drop_chains(); delete ctx->cache; }
     if (ctx->q8_scratch) cudaFree(ctx->q8_scratch);
     if (ctx->fa_scratch) cudaFree(ctx->fa_scratch);
+    if (ctx->xb_scratch) cudaFree(ctx->xb_scratch);
     if (ctx->ev_begin) cudaEventDestroy(ctx->ev_begin);
     if (ctx->ev_end) cudaEventDestroy(ctx->ev_end);
     cudaStreamDestroy(ctx->stream);
