@@ -254,20 +254,39 @@ def main_b200(a):
     e2e_cabi = N_GEN * a.steps / e2e_s
     h2d, d2h = 4 * N_GEN, shape.n_vocab * 4 * N_GEN
 
-    # ---- roofline of the dominant kernel: all GEMV launches of one token, alone
+    # ---- roofline of the dominant kernel
     hbm_peak, peak_src = peaks()
-    gemv_ms, gemv_n = sess.time_gemv_only(reps=max(20, a.steps * 4))
-    wbytes = sess.weight_bytes_local
-    achieved = wbytes / (gemv_ms / 1e3) / 1e9
     bpt = gguf_synth.decode_bytes_per_token(shape, n_ctx_avg=(N_GEN - 1) / 2.0)
-    roofline = {"bound": "hbm", "kernel": "quantized GEMV (b200_mul_mat_vec_q family), every GEMV launch of one token replayed alone",
-                "achieved": round(achieved, 1), "peak": hbm_peak, "unit": "GB/s", "frac": round(achieved / hbm_peak, 4),
-                "traffic": None, "peak_source": peak_src, "launches_per_token": gemv_n,
-                "bytes_per_launch_avg": int(wbytes / max(gemv_n, 1)), "us_per_launch_avg": round(gemv_ms * 1e3 / max(gemv_n, 1), 3),
-                "step": {"bytes_per_token": bpt["total"] // world if world > 1 else bpt["total"],
-                         "achieved": round(bpt["total"] / world * value / 1e9, 1),
-                         "frac": round(bpt["total"] / world * value / 1e9 / hbm_peak, 4),
-                         "frac_of_nominal_8000": round(bpt["total"] / world * value / 1e9 / 8000.0, 4)}}
+    wbytes = sess.weight_bytes_local
+    chain_mode = mode == "chain"
+    gemv_ms, gemv_n = sess.time_gemv_only(reps=max(20, a.steps * 4))       # one streaming-GEMV launch per matmul group, alone
+    gemv_alone = {"achieved": round(wbytes / (gemv_ms / 1e3) / 1e9, 1), "launches_per_token": gemv_n,
+                  "bytes_per_launch_avg": int(wbytes / max(gemv_n, 1)), "us_per_launch_avg": round(gemv_ms * 1e3 / max(gemv_n, 1), 3)}
+    traffic = None
+    try:   # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch from the committed ncu --set full capture (profiles/)
+        with open(os.path.join(ROOT, "profiles", "r01_chain_ncu_summary.json")) as f:
+            traffic = json.load(f).get("dram_bytes_per_launch") if chain_mode else None
+    except Exception:
+        traffic = None
+    if chain_mode:
+        # the whole token is ONE launch of the persistent chain kernel (plus a get_rows and a 644 B memset): its average
+        # duration over the timed region is ms_per_step / N_GEN (CUDA events on the launching stream, bracketing K steps)
+        us_launch = ms_per_step * 1e3 / N_GEN
+        alg = bpt["total"]
+        roofline = {"bound": "hbm", "kernel": "gemv_stream_kernel<CHAIN> (decode chain: every matmul, RoPE, KV write and attention of one token in one cooperative launch)",
+                    "achieved": round(alg / us_launch / 1e3, 1), "peak": hbm_peak, "unit": "GB/s", "frac": round(alg / us_launch / 1e3 / hbm_peak, 4),
+                    "traffic": traffic, "peak_source": peak_src, "launches_per_token": 1, "algorithmic_bytes_per_launch": alg,
+                    "us_per_launch_avg": round(us_launch, 2), "frac_of_nominal_8000": round(alg / us_launch / 1e3 / 8000.0, 4),
+                    "matmul_launches_alone": gemv_alone}
+    else:
+        roofline = {"bound": "hbm", "kernel": "quantized GEMV (gemv_stream_kernel / b200_mul_mat_vec_q family), every GEMV launch of one token replayed alone",
+                    "achieved": gemv_alone["achieved"], "peak": hbm_peak, "unit": "GB/s", "frac": round(gemv_alone["achieved"] / hbm_peak, 4),
+                    "traffic": traffic, "peak_source": peak_src, "launches_per_token": gemv_n,
+                    "bytes_per_launch_avg": gemv_alone["bytes_per_launch_avg"], "us_per_launch_avg": gemv_alone["us_per_launch_avg"],
+                    "step": {"bytes_per_token": bpt["total"] // world if world > 1 else bpt["total"],
+                             "achieved": round(bpt["total"] / world * value / 1e9, 1),
+                             "frac": round(bpt["total"] / world * value / 1e9 / hbm_peak, 4),
+                             "frac_of_nominal_8000": round(bpt["total"] / world * value / 1e9 / 8000.0, 4)}}
 
     line = {"metric": "llama-bench tg128 tok/s", "value": round(value, 2), "unit": "tok/s", "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": round(ms_per_step, 3), "higher_is_better": True, "scaling": "strong",
