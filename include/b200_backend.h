@@ -44,6 +44,7 @@ struct ggml_b200_stats {
     unsigned long long nodes_last_graph;  /* kernel nodes in the most recent graph */
     double device_ms_total;               /* sum of event-timed graph durations (GGML_B200_TIMING=1) */
     double device_ms_last;
+    double host_ms_total;                 /* wall time spent inside graph_compute (host side: keying, planning, launches) */
 };
 void ggml_backend_b200_get_stats(struct ggml_b200_stats * out);
 void ggml_backend_b200_reset_stats(void);

@@ -52,6 +52,7 @@ void                     b200_set_device(int id);
 
 // ---- buffer types (buffer.cpp)
 ggml_backend_buffer_type_t b200_buffer_type(int device);
+ggml_backend_buffer_type_t b200_host_buffer_type();   // pinned host memory (cudaMallocHost)
 bool                       b200_buft_is_b200(ggml_backend_buffer_type_t buft);
 bool                       b200_buft_is_split(ggml_backend_buffer_type_t buft);
 int                        b200_buft_device(ggml_backend_buffer_type_t buft);
@@ -89,8 +90,14 @@ struct b200_plan_item {
 struct b200_plan {
     std::vector<b200_plan_item> items;
     std::deque<b200_tensor>     pool;            // descriptors the phases point to (norm weights, biases, positions, masks)
-    int64_t                     scratch_floats = 0;
+    int64_t                     scratch_floats = 0;  // per-chain scratch of the attention blocks (raw q/k/v of the current layer)
+    // Phase outputs whose ggml buffer cannot be used (ggml-alloc gave them the memory of a tensor the phase still reads)
+    // and whose consumers are all chain phases live in a plan-private buffer instead.  The planner hands out addresses
+    // from a virtual range; the executor maps them onto the real allocation when it builds the chains.
+    int64_t                     redirect_bytes = 0;
 };
+#define B200_REDIRECT_VBASE ((uintptr_t) 0x7e0000000000ull)
+static inline bool b200_is_redirect(const void * p) { return (uintptr_t) p >= B200_REDIRECT_VBASE && (uintptr_t) p < B200_REDIRECT_VBASE + ((uintptr_t) 1 << 32); }
 void b200_plan_build(ggml_cgraph * g, b200_plan & plan);
 bool b200_gemv_fused_supported_rel(const b200_gemv_fused_args & a);
 

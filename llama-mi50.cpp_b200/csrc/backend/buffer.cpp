@@ -124,3 +124,35 @@ bool b200_buft_is_b200(ggml_backend_buffer_type_t buft) {
 int b200_buft_device(ggml_backend_buffer_type_t buft) {
     return buft && buft->iface.get_name == buft_name ? ((buft_ctx *) buft->context)->device : -1;
 }
+
+// ---------------------------------------------------------------- pinned host buffer type
+// Replaces ggml_backend_cuda_host_buffer_type (reference ggml-cuda.cu:1111-1176): libllama places the logits output buffer
+// and CPU-side tensors here, so the per-token logits D2H and the input H2D copies run at PCIe speed instead of being staged
+// through pageable memory.  The buffer behaves like a CPU buffer (ggml-base's ggml_backend_cpu_buffer_from_ptr) whose
+// memory is cudaMallocHost'ed; allocation failure falls back to the caller's default (nullptr).
+namespace {
+const char * host_buft_name(ggml_backend_buffer_type_t) { return "B200_Host"; }
+void host_buffer_free(ggml_backend_buffer_t buffer) { cudaFreeHost(buffer->context); }
+ggml_backend_buffer_t host_buft_alloc(ggml_backend_buffer_type_t buft, size_t size) {
+    if (getenv("GGML_B200_NO_PINNED")) return nullptr;
+    void * ptr = nullptr;
+    if (cudaMallocHost(&ptr, size ? size : 1) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    ggml_backend_buffer_t buffer = ggml_backend_cpu_buffer_from_ptr(ptr, size);
+    buffer->buft = buft;
+    buffer->iface.free_buffer = host_buffer_free;
+    return buffer;
+}
+size_t host_buft_alignment(ggml_backend_buffer_type_t) { return 64; }
+bool host_buft_is_host(ggml_backend_buffer_type_t) { return true; }
+}  // namespace
+
+ggml_backend_buffer_type_t b200_host_buffer_type() {
+    static ggml_backend_buffer_type type = {
+        /* iface   */ { host_buft_name, host_buft_alloc, host_buft_alignment, nullptr, nullptr, host_buft_is_host },
+        /* device  */ nullptr,
+        /* context */ nullptr,
+    };
+    static std::once_flag once;
+    std::call_once(once, [] { type.device = b200_dev(0); });
+    return &type;
+}

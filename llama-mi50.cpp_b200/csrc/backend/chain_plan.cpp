@@ -50,6 +50,40 @@ struct matcher {
     ggml_cgraph * g;
     b200_plan & plan;
     std::unordered_map<const ggml_tensor *, int> index;
+    std::unordered_map<const ggml_tensor *, void *> redirect;      // tensor -> plan-private (virtual) address
+    std::unordered_map<const ggml_tensor *, int> redirect_uses;
+    bool allow_redirect = true;
+
+    // descriptor of a tensor a phase READS: follows a redirect and counts the use
+    b200_tensor read_desc(const ggml_tensor * t) {
+        b200_tensor d = b200_desc(t);
+        auto it = redirect.find(t);
+        if (it != redirect.end()) d.data = it->second;
+        return d;
+    }
+    void * valloc(int64_t bytes) {
+        void * p = (void *) (B200_REDIRECT_VBASE + (uintptr_t) plan.redirect_bytes);
+        plan.redirect_bytes += (bytes + 255) & ~(int64_t) 255;
+        return p;
+    }
+    // every redirected tensor must be read by chain phases only: count the reads in the finished plan
+    bool redirects_ok() {
+        std::unordered_map<const void *, const ggml_tensor *> by_addr;
+        for (auto & kv : redirect) by_addr[kv.second] = kv.first;
+        redirect_uses.clear();
+        auto note = [&](const void * p) { auto it = by_addr.find(p); if (it != by_addr.end()) redirect_uses[it->second]++; };
+        for (const b200_plan_item & it : plan.items) {
+            if (it.kind != B200_ITEM_PHASE || it.phase.kind != B200_PHASE_GEMV) continue;
+            note(it.phase.gemv.x.data);
+            for (int s = 0; s < it.phase.gemv.n_seg; ++s) if (it.phase.gemv.seg[s].bias) note(it.phase.gemv.seg[s].bias->data);
+        }
+        for (auto & kv : redirect) {
+            const int i = idx(kv.first);
+            auto u = redirect_uses.find(kv.first);
+            if (i < 0 || is_output(kv.first) || ggml_node_get_use_count(g, i) != (u == redirect_uses.end() ? 0 : u->second)) return false;
+        }
+        return true;
+    }
 
     matcher(ggml_cgraph * g_, b200_plan & p) : g(g_), plan(p) {
         for (int i = 0; i < g->n_nodes; ++i) index[g->nodes[i]] = i;
@@ -83,7 +117,7 @@ struct matcher {
     }
 
     // [RMS_NORM, MUL(norm, w)] at i: fills x / norm_w / eps, returns the MUL node or null
-    const ggml_tensor * match_norm(int i, b200_gemv_fused_args & a) {
+    const ggml_tensor * match_norm(int i, b200_gemv_fused_args & a, bool allow_output = false) {
         if (i + 1 >= g->n_nodes) return nullptr;
         const ggml_tensor * rn = g->nodes[i]; const ggml_tensor * mul = g->nodes[i + 1];
         if (rn->op != GGML_OP_RMS_NORM || mul->op != GGML_OP_MUL) return nullptr;
@@ -92,8 +126,8 @@ struct matcher {
         if (!is_f32_vec(x, K) || !is_f32_vec(rn, K) || !is_f32_vec(mul, K)) return nullptr;
         const ggml_tensor * w = mul->src[0] == rn ? mul->src[1] : mul->src[1] == rn ? mul->src[0] : nullptr;
         if (!w || !is_f32_vec(w, K) || w->op != GGML_OP_NONE) return nullptr;
-        if (ggml_node_get_use_count(g, i) != 1 || is_output(rn) || is_output(mul)) return nullptr;
-        a.x = b200_desc(x);
+        if (ggml_node_get_use_count(g, i) != 1 || is_output(rn) || (is_output(mul) && !allow_output)) return nullptr;
+        a.x = read_desc(x);
         a.norm_w = keep(w);
         memcpy(&a.eps, rn->op_params, sizeof(float));
         return mul;
@@ -277,9 +311,13 @@ struct matcher {
     int match_norm_group(int i) {
         b200_phase ph{}; ph.kind = B200_PHASE_GEMV;
         b200_gemv_fused_args & a = ph.gemv;
-        const ggml_tensor * mul = match_norm(i, a);
+        // an OUTPUT-flagged norm (llama's result_norm) is still fused into the matmul phase; the norm itself is then
+        // materialised by a plain kernel AFTER the phase (it is computed in place over x, which the phase reads)
+        const ggml_tensor * mul = match_norm(i, a, true);
         if (!mul) return 0;
+        const bool defer_norm = is_output(mul);
         std::vector<int> members = {i, i + 1}, elided = {i, i + 1};
+        if (defer_norm) elided.clear();
         int j = i + 2;
         // gate / up / GLU
         if (j + 2 < g->n_nodes && single_column_mm(g->nodes[j]) && single_column_mm(g->nodes[j + 1]) && g->nodes[j + 2]->op == GGML_OP_GLU) {
@@ -322,8 +360,15 @@ struct matcher {
         if ((int) members.size() != last - i + 1) return 0;
         if (!uses_confined(members, elided)) return 0;
         if (!b200_gemv_fused_supported(&a)) return 0;
+        if (defer_norm) {
+            // nothing the phase writes may alias the deferred norm's output, and nobody but the phase may read it before
+            for (int s2 = 0; s2 < a.n_seg; ++s2)
+                if (overlap(a.seg[s2].dst.data, (size_t) a.seg[s2].dst.ne[0] * 4, mul->data, ggml_nbytes(mul))) return 0;
+            if (ggml_node_get_use_count(g, i + 1) != n_mm) return 0;
+        }
         b200_plan_item it{}; it.kind = B200_ITEM_PHASE; it.phase = ph; it.first_node = i;
         plan.items.push_back(it);
+        if (defer_norm) { b200_plan_item pn{}; pn.kind = B200_ITEM_NODE; pn.first_node = i; pn.n_nodes = 2; pn.hoisted = true; plan.items.push_back(pn); }
         return last - i + 1;
     }
 
@@ -333,7 +378,7 @@ struct matcher {
         if (!single_column_mm(mm)) return 0;
         b200_phase ph{}; ph.kind = B200_PHASE_GEMV;
         b200_gemv_fused_args & a = ph.gemv;
-        a.x = b200_desc(mm->src[1]); a.x.ne[1] = a.x.ne[2] = a.x.ne[3] = 1;
+        a.x = read_desc(mm->src[1]); a.x.ne[1] = a.x.ne[2] = a.x.ne[3] = 1;
         a.n_seg = 1; a.glu_op = B200_GLU_NONE;
         const int64_t M = mm->ne[0];
         const ggml_tensor * out = mm; const ggml_tensor * addend = nullptr;
@@ -368,12 +413,14 @@ struct matcher {
         const size_t xb = (size_t) a.x.ne[0] * 4, ob = (size_t) M * 4;
         // the residual may alias the output element for element (in-place ADD); any other overlap of what the phase
         // reads with what it writes is a hazard (ggml-alloc reuses dead buffers): fall back to the bare matmul
+        void * out_data = out->data;
         if (addend && (overlap(a.x.data, xb, out->data, ob) || (addend->data != out->data && overlap(addend->data, ob, out->data, ob)))) {
-            out = mm; addend = nullptr; consumed = 1;
+            if (allow_redirect) { out_data = valloc((int64_t) ob); redirect[out] = out_data; }     // readers are checked at the end of the plan
+            else { out = mm; addend = nullptr; consumed = 1; out_data = out->data; }
         }
-        a.seg[0].dst = vec_desc(out->data, M);
-        a.seg[0].bias = addend ? keep(addend) : nullptr;
-        if (overlap(a.x.data, xb, out->data, ob)) return 0;
+        a.seg[0].dst = vec_desc(out_data, M);
+        if (addend) { plan.pool.push_back(read_desc(addend)); a.seg[0].bias = &plan.pool.back(); }
+        if (overlap(a.x.data, xb, out_data, ob)) return 0;
         if (!b200_gemv_fused_supported(&a)) return 0;
         b200_plan_item it{}; it.kind = B200_ITEM_PHASE; it.phase = ph; it.first_node = i;
         plan.items.push_back(it);
@@ -391,9 +438,10 @@ bool b200_gemv_fused_supported_rel(const b200_gemv_fused_args & a) {
     return b200_gemv_fused_supported(&t) != 0;
 }
 
-void b200_plan_build(ggml_cgraph * g, b200_plan & plan) {
-    plan.items.clear(); plan.pool.clear(); plan.scratch_floats = 0;
+static bool plan_build_once(ggml_cgraph * g, b200_plan & plan, bool allow_redirect) {
+    plan.items.clear(); plan.pool.clear(); plan.scratch_floats = 0; plan.redirect_bytes = 0;
     matcher m(g, plan);
+    m.allow_redirect = allow_redirect;
     for (int i = 0; i < g->n_nodes;) {
         ggml_tensor * n = g->nodes[i];
         if (ggml_is_empty(n) || (n->flags & GGML_TENSOR_FLAG_COMPUTE) == 0) { ++i; continue; }
@@ -405,4 +453,16 @@ void b200_plan_build(ggml_cgraph * g, b200_plan & plan) {
         plan.items.push_back(it);
         ++i;
     }
+    const bool ok = m.redirects_ok();
+    if (getenv("B200_PLAN_DEBUG")) {
+        for (auto & kv : m.redirect) {
+            auto u = m.redirect_uses.find(kv.first);
+            fprintf(stderr, "plan: redirected %s uses %d phase-reads %d output %d\n", kv.first->name, m.uses(kv.first), u == m.redirect_uses.end() ? 0 : u->second, (int) m.is_output(kv.first));
+        }
+    }
+    return ok;
+}
+
+void b200_plan_build(ggml_cgraph * g, b200_plan & plan) {
+    if (!plan_build_once(g, plan, true)) plan_build_once(g, plan, false);      // a redirected tensor has a reader outside the chains
 }

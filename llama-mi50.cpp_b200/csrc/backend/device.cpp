@@ -126,7 +126,7 @@ void dev_props(ggml_backend_dev_t d, ggml_backend_dev_props * p) {
     p->name = info.name.c_str(); p->description = info.description.c_str(); p->type = GGML_BACKEND_DEVICE_TYPE_GPU;
     p->device_id = info.pci_bus_id.c_str();
     dev_memory(d, &p->memory_free, &p->memory_total);
-    p->caps = { /* async */ true, /* host_buffer */ false, /* buffer_from_host_ptr */ false, /* events */ true };
+    p->caps = { /* async */ true, /* host_buffer */ true, /* buffer_from_host_ptr */ false, /* events */ true };
 }
 ggml_backend_t dev_init_backend(ggml_backend_dev_t d, const char *) {
     const int device = ((dev_ctx *) d->context)->device;
@@ -140,6 +140,7 @@ ggml_backend_t dev_init_backend(ggml_backend_dev_t d, const char *) {
     return new ggml_backend{ backend_guid(), kBackendIface, d, c };
 }
 ggml_backend_buffer_type_t dev_buft(ggml_backend_dev_t d) { return b200_buffer_type(((dev_ctx *) d->context)->device); }
+ggml_backend_buffer_type_t dev_host_buft(ggml_backend_dev_t) { return b200_host_buffer_type(); }
 bool dev_supports_op(ggml_backend_dev_t d, const ggml_tensor * op) { return b200_supports_op(((dev_ctx *) d->context)->device, op); }
 bool dev_supports_buft(ggml_backend_dev_t d, ggml_backend_buffer_type_t buft) {
     if (b200_buft_is_split(buft)) return true;
@@ -163,7 +164,7 @@ const ggml_backend_device_i kDevIface = {
     /* get_props            */ dev_props,
     /* init_backend         */ dev_init_backend,
     /* get_buffer_type      */ dev_buft,
-    /* get_host_buffer_type */ nullptr,
+    /* get_host_buffer_type */ dev_host_buft,
     /* buffer_from_host_ptr */ nullptr,
     /* supports_op          */ dev_supports_op,
     /* supports_buft        */ dev_supports_buft,

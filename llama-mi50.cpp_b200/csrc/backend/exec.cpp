@@ -9,6 +9,7 @@
 //   * kernels are chained with programmatic dependent launch inside one captured CUDA graph.
 #include "b200_plugin.h"
 
+#include <chrono>
 #include <cmath>
 #include <cstring>
 
@@ -239,6 +240,18 @@ void make_key(const ggml_tensor * n, node_key & k) {
     memcpy(k.op_params, n->op_params, sizeof(k.op_params));
 }
 
+// the per-token check (a graph is resubmitted unchanged ~1000 nodes x every token): field compares, no copies
+bool key_matches(const ggml_tensor * n, const node_key & k) {
+    if (k.node != n || k.data != n->data || k.op != (int) n->op || k.flags != n->flags) return false;
+    for (int i = 0; i < 4; ++i) if (k.ne[i] != n->ne[i] || k.nb[i] != n->nb[i]) return false;
+    for (int i = 0; i < GGML_MAX_SRC; ++i) {
+        const ggml_tensor * s = n->src[i];
+        if (k.src[i] != s) return false;
+        if (s && k.src_data[i] != s->data) return false;
+    }
+    return memcmp(k.op_params, n->op_params, sizeof(k.op_params)) == 0;
+}
+
 }  // namespace
 
 struct b200_chain_entry { b200_chain * chain = nullptr; float * scratch = nullptr; int n_phases = 0; };
@@ -247,9 +260,11 @@ struct b200_graph_cache {
     b200_plan plan;                    // the graph `keys` describes, compiled into chain phases + plain nodes
     bool plan_built = false;
     std::vector<b200_chain_entry> chains;
+    char * redirect_buf = nullptr;     // plan-private tensors (b200_plan::redirect_bytes)
     void drop_chains() {
         for (b200_chain_entry & e : chains) { b200_chain_destroy(e.chain); if (e.scratch) cudaFree(e.scratch); }
         chains.clear(); plan_built = false;
+        if (redirect_buf) { cudaFree(redirect_buf); redirect_buf = nullptr; }
     }
     std::vector<node_key> keys;        // properties of the graph last seen
     cudaGraphExec_t exec = nullptr;    // instantiated capture of `keys` (or null)
@@ -345,8 +360,19 @@ void flush_chain(exec_state & st, b200_graph_cache & c, std::vector<b200_plan_it
             b200_chain_entry e;
             if (c.plan.scratch_floats > 0) B200_CUDA_CHECK(cudaMalloc((void **) &e.scratch, (size_t) c.plan.scratch_floats * sizeof(float)));
             std::vector<b200_phase> ph;
+            std::deque<b200_tensor> fixed;                     // biases whose data pointer is a plan-private address
+            auto fix = [&](void *& p) { if (b200_is_redirect(p)) p = c.redirect_buf + ((uintptr_t) p - B200_REDIRECT_VBASE); };
             for (b200_plan_item * it : pending) {
                 b200_phase p = it->phase;
+                if (p.kind == B200_PHASE_GEMV) {
+                    fix(p.gemv.x.data);
+                    for (int s = 0; s < p.gemv.n_seg; ++s) {
+                        fix(p.gemv.seg[s].dst.data);
+                        if (p.gemv.seg[s].bias && b200_is_redirect(p.gemv.seg[s].bias->data)) {
+                            fixed.push_back(*p.gemv.seg[s].bias); fix(fixed.back().data); p.gemv.seg[s].bias = &fixed.back();
+                        }
+                    }
+                }
                 if (it->scratch_rel) {
                     char * base = (char *) e.scratch;
                     if (p.kind == B200_PHASE_GEMV) { for (int s = 0; s < p.gemv.n_seg; ++s) p.gemv.seg[s].dst.data = base + (intptr_t) p.gemv.seg[s].dst.data; }
@@ -374,7 +400,11 @@ void walk_plan(exec_state & st, ggml_cgraph * g, b200_graph_cache & c, bool fusi
     for (size_t k = 0; k < items.size(); ++k) {
         b200_plan_item & it = items[k];
         if (it.kind == B200_ITEM_PHASE) { pending.push_back(&it); continue; }
-        if (it.hoisted) { flush_chain(st, c, pending, seq); run_fused(st, g, it.first_node, false, it.first_node + 1); continue; }
+        if (it.hoisted) {      // runs alone, out of index order (n_nodes > 1: a fusable run such as RMS_NORM + MUL)
+            flush_chain(st, c, pending, seq);
+            for (int n0 = it.first_node, n1 = it.first_node + std::max(it.n_nodes, 1); n0 < n1;) n0 += run_fused(st, g, n0, it.n_nodes > 1, n1);
+            continue;
+        }
         if (it.first_node < next_node) continue;                  // consumed by a fusion of the previous plain node
         flush_chain(st, c, pending, seq);
         int limit = g->n_nodes;                                   // plain-node fusions stop where the next phase begins
@@ -410,6 +440,7 @@ void b200_timing_collect(b200_context * ctx) {
 }
 
 ggml_status b200_graph_compute(b200_context * ctx, ggml_cgraph * g) {
+    const auto t_host0 = std::chrono::steady_clock::now();
     b200_set_device(ctx->device);
     static const bool no_graphs = env_flag("GGML_B200_DISABLE_GRAPHS"), no_fusion = env_flag("GGML_B200_DISABLE_FUSION");
     static const bool no_chain = env_flag("GGML_B200_DISABLE_CHAIN") || no_fusion;
@@ -417,11 +448,12 @@ ggml_status b200_graph_compute(b200_context * ctx, ggml_cgraph * g) {
     b200_graph_cache & c = *ctx->cache;
 
     // 1. has this exact graph been submitted before?
-    std::vector<node_key> keys((size_t) g->n_nodes);
-    for (int i = 0; i < g->n_nodes; ++i) make_key(g->nodes[i], keys[i]);
-    const bool same = keys.size() == c.keys.size() && (keys.empty() || memcmp(keys.data(), c.keys.data(), keys.size() * sizeof(node_key)) == 0);
+    bool same = (size_t) g->n_nodes == c.keys.size();
+    for (int i = 0; same && i < g->n_nodes; ++i) same = key_matches(g->nodes[i], c.keys[(size_t) i]);
     if (!same) {
-        c.keys.swap(keys); c.seen = 0;
+        c.keys.resize((size_t) g->n_nodes);
+        for (int i = 0; i < g->n_nodes; ++i) make_key(g->nodes[i], c.keys[(size_t) i]);
+        c.seen = 0;
         if (c.exec) { cudaGraphExecDestroy(c.exec); c.exec = nullptr; }
         if (!c.chains.empty()) B200_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));   // a chain of the previous graph may still be running
         c.drop_chains();
@@ -439,7 +471,21 @@ ggml_status b200_graph_compute(b200_context * ctx, ggml_cgraph * g) {
         launched = c.kernels; replay = true;
     } else {
         // 2. size the scratch arenas (no launches)
-        if (!no_chain && !c.plan_built) { b200_plan_build(g, c.plan); c.plan_built = true; }
+        if (!no_chain && !c.plan_built) {
+            b200_plan_build(g, c.plan); c.plan_built = true;
+            if (env_flag("GGML_B200_PRINT_PLAN")) {
+                int phases = 0, chains = 0, plain = 0; bool in_chain = false;
+                for (const b200_plan_item & it : c.plan.items) {
+                    if (it.kind == B200_ITEM_PHASE) { ++phases; if (!in_chain) { ++chains; in_chain = true; } continue; }
+                    const ggml_tensor * n = g->nodes[it.first_node];
+                    if (n->op == GGML_OP_NONE || n->op == GGML_OP_VIEW || n->op == GGML_OP_RESHAPE || n->op == GGML_OP_PERMUTE || n->op == GGML_OP_TRANSPOSE) continue;
+                    in_chain = false; ++plain;
+                    fprintf(stderr, "ggml-b200 plan: plain node %d %s %s [%lld,%lld,%lld]\n", it.first_node, ggml_op_name(n->op), n->name, (long long) n->ne[0], (long long) n->ne[1], (long long) n->ne[2]);
+                }
+                fprintf(stderr, "ggml-b200 plan: %d nodes -> %d phases in %d chains, %d plain compute nodes, redirect %lld B\n", g->n_nodes, phases, chains, plain, (long long) c.plan.redirect_bytes);
+            }
+            if (c.plan.redirect_bytes > 0) B200_CUDA_CHECK(cudaMalloc((void **) &c.redirect_buf, (size_t) c.plan.redirect_bytes));
+        }
         auto walk = [&](exec_state & s) { if (no_chain) walk_graph(s, g, !no_fusion); else walk_plan(s, g, c, true); };
         exec_state sz; sz.ctx = ctx; sz.validate = false; sz.sizing = true;
         walk(sz);
@@ -467,6 +513,7 @@ ggml_status b200_graph_compute(b200_context * ctx, ggml_cgraph * g) {
         std::lock_guard<std::mutex> lock(b200_stats().mu);
         ggml_b200_stats & s = b200_stats().s;
         s.graphs_computed++; s.graphs_replayed += replay; s.kernels_launched += launched; s.nodes_last_graph = launched;
+        s.host_ms_total += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_host0).count();
     }
     return GGML_STATUS_SUCCESS;
 }
@@ -474,6 +521,13 @@ ggml_status b200_graph_compute(b200_context * ctx, ggml_cgraph * g) {
 void b200_context_free(b200_context * ctx) {
     b200_set_device(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    if (env_flag("GGML_B200_PRINT_STATS")) {
+        b200_timing_collect(ctx);
+        std::lock_guard<std::mutex> lock(b200_stats().mu);
+        const ggml_b200_stats & s = b200_stats().s;
+        fprintf(stderr, "ggml-b200 stats: graphs %llu (replayed %llu), kernel launches %llu, host ms in graph_compute %.2f (%.1f us/graph), device ms %.2f\n",
+                s.graphs_computed, s.graphs_replayed, s.kernels_launched, s.host_ms_total, s.graphs_computed ? 1e3 * s.host_ms_total / s.graphs_computed : 0.0, s.device_ms_total);
+    }
     if (ctx->cache) { if (ctx->cache->exec) cudaGraphExecDestroy(ctx->cache->exec); ctx->cache->drop_chains(); delete ctx->cache; }
     if (ctx->q8_scratch) cudaFree(ctx->q8_scratch);
     if (ctx->fa_scratch) cudaFree(ctx->fa_scratch);
