@@ -18,7 +18,7 @@ import os
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 REPO_ROOT = os.path.dirname(PKG_DIR)
-KERNELS_SO = os.path.join(PKG_DIR, "libb200_kernels.so")
+KERNELS_SO = os.environ.get("B200_KERNELS_SO") or os.path.join(PKG_DIR, "libb200_kernels.so")   # override: A/B runs of kernel builds (tools/)
 BACKEND_SO = os.path.join(PKG_DIR, "libggml-b200.so")
 REF_DIR = os.path.join(REPO_ROOT, "oracle", "_ref")   # unmodified reference host build (harness only)
 

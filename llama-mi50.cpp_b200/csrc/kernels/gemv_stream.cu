@@ -51,8 +51,6 @@ struct gs_seg {
     int32_t M, rb, type, nsub;     // rows, row bytes, ggml type, 1 (or 2 for a GLU pair)
     int32_t R, KS, spr, ipr;       // rows per chunk, warps along K, steps per row, items per row
     int32_t spw, _pad;             // K-steps per warp (1, 2 or 4): the per-step activation registers are hoisted
-    unsigned long long *       dst_ll;    // chain: tagged copy of dst ({f32 bits, launch tag} per element), or null
-    const unsigned long long * bias_ll;   // chain: tagged copy of bias when an earlier phase of the launch produced it
 };
 // attention phase of the decode chain: one query position, f16 KV cache, RoPE + KV-cache write fused in
 struct gs_attn {
@@ -62,8 +60,6 @@ struct gs_attn {
     int64_t k_nb1, k_nb2, v_nb1, v_nb2;
     int32_t D, H, H_kv, n_kv, rope_mode, n_dims;
     float scale, theta_scale, freq_scale;
-    const unsigned long long * q_ll; const unsigned long long * k_ll; const unsigned long long * v_ll;   // tagged copies (or null)
-    unsigned long long * dst_ll;
 };
 struct alignas(16) gs_phase {
     int32_t kind;                  // 0 = GEMV, 1 = attention
@@ -74,12 +70,6 @@ struct alignas(16) gs_phase {
     blk_q8_1 * xq_out;
     int64_t total_bytes;
     gs_attn attn;
-    const unsigned long long * x_ll;   // chain: tagged copy of x; the prologue spins on the tags instead of a grid barrier
-    int32_t wait_bar;                  // chain: wait for every CTA to have finished the previous phase (plain reads follow)
-    int32_t publish;                   // chain: a later phase waits on this phase's arrival counter
-    int32_t next_wait;                 // wait_bar of the NEXT phase (known before that phase's descriptor is staged)
-    int32_t next_K;                    // K and norm weights of the NEXT phase: prefetched into L2 a phase ahead
-    const float * next_norm_w;
 };
 struct gs_params {
     gs_phase inl;                  // the phase of a single-phase launch (b200_gemv_fused)
@@ -92,7 +82,6 @@ struct gs_params {
     int32_t attn_floats;           // attention scratch (floats) after the activation scales
     int32_t flags;                 // tuning/debug: bit 0 = consumers skip the dot products (bandwidth probe)
     unsigned long long * dbg;      // flags bit 2: globaltimer stamps [phase][cta 0 | last cta][4]
-    unsigned int * epoch;          // chain: launch counter = the tag of this launch's tagged activations
 };
 
 // ---------------------------------------------------------------- PTX helpers
@@ -125,35 +114,6 @@ __device__ __forceinline__ uint64_t policy_evict_first() {
     return p;
 }
 __device__ __forceinline__ void named_bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
-
-// ---- tagged activations: a value and the tag of the launch that wrote it travel in ONE 64-bit word, so a reader that
-// sees the tag has the value — no fence, no counter, no second round trip (the idea of NCCL's LL protocol).
-__device__ __forceinline__ void ll_store(unsigned long long * p, float v, unsigned int tag) {
-    const unsigned long long w = (unsigned long long) __float_as_uint(v) | ((unsigned long long) tag << 32);
-    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
-}
-__device__ __forceinline__ unsigned long long ll_load1(const unsigned long long * p) {
-    unsigned long long w;
-    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
-    return w;
-}
-__device__ __forceinline__ ulonglong2 ll_load2(const unsigned long long * p) {      // two elements, 16 B aligned
-    ulonglong2 r;
-    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(r.x), "=l"(r.y) : "l"(p) : "memory");
-    return r;
-}
-__device__ __forceinline__ bool ll_ok(unsigned long long w, unsigned int tag) { return (unsigned int) (w >> 32) == tag; }
-// bounded spins: a protocol error traps instead of hanging the GPU
-__device__ __forceinline__ float ll_read(const unsigned long long * p, unsigned int tag) {
-    unsigned long long w = ll_load1(p);
-    unsigned int spins = 0;
-    while (!ll_ok(w, tag)) { if (++spins > (1u << 22)) __trap(); w = ll_load1(p); }
-    return __uint_as_float((unsigned int) w);
-}
-__device__ __forceinline__ void ll_settle2(ulonglong2 & a, const unsigned long long * p, unsigned int tag) {
-    unsigned int spins = 0;
-    while (!ll_ok(a.x, tag) || !ll_ok(a.y, tag)) { if (++spins > (1u << 22)) __trap(); a = ll_load2(p); }
-}
 
 // N consecutive little-endian u32 words starting at an arbitrarily aligned shared-memory byte address
 template <int N>
@@ -401,7 +361,6 @@ struct gs_shared {
 struct gs_ctx {                    // per-thread view of the launch-wide shared memory carve-up
     uint8_t * ring; uint8_t * aq; float2 * ads; float * attn; gs_shared * sh;
     int stage_stride, flags;
-    unsigned int tag;              // chain: this launch's tag
 };
 
 __device__ __forceinline__ void gs_row_range(const gs_seg & sg, int64_t lo, int64_t hi, int & r0, int & r1) {
@@ -427,7 +386,6 @@ __device__ __forceinline__ void consume_segment(const gs_ctx & c, const gs_phase
                                                            // chunk shorter than a CTA pass does not leave the same warps idle
     const float * __restrict__ bias = sg.bias;
     float * __restrict__ dst = sg.dst;
-    const unsigned long long * bias_ll = sg.bias_ll; unsigned long long * dst_ll = sg.dst_ll;
     const int glu_op = ph.glu_op; const float glu_alpha = ph.glu_alpha, glu_limit = ph.glu_limit;
     uint32_t ga0 = (uint32_t) ((uintptr_t) (sg.w[0] + (int64_t) r0 * rb) & 15);
     uint32_t ga1 = pair ? (uint32_t) ((uintptr_t) (sg.w[1] + (int64_t) r0 * rb) & 15) : 0u;
@@ -452,8 +410,7 @@ __device__ __forceinline__ void consume_segment(const gs_ctx & c, const gs_phase
 #pragma unroll
             for (int j = 0; j < GS_RB; ++j) {
                 bv[j] = 0.0f;
-                if (bias && ks == 0 && lane == 0 && j < rpp && jb + j < nr)
-                    bv[j] = (COHERENT && bias_ll) ? ll_read(bias_ll + row + jb + j, c.tag) : COHERENT ? __ldcg(bias + row + jb + j) : bias[row + jb + j];
+                if (bias && ks == 0 && lane == 0 && j < rpp && jb + j < nr) bv[j] = COHERENT ? __ldcg(bias + row + jb + j) : bias[row + jb + j];
             }
             float acc[GS_RB];
 #pragma unroll
@@ -483,17 +440,11 @@ __device__ __forceinline__ void consume_segment(const gs_ctx & c, const gs_phase
             }
             if (ks == 0 && lane == 0) {
                 if (pair) {
-                    const float v = gs_glu(glu_op, acc[0], acc[1], glu_alpha, glu_limit) + bv[0];
-                    dst[row + jb] = v;
-                    if (COHERENT && dst_ll) ll_store(dst_ll + row + jb, v, c.tag);
+                    dst[row + jb] = gs_glu(glu_op, acc[0], acc[1], glu_alpha, glu_limit) + bv[0];
                 } else {
 #pragma unroll
                     for (int j = 0; j < GS_RB; ++j)
-                        if (j < rpp && jb + j < nr) {
-                            const float v = acc[j] + bv[j];
-                            dst[row + jb + j] = v;
-                            if (COHERENT && dst_ll) ll_store(dst_ll + row + jb + j, v, c.tag);
-                        }
+                        if (j < rpp && jb + j < nr) dst[row + jb + j] = acc[j] + bv[j];
                 }
             }
         }
@@ -559,35 +510,13 @@ __device__ __forceinline__ void gs_prologue(const gs_ctx & c, const gs_phase & p
     if (nblk <= BPP * NV) {
         // ---- all loads first (one L2 round trip), values stay in registers for both passes
         float4 xv[NV], wv[NV];
-        const unsigned long long * xl = COHERENT ? ph.x_ll : nullptr;      // tagged copy: spin on the tags, no grid barrier before
 #pragma unroll
         for (int it = 0; it < NV; ++it) {
             const int blk = pw * 4 + bw + it * BPP;
             xv[it] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); wv[it] = xv[it];
             if (blk < nblk) {
-                if (!xl) xv[it] = gs_ld4<COHERENT>(x + blk * 32 + sub * 4);
+                xv[it] = gs_ld4<COHERENT>(x + blk * 32 + sub * 4);
                 if (nw) wv[it] = *(const float4 *) (nw + blk * 32 + sub * 4);
-            }
-        }
-        if (xl) {
-#pragma unroll
-            for (int it0 = 0; it0 < NV; it0 += 2) {                        // two passes (four 16 B loads) in flight per thread
-                ulonglong2 a[2], b[2];
-#pragma unroll
-                for (int u = 0; u < 2; ++u) {
-                    const int blk = pw * 4 + bw + (it0 + u) * BPP;
-                    a[u] = make_ulonglong2(0, 0); b[u] = a[u];
-                    if (blk < nblk) { a[u] = ll_load2(xl + blk * 32 + sub * 4); b[u] = ll_load2(xl + blk * 32 + sub * 4 + 2); }
-                }
-#pragma unroll
-                for (int u = 0; u < 2; ++u) {
-                    const int blk = pw * 4 + bw + (it0 + u) * BPP;
-                    if (blk < nblk) {
-                        ll_settle2(a[u], xl + blk * 32 + sub * 4, c.tag); ll_settle2(b[u], xl + blk * 32 + sub * 4 + 2, c.tag);
-                        xv[it0 + u] = make_float4(__uint_as_float((unsigned int) a[u].x), __uint_as_float((unsigned int) a[u].y),
-                                                  __uint_as_float((unsigned int) b[u].x), __uint_as_float((unsigned int) b[u].y));
-                    }
-                }
             }
         }
         float scale = 1.0f;
@@ -643,7 +572,7 @@ __device__ __forceinline__ void gs_prologue(const gs_ctx & c, const gs_phase & p
 // from the raw projections (RoPE applied, rounded to f16 exactly as the cache stores them) and written to the cache by
 // the first query head of each KV group; all other positions are read from the cache.
 template <int D>
-__device__ __forceinline__ void gs_attn_item(const gs_attn & a, int h, float * sm, int warp, int lane, unsigned int tag) {
+__device__ __forceinline__ void gs_attn_item(const gs_attn & a, int h, float * sm, int warp, int lane) {
     constexpr int LPP = D / 32, PPB = 32 / LPP, DPL = D / 32;     // lanes per position, positions per batch, dims per lane (V)
     const int tid = warp * 32 + lane;
     const int gqa = a.H / a.H_kv, g = h / gqa;
@@ -656,25 +585,24 @@ __device__ __forceinline__ void gs_attn_item(const gs_attn & a, int h, float * s
             const bool isk = tid >= D / 2;
             const int i = isk ? tid - D / 2 : tid;
             const float * src = isk ? a.k_new + (int64_t) g * D : a.q + (int64_t) h * D;
-            const unsigned long long * sll = isk ? (a.k_ll ? a.k_ll + (int64_t) g * D : nullptr) : (a.q_ll ? a.q_ll + (int64_t) h * D : nullptr);
             float * dst = isk ? s_k : s_q;
             if (i < half_d) {
                 const int i0 = a.rope_mode == 2 ? i : 2 * i, i1 = a.rope_mode == 2 ? i + half_d : 2 * i + 1;
                 const float theta = (float) pos * powf(a.theta_scale, (float) i) * a.freq_scale;
                 float sn, cs; sincosf(theta, &sn, &cs);
-                const float x0 = sll ? ll_read(sll + i0, tag) : __ldcg(src + i0), x1 = sll ? ll_read(sll + i1, tag) : __ldcg(src + i1);
+                const float x0 = __ldcg(src + i0), x1 = __ldcg(src + i1);
                 float y0 = x0 * cs - x1 * sn, y1 = x0 * sn + x1 * cs;
                 if (isk) { y0 = __half2float(__float2half_rn(y0)); y1 = __half2float(__float2half_rn(y1)); }
                 else     { y0 *= a.scale; y1 *= a.scale; }
                 dst[i0] = y0; dst[i1] = y1;
             }
             for (int d = a.n_dims + i; d < D; d += D / 2) {       // dims beyond n_dims pass through
-                const float y = sll ? ll_read(sll + d, tag) : __ldcg(src + d);
+                const float y = __ldcg(src + d);
                 dst[d] = isk ? __half2float(__float2half_rn(y)) : y * a.scale;
             }
         } else if (tid < 2 * D) {
             const int d = tid - D;
-            s_v[d] = __half2float(__float2half_rn(a.v_ll ? ll_read(a.v_ll + (int64_t) g * D + d, tag) : __ldcg(a.v_new + (int64_t) g * D + d)));
+            s_v[d] = __half2float(__float2half_rn(__ldcg(a.v_new + (int64_t) g * D + d)));
         }
     }
     named_bar_sync(3, GS_CON_THREADS);
@@ -765,7 +693,6 @@ __device__ __forceinline__ void gs_attn_item(const gs_attn & a, int h, float * s
             A += wgt * s_part[w * (D + 2) + tid]; L += wgt * s_part[w * (D + 2) + D + 1];
         }
         a.dst[(int64_t) h * D + tid] = A / L;
-        if (a.dst_ll) ll_store(a.dst_ll + (int64_t) h * D + tid, A / L, tag);
     }
     named_bar_sync(3, GS_CON_THREADS);                            // scratch is reused by the next item
 }
@@ -801,7 +728,6 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
     c.ads  = (float2 *) (c.aq + p.act_qs_bytes);                              // (d, d*sum) per unit; sized with act_qs_bytes/4
     c.attn = (float *) ((uint8_t *) c.ads + (p.act_qs_bytes >> 2) + 64);      // attention scratch
     c.sh = &sh; c.stage_stride = p.stage_stride; c.flags = p.flags;
-    c.tag = (CHAIN && p.epoch) ? __ldcg(p.epoch) : 0u;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
@@ -857,35 +783,22 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
     }
 
     // ================= consumers (warps 0..GS_NW-1)
-    int wait_next = 0;
-    uint4 next_desc = make_uint4(0, 0, 0, 0);
     for (int ip = 0; ip < n_phases; ++ip) {
         const gs_phase & ph = s_ph[ip & 1];
-        // the descriptor was staged while the previous phase ran (below); only the first one is fetched here
-        if (ip == 0) for (int i = tid; i < PH_VEC; i += GS_CON_THREADS) ((uint4 *) &s_ph[0])[i] = ((const uint4 *) phases)[i];
+        // static data: staged (and the norm weights requested into L2) before the dependency wait
+        for (int i = tid; i < PH_VEC; i += GS_CON_THREADS) ((uint4 *) &s_ph[ip & 1])[i] = ((const uint4 *) (phases + ip))[i];
         // ---- dependency: everything this phase reads was produced by the previous phase (or earlier kernels)
         if (ip == 0) {
             pdl_wait();
-        } else if (tid == 0 && wait_next) {
-            unsigned int spins = 0;
+        } else if (tid == 0) {
+            unsigned int spins = 0;                            // bounded: a protocol error traps instead of hanging the GPU
             while (ld_acquire_gpu(p.bar + ip - 1) < gridDim.x) { if (++spins > (1u << 24)) __trap(); }
         }
-        named_bar_sync(1, GS_CON_THREADS);                      // also: every warp has left the previous phase's activations
-        wait_next = ph.next_wait;
+        named_bar_sync(1, GS_CON_THREADS);
         if (CHAIN && tid == 0) GS_STAMP(ip, 0);
-        if (CHAIN && ip + 1 < n_phases) {
-            // stage the NEXT descriptor now (its buffer held phase ip-1, which every warp has left) and pull the next
-            // phase's norm weights into L2: both are static, and fetching them at the top of the next phase would put an
-            // L2 round trip (descriptor) and an HBM miss (norm weights: evicted by 4.6 GB of streamed weights per token)
-            // on every phase's critical path
-            static_assert(PH_VEC <= GS_CON_THREADS, "one uint4 of the descriptor per thread");
-            if (tid < PH_VEC) next_desc = __ldg((const uint4 *) (phases + ip + 1) + tid);     // stored after this phase's prologue
-            if (ph.next_norm_w && tid * 32 < ph.next_K) asm volatile("prefetch.global.L2 [%0];" ::"l"(ph.next_norm_w + tid * 32));
-        }
         if (ph.kind == 0) {
             gs_prologue<CHAIN>(c, ph, warp, lane);
             if (CHAIN && tid == 0) GS_STAMP(ip, 1);
-            if (CHAIN && ip + 1 < n_phases && tid < PH_VEC) ((uint4 *) &s_ph[(ip + 1) & 1])[tid] = next_desc;
             const int64_t lo = ph.total_bytes * (int64_t) blockIdx.x / gridDim.x, hi = ph.total_bytes * (int64_t) (blockIdx.x + 1) / gridDim.x;
             for (int s = 0; s < ph.n_ws; ++s) {
                 const gs_seg & sg = ph.seg[s];
@@ -895,24 +808,19 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
                 else               consume_dispatch<T1, CHAIN>(c, ph, sg, r0, r1, pos, warp, lane);
             }
         } else if (CHAIN) {
-            if (ip + 1 < n_phases && tid < PH_VEC) ((uint4 *) &s_ph[(ip + 1) & 1])[tid] = next_desc;
             for (int h = blockIdx.x; h < ph.attn.H; h += gridDim.x) {
-                if (ph.attn.D == 128) gs_attn_item<128>(ph.attn, h, c.attn, warp, lane, c.tag);
-                else                  gs_attn_item<64>(ph.attn, h, c.attn, warp, lane, c.tag);
+                if (ph.attn.D == 128) gs_attn_item<128>(ph.attn, h, c.attn, warp, lane);
+                else                  gs_attn_item<64>(ph.attn, h, c.attn, warp, lane);
             }
         }
         if (CHAIN) {
             if (tid == 0) GS_STAMP(ip, 2);
             // ---- publish: this CTA's stores of the phase are visible device-wide, then count it in
-            if (ph.publish) {
-                __threadfence();
-                named_bar_sync(1, GS_CON_THREADS);
-                if (tid == 0) { GS_STAMP(ip, 4); atomicAdd(p.bar + ip, 1u); GS_STAMP(ip, 3); }
-            } else if (tid == 0) { GS_STAMP(ip, 4); GS_STAMP(ip, 3); }
+            __threadfence();
+            named_bar_sync(1, GS_CON_THREADS);
+            if (tid == 0) { GS_STAMP(ip, 4); atomicAdd(p.bar + ip, 1u); GS_STAMP(ip, 3); }
         }
     }
-    // the next launch uses the next tag (every CTA that produces or consumes anything has read this one long ago)
-    if (CHAIN && p.epoch && blockIdx.x == 0 && tid == 0) *p.epoch = c.tag + 1u;
 }
 
 // ---------------------------------------------------------------- host side
@@ -1112,9 +1020,6 @@ struct b200_chain {
     unsigned int * d_bar = nullptr;
     int n_gemv = 0, n_attn = 0;
     unsigned long long * d_dbg = nullptr;
-    unsigned long long * d_ll = nullptr;      // tagged copies of every phase output
-    unsigned int * d_epoch = nullptr;
-    int n_ll_phases = 0;
 };
 
 static bool gs_build_attn(const b200_attn_phase * a, gs_phase & ph, int & attn_floats) {
@@ -1165,66 +1070,6 @@ extern "C" b200_chain * b200_chain_create(const b200_phase * phases, int n_phase
     for (int i = 0; i < n_phases; ++i)
         if (ph[i].kind == 0 && !gs_finish_phase(ph[i], cfg.stage_payload)) { set_error("b200_chain_create: phase %d: row does not fit a stage", i); delete ch; return nullptr; }
     cudaGetDevice(&ch->device);
-    // ---- dependencies between phases.  Every phase output gets a tagged copy ({value, launch tag} per element, private to
-    // the phase: no reuse inside a launch, so the tag alone tells "written by this launch").  A phase whose inputs all
-    // come from tagged copies spins on the tags in its prologue; otherwise (long activations: the tagged copy would double
-    // the L2 traffic of a 57 KB broadcast; inputs only partially produced in the chain) it waits on the arrival counter of
-    // the previous phase, which then has to publish (fence + atomic).  flags bit 3: counters everywhere (A/B, fallback).
-    {
-        const bool use_ll = !(flags & 8);
-        struct out_t { const char * p; int64_t n; int64_t off; };
-        std::vector<std::vector<out_t>> outs((size_t) n_phases);
-        int64_t total = 0;
-        for (int i = 0; i < n_phases; ++i) {
-            if (ph[i].kind == 0) { for (int s2 = 0; s2 < ph[i].n_ws; ++s2) { outs[i].push_back({(const char *) ph[i].seg[s2].dst, ph[i].seg[s2].M, total}); total += (ph[i].seg[s2].M + 1) & ~(int64_t) 1; } }
-            else { const int64_t n = (int64_t) ph[i].attn.D * ph[i].attn.H; outs[i].push_back({(const char *) ph[i].attn.dst, n, total}); total += (n + 1) & ~(int64_t) 1; }
-        }
-        if (use_ll && total > 0) {
-            if (cudaMalloc((void **) &ch->d_ll, (size_t) total * 8) != cudaSuccess || cudaMemset(ch->d_ll, 0, (size_t) total * 8) != cudaSuccess ||
-                cudaMalloc((void **) &ch->d_epoch, 4) != cudaSuccess) {
-                set_error("b200_chain_create: device allocation failed"); cudaGetLastError();
-                if (ch->d_ll) cudaFree(ch->d_ll); if (ch->d_epoch) cudaFree(ch->d_epoch); delete ch; return nullptr;
-            }
-            const unsigned int one = 1;
-            cudaMemcpy(ch->d_epoch, &one, 4, cudaMemcpyHostToDevice);
-        }
-        // 1 = inside one earlier output (tagged copy returned), -1 = overlaps earlier outputs some other way, 0 = external
-        auto find = [&](const void * ptr, int64_t n, int i, const unsigned long long *& ll) -> int {
-            ll = nullptr;
-            const char * a = (const char *) ptr; const char * b = a + n * 4;
-            for (int j = i - 1; j >= 0; --j)
-                for (const out_t & o : outs[j]) {
-                    const char * oa = o.p; const char * ob = o.p + o.n * 4;
-                    if (a >= oa && b <= ob) { if (ch->d_ll) ll = ch->d_ll + o.off + (a - oa) / 4; return 1; }
-                    if (a < ob && oa < b) return -1;
-                }
-            return 0;
-        };
-        for (int i = 0; i < n_phases; ++i) {
-            gs_phase & P = ph[i];
-            bool need_bar = false;
-            const unsigned long long * ll;
-            if (P.kind == 0) {
-                const int rx = find(P.x, P.K, i, ll);
-                if (rx == 1 && use_ll && P.K <= 8192 && ((uintptr_t) ll % 16) == 0) P.x_ll = ll; else if (rx != 0) need_bar = true;
-                for (int s2 = 0; s2 < P.n_ws; ++s2) {
-                    gs_seg & g = P.seg[s2];
-                    if (g.bias) { const int rb2 = find(g.bias, g.M, i, ll); if (rb2 == 1 && use_ll) g.bias_ll = ll; else if (rb2 != 0) need_bar = true; }
-                    if (use_ll && ch->d_ll) g.dst_ll = ch->d_ll + outs[i][(size_t) s2].off;
-                }
-            } else {
-                gs_attn & A = P.attn;
-                const int64_t nq = (int64_t) A.D * A.H, nk = (int64_t) A.D * A.H_kv;
-                const int r0 = find(A.q, nq, i, ll); if (r0 == 1 && use_ll) A.q_ll = ll; else if (r0 != 0) need_bar = true;
-                const int r1 = find(A.k_new, nk, i, ll); if (r1 == 1 && use_ll) A.k_ll = ll; else if (r1 != 0) need_bar = true;
-                const int r2 = find(A.v_new, nk, i, ll); if (r2 == 1 && use_ll) A.v_ll = ll; else if (r2 != 0) need_bar = true;
-                if (use_ll && ch->d_ll) A.dst_ll = ch->d_ll + outs[i][0].off;
-            }
-            if (i + 1 < n_phases && ph[i + 1].kind == 0) { P.next_K = ph[i + 1].K; P.next_norm_w = ph[i + 1].norm_w; }
-            P.wait_bar = (i > 0 && need_bar) ? 1 : 0;
-            if (P.wait_bar) { ph[i - 1].publish = 1; ph[i - 1].next_wait = 1; ch->n_ll_phases += 0; } else if (i > 0) ch->n_ll_phases++;
-        }
-    }
     if (cudaMalloc((void **) &ch->d_phases, sizeof(gs_phase) * (size_t) n_phases) != cudaSuccess ||
         cudaMalloc((void **) &ch->d_bar, sizeof(unsigned int) * (size_t) n_phases) != cudaSuccess ||
         cudaMemcpy(ch->d_phases, ph.data(), sizeof(gs_phase) * (size_t) n_phases, cudaMemcpyHostToDevice) != cudaSuccess) {
@@ -1235,7 +1080,7 @@ extern "C" b200_chain * b200_chain_create(const b200_phase * phases, int n_phase
     memset(&ch->p, 0, sizeof(ch->p));
     ch->p.phases = ch->d_phases; ch->p.bar = ch->d_bar; ch->p.n_phases = n_phases;
     ch->p.act_qs_bytes = cfg.act_qs; ch->p.stage_stride = cfg.stage_payload + GS_STAGE_SLACK; ch->p.n_stages = cfg.n_stages;
-    ch->p.attn_floats = cfg.attn_floats; ch->p.flags = flags; ch->p.epoch = ch->d_epoch;
+    ch->p.attn_floats = cfg.attn_floats; ch->p.flags = flags;
     if (flags & 4) {
         if (cudaMalloc((void **) &ch->d_dbg, sizeof(unsigned long long) * 16 * (size_t) n_phases) == cudaSuccess)
             cudaMemset(ch->d_dbg, 0, sizeof(unsigned long long) * 16 * (size_t) n_phases);
@@ -1262,6 +1107,5 @@ extern "C" int b200_chain_debug_read(b200_chain * ch, unsigned long long * out, 
 extern "C" void b200_chain_destroy(b200_chain * ch) {
     if (!ch) return;
     cudaFree(ch->d_phases); cudaFree(ch->d_bar); if (ch->d_dbg) cudaFree(ch->d_dbg);
-    if (ch->d_ll) cudaFree(ch->d_ll); if (ch->d_epoch) cudaFree(ch->d_epoch);
     delete ch;
 }
