@@ -185,8 +185,10 @@ def main_b200(a):
     if world > 1:
         from llama_mi50_b200.rowsplit import make_gather
         gather = make_gather(dist, world, rank)
-    mode = {"chain": "chain", "fused": True, "basic": False}[a.mode if world == 1 or a.mode != "chain" else "fused"]
-    sess = DecodeSession(shape, n_ctx=n_ctx, rank=rank, world=world, gather=gather, fused=mode)
+    # N > 1: the chain runs row-split over NVLink peer memory (outputs stored into every rank's buffers by the GEMV
+    # epilogue, barriers spanning the ranks); --rowsplit nccl keeps one launch + one all-gather per matmul group
+    mode = {"chain": "chain", "fused": True, "basic": False}[a.mode if world == 1 or a.mode != "chain" or a.rowsplit == "peer" else "fused"]
+    sess = DecodeSession(shape, n_ctx=n_ctx, rank=rank, world=world, gather=gather, fused=mode, peer_dist=dist if world > 1 else None)
     sess.chain_flags = a.chain_flags
     sess.capture(sess.n_kv_for(N_GEN - 1))
     lib = capi.lib()
@@ -272,7 +274,8 @@ def main_b200(a):
         # the whole token is ONE launch of the persistent chain kernel (plus a get_rows and a 644 B memset): its average
         # duration over the timed region is ms_per_step / N_GEN (CUDA events on the launching stream, bracketing K steps)
         us_launch = ms_per_step * 1e3 / N_GEN
-        alg = bpt["total"]
+        # N > 1: this rank's row slices of the weights; the KV cache, embedding row and logits are per rank (replicated attention)
+        alg = bpt["total"] if world == 1 else wbytes + bpt["total"] - bpt["weights"]
         roofline = {"bound": "hbm", "kernel": "gemv_stream_kernel<CHAIN> (decode chain: every matmul, RoPE, KV write and attention of one token in one cooperative launch)",
                     "achieved": round(alg / us_launch / 1e3, 1), "peak": hbm_peak, "unit": "GB/s", "frac": round(alg / us_launch / 1e3 / hbm_peak, 4),
                     "traffic": traffic, "peak_source": peak_src, "launches_per_token": 1, "algorithmic_bytes_per_launch": alg,
@@ -292,7 +295,8 @@ def main_b200(a):
             "warmup": a.warmup, "ms_per_step": round(ms_per_step, 3), "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "int8 x int4/6 dp4a, f32 accumulate", "data": "synthetic",
             "config": {"workload": key, "n_gen": N_GEN, "n_kv": n_ctx, "kv_type": "f16", "flash_attn": 1,
-                       "parallelism": f"row-split tp{world}" if world > 1 else "single GPU", "issue": a.mode,
+                       "parallelism": (f"row-split tp{world}, " + ("decode chain over NVLink peer memory (no collective)" if mode == "chain" else "NCCL all-gather per matmul"))
+                                      if world > 1 else "single GPU", "issue": a.mode,
                        "l2": "inputs larger than L2 (weights %.2f GB per token vs 126 MB L2)" % (wbytes / 1e9)},
             "roofline": roofline, "clocks": clocks, "gpu_launches": gpu_launches,
             "e2e": {"value": round(e2e_cabi, 2), "unit": "tok/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -344,6 +348,8 @@ if __name__ == "__main__":
     ap.add_argument("--mode", default="chain", choices=["chain", "fused", "basic"],
                     help="chain: one cooperative launch per token; fused: one streaming-GEMV launch per matmul group; basic: unfused ops")
     ap.add_argument("--chain-flags", type=lambda x: int(x, 0), default=0)
+    ap.add_argument("--rowsplit", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: peer = decode chain with peer-memory stores; nccl = per-matmul launches + all-gather")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     sys.exit(main_reference(args) if args.impl == "reference" else main_b200(args))

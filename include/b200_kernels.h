@@ -138,7 +138,8 @@ typedef struct b200_rope_params {
  * barriers which only the consuming warps wait on, while the producer warp keeps streaming the next
  * phase's weights, so HBM does not drain at matmul boundaries (the reference pays one launch + one
  * quantize launch per matmul).  All pointers are captured at create time. */
-enum b200_phase_kind { B200_PHASE_GEMV = 0, B200_PHASE_ATTN = 1 };
+enum b200_phase_kind { B200_PHASE_GEMV = 0, B200_PHASE_ATTN = 1,
+                       B200_PHASE_NOP = 2 /* nothing to compute (a rank that owns no rows of a matrix); takes part in the barrier */ };
 typedef struct b200_attn_phase {
     b200_tensor q, k_new, v_new;     /* f32 raw projections of the current token: [D*H], [D*H_kv], [D*H_kv] */
     b200_tensor k_cache, v_cache;    /* f16 [D, n_kv, H_kv] views of the layer's cache (nb[1] = position stride) */
@@ -162,6 +163,37 @@ B200_API int          b200_chain_launch(b200_chain * chain, void * stream);
 B200_API void         b200_chain_destroy(b200_chain * chain);
 /* flags bit 2 at create time: per-phase globaltimer stamps of the first and last CTA (tools/timeline_chain.py) */
 B200_API int          b200_chain_debug_read(b200_chain * chain, unsigned long long * out, int n_phases);
+
+/* ---- row split across GPUs: the decode chain over NVLink peer memory --------------------------------
+ * Replaces the reference's row-split matmul (ggml-cuda.cu:791-804 get_row_split, :1497-1700 ggml_cuda_op_mul_mat:
+ * per matmul, the main device quantizes the activation, copies it to every device, each device runs its row slice,
+ * and the slices are copied back behind events).  Here one process per GPU runs the SAME chain over its own row
+ * slices (each rank passes its slice of every weight, bias and dst); the GEMV epilogue stores every output value into
+ * the activation buffers of ALL ranks (plain peer stores over NVLink), and the in-kernel barrier between phases counts
+ * the CTAs of all ranks (system-scope reductions on every rank's counter).  No collective, no extra launch: the
+ * exchange is part of the matmul.  Attention phases are computed by every rank (replicated KV cache).
+ *
+ * Requirements: every rank allocates a "symmetric arena" of the same size with the same layout (b200_peer_alloc),
+ * maps the arenas of the others (b200_peer_export / b200_peer_open) and passes delta[r] = arena of rank r - own arena
+ * (as mapped in this process).  Every GEMV dst and the barrier counters `sync` (>= n_phases u32, zero before the first
+ * launch of any rank) must lie inside the arena.  All ranks create the same list of phases (kinds in the same order)
+ * and launch the chain the same number of times. */
+#define B200_MAX_RANKS 8
+typedef struct b200_peer_group {
+    int32_t rank, n_ranks;
+    int32_t total_ctas;              /* sum over ranks of the SM count (the grid of the chain on that rank) */
+    int32_t _pad;
+    void *  arena; size_t arena_bytes;
+    int64_t delta[B200_MAX_RANKS];   /* bytes; delta[rank] == 0 */
+    unsigned int * sync;
+} b200_peer_group;
+B200_API b200_chain * b200_chain_create_peer(const b200_phase * phases, int n_phases, int flags, const b200_peer_group * pg);
+B200_API int  b200_chain_grid(void);                                       /* CTAs the chain uses on the current device */
+B200_API int  b200_peer_alloc(size_t bytes, void ** ptr);                  /* zero-filled device memory suitable for export */
+B200_API int  b200_peer_free(void * ptr);
+B200_API int  b200_peer_export(void * ptr, unsigned char handle[64]);      /* handle: send to the other processes */
+B200_API int  b200_peer_open(const unsigned char handle[64], void ** ptr); /* maps another rank's arena (enables peer access) */
+B200_API int  b200_peer_close(void * ptr);
 
 /* ---- K5: prefill GEMM on the tensor cores (tcgen05 + TMEM) ------------------------------------------
  * dst[M, N] = W[M, K] . x[K, N] for N > 8 columns.  Replaces ggml_cuda_mul_mat_q (reference ggml-cuda/mmq.cu:71-218,

@@ -316,22 +316,99 @@ class Phase(C.Structure):
     _fields_ = [("kind", C.c_int32), ("_pad", C.c_int32), ("gemv", GemvFusedArgs), ("attn", AttnPhase)]
 
 
-PHASE_GEMV, PHASE_ATTN = 0, 1
+PHASE_GEMV, PHASE_ATTN, PHASE_NOP = 0, 1, 2
+MAX_RANKS = 8
+
+
+class PeerGroup(C.Structure):
+    """b200_peer_group (include/b200_kernels.h)."""
+    _fields_ = [("rank", C.c_int32), ("n_ranks", C.c_int32), ("total_ctas", C.c_int32), ("_pad", C.c_int32),
+                ("arena", C.c_void_p), ("arena_bytes", C.c_size_t), ("delta", C.c_int64 * MAX_RANKS), ("sync", C.c_void_p)]
+
+
+class _RawCuda:
+    """Device memory not owned by torch, presented through __cuda_array_interface__."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+class PeerArena:
+    """Symmetric activation arena of the row-split decode chain: the same allocation, with the same layout, on every
+    rank; each rank maps the arenas of the others over CUDA IPC (NVLink peer access).  `dist` is an initialised
+    torch.distributed (plumbing: it only carries the 64-byte handles and a barrier)."""
+
+    def __init__(self, nbytes: int, dist, rank: int, world: int, device):
+        import torch
+        L = lib()
+        vp = C.c_void_p
+        L.b200_peer_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
+        L.b200_peer_export.argtypes = [vp, C.c_char_p]
+        L.b200_peer_open.argtypes = [C.c_char_p, C.POINTER(vp)]
+        L.b200_peer_close.argtypes = [vp]
+        L.b200_peer_free.argtypes = [vp]
+        assert 1 <= world <= MAX_RANKS
+        self.rank, self.world, self.nbytes, self.dist = rank, world, nbytes, dist
+        base = vp()
+        check(L.b200_peer_alloc(nbytes, C.byref(base)), "peer_alloc")
+        self.base = base.value
+        handle = C.create_string_buffer(64)
+        check(L.b200_peer_export(self.base, handle), "peer_export")
+        handles, grids = [None] * world, [None] * world
+        dist.all_gather_object(handles, bytes(handle.raw))
+        dist.all_gather_object(grids, int(L.b200_chain_grid()))
+        self.total_ctas = sum(grids)
+        self.delta, self.mapped = [0] * MAX_RANKS, []
+        for r in range(world):
+            if r == rank:
+                continue
+            p = vp()
+            check(L.b200_peer_open(handles[r], C.byref(p)), f"peer_open(rank {r})")
+            self.mapped.append(p.value)
+            self.delta[r] = p.value - self.base
+        self.bytes_t = torch.as_tensor(_RawCuda(self.base, nbytes), device=device)
+        assert self.bytes_t.data_ptr() == self.base
+        self.off = 0
+        dist.barrier()               # every arena is zeroed and mapped before any rank can write to it
+
+    def carve(self, n: int, dtype):
+        """n elements of `dtype`, 256-byte aligned, at the same offset on every rank (same call sequence)."""
+        import torch
+        size = n * torch.empty((), dtype=dtype).element_size()
+        off = (self.off + 255) & ~255
+        assert off + size <= self.nbytes, "peer arena exhausted"
+        self.off = off + size
+        return self.bytes_t[off:off + size].view(dtype)
+
+    def group(self, sync) -> PeerGroup:
+        g = PeerGroup()
+        g.rank, g.n_ranks, g.total_ctas = self.rank, self.world, self.total_ctas
+        g.arena, g.arena_bytes = self.base, self.nbytes
+        for r in range(MAX_RANKS):
+            g.delta[r] = self.delta[r]
+        g.sync = sync.data_ptr()
+        return g
 
 
 class Chain:
-    """Owns a b200_chain (device-side phase descriptors). launch() is capturable into a CUDA graph."""
+    """Owns a b200_chain (device-side phase descriptors). launch() is capturable into a CUDA graph.
+    `peer`: a PeerGroup — the chain runs row-split over peer memory (b200_chain_create_peer)."""
 
-    def __init__(self, phases, flags=0, keep=None):
+    def __init__(self, phases, flags=0, keep=None, peer=None):
         L = lib()
         L.b200_chain_create.restype = C.c_void_p
         L.b200_chain_create.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.b200_chain_create_peer.restype = C.c_void_p
+        L.b200_chain_create_peer.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.b200_chain_launch.argtypes = [C.c_void_p, C.c_void_p]
         L.b200_chain_destroy.argtypes = [C.c_void_p]
         arr = (Phase * len(phases))(*phases)
-        self._keep = (arr, keep)
+        self._keep = (arr, keep, peer)
         self.n = len(phases)
-        self.h = L.b200_chain_create(arr, len(phases), flags)
+        if peer is not None:
+            self.h = L.b200_chain_create_peer(arr, len(phases), flags, C.byref(peer))
+        else:
+            self.h = L.b200_chain_create(arr, len(phases), flags)
         if not self.h:
             raise RuntimeError("b200_chain_create: " + L.b200_last_error().decode())
 
@@ -345,6 +422,12 @@ class Chain:
                 self.h = None
         except Exception:
             pass
+
+
+def nop_phase():
+    ph = Phase()
+    ph.kind = PHASE_NOP
+    return ph
 
 
 def gemv_phase(x, segs, **kw):

@@ -82,6 +82,11 @@ struct gs_params {
     int32_t attn_floats;           // attention scratch (floats) after the activation scales
     int32_t flags;                 // tuning/debug: bit 0 = consumers skip the dot products (bandwidth probe)
     unsigned long long * dbg;      // flags bit 2: globaltimer stamps [phase][cta 0 | last cta][4]
+    // ---- row split over peer memory (MODE 2): outputs and barrier arrivals are mirrored to the other ranks
+    int32_t n_peers;               // other ranks
+    int32_t total_ctas;            // CTAs of all ranks: arrivals per phase and launch
+    int64_t peer_delta[B200_MAX_RANKS - 1];   // byte offset from a local arena address to the same location on peer r
+    unsigned int * epoch;          // launches completed so far on this rank (the counters are never reset)
 };
 
 // ---------------------------------------------------------------- PTX helpers
@@ -356,6 +361,7 @@ struct gs_shared {
     uint64_t full[GS_MAX_STAGES], empty[GS_MAX_STAGES];
     float part[GS_NW];
     float slots[2][GS_NW][GS_RB];  // per-warp row sums of a pass, combined across the KS warps of a row group
+    unsigned int target;           // value a phase counter reaches when every CTA (of every rank) has arrived
 };
 
 struct gs_ctx {                    // per-thread view of the launch-wide shared memory carve-up
@@ -372,8 +378,19 @@ __device__ __forceinline__ void gs_row_range(const gs_seg & sg, int64_t lo, int6
 // consumer warps: all chunks of one work segment.  A pass of a warp covers GS_RB rows (for a GLU pair: the gate row and the
 // up row of ONE output row); the KS warps of a row group each own a K slice, reduce their lanes by shuffles and meet at a
 // named barrier of their own; warp ks == 0 sums the KS values in fixed order, applies the epilogue and stores.
-template <int TYPE, int SPW, bool COHERENT>
-__device__ __forceinline__ void consume_segment(const gs_ctx & c, const gs_phase & ph, const gs_seg & sg, int r0, int r1, gs_pos & pos, int warp, int lane) {
+// one output value: the local store and, under row split, the same store into every peer's copy of the buffer
+template <bool PEER>
+__device__ __forceinline__ void gs_put(const gs_params & p, float * d, float v) {
+    *d = v;
+    if (PEER) {
+#pragma unroll
+        for (int r = 0; r < B200_MAX_RANKS - 1; ++r)
+            if (r < p.n_peers) *(float *) ((char *) d + p.peer_delta[r]) = v;
+    }
+}
+
+template <int TYPE, int SPW, bool COHERENT, bool PEER>
+__device__ __forceinline__ void consume_segment(const gs_params & p, const gs_ctx & c, const gs_phase & ph, const gs_seg & sg, int r0, int r1, gs_pos & pos, int warp, int lane) {
     const int KS = sg.KS, ksl = 31 - __clz(KS), ks = warp & (KS - 1), rg = warp >> ksl, RG = GS_NW >> ksl;
     item<TYPE> itm[SPW];
 #pragma unroll
@@ -440,11 +457,11 @@ __device__ __forceinline__ void consume_segment(const gs_ctx & c, const gs_phase
             }
             if (ks == 0 && lane == 0) {
                 if (pair) {
-                    dst[row + jb] = gs_glu(glu_op, acc[0], acc[1], glu_alpha, glu_limit) + bv[0];
+                    gs_put<PEER>(p, dst + row + jb, gs_glu(glu_op, acc[0], acc[1], glu_alpha, glu_limit) + bv[0]);
                 } else {
 #pragma unroll
                     for (int j = 0; j < GS_RB; ++j)
-                        if (j < rpp && jb + j < nr) dst[row + jb + j] = acc[j] + bv[j];
+                        if (j < rpp && jb + j < nr) gs_put<PEER>(p, dst + row + jb + j, acc[j] + bv[j]);
                 }
             }
         }
@@ -455,12 +472,12 @@ __device__ __forceinline__ void consume_segment(const gs_ctx & c, const gs_phase
     }
 }
 
-template <int TYPE, bool COHERENT>
-__device__ __forceinline__ void consume_dispatch(const gs_ctx & c, const gs_phase & ph, const gs_seg & sg, int r0, int r1, gs_pos & pos, int warp, int lane) {
-    if (sg.spw == 1)      consume_segment<TYPE, 1, COHERENT>(c, ph, sg, r0, r1, pos, warp, lane);
-    else if (sg.spw == 2) consume_segment<TYPE, 2, COHERENT>(c, ph, sg, r0, r1, pos, warp, lane);
+template <int TYPE, bool COHERENT, bool PEER>
+__device__ __forceinline__ void consume_dispatch(const gs_params & p, const gs_ctx & c, const gs_phase & ph, const gs_seg & sg, int r0, int r1, gs_pos & pos, int warp, int lane) {
+    if (sg.spw == 1)      consume_segment<TYPE, 1, COHERENT, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
+    else if (sg.spw == 2) consume_segment<TYPE, 2, COHERENT, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
     else if (item<TYPE>::max_spw >= 4)
-        consume_segment<TYPE, (item<TYPE>::max_spw >= 4 ? 4 : 1), COHERENT>(c, ph, sg, r0, r1, pos, warp, lane);
+        consume_segment<TYPE, (item<TYPE>::max_spw >= 4 ? 4 : 1), COHERENT, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
 }
 
 // ---------------------------------------------------------------- phase pieces
@@ -712,10 +729,34 @@ __device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int * p) {
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int * p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// thread 0 of a CTA: wait until counter `bar` has seen every arrival of this launch.  Bounded by wall time: a rank
+// that never arrives (crashed process, mismatched phase lists) becomes a trap, not a hung GPU.
+template <bool PEER>
+__device__ __forceinline__ void gs_wait_counter(const unsigned int * bar, unsigned int target) {
+    if (!PEER) {
+        unsigned int spins = 0;
+        while (ld_acquire_gpu(bar) < target) { if (++spins > (1u << 24)) __trap(); }
+    } else {
+        unsigned int spins = 0; unsigned long long t0 = 0;
+        while ((int) (ld_acquire_sys(bar) - target) < 0) {
+            if ((++spins & 0xFFFu) == 0) {
+                const unsigned long long now = gs_now();
+                if (!t0) t0 = now; else if (now - t0 > 20000000000ull) __trap();      // 20 s
+            }
+        }
+    }
+}
 
 // ---------------------------------------------------------------- the kernel
-template <int T0, int T1, bool CHAIN>
+// MODE 0: one phase (b200_gemv_fused, PDL); 1: decode chain on one GPU; 2: decode chain, row split over peer memory
+template <int T0, int T1, int MODE>
 __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid_constant__ gs_params p) {
+    constexpr bool CHAIN = MODE >= 1, PEER = MODE == 2;
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ gs_shared sh;
     // phase descriptors are staged in shared memory: read from global inside the chunk loops they cost an L2 round
@@ -732,6 +773,8 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
         for (int s = 0; s < p.n_stages; ++s) { mbar_init(&sh.full[s], 1); mbar_init(&sh.empty[s], GS_NW); }
+        // PEER: the counters are shared with the other ranks and never reset; arrivals accumulate over launches
+        sh.target = PEER ? (__ldcg(p.epoch) + 1u) * (unsigned int) p.total_ctas : gridDim.x;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -791,8 +834,7 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
         if (ip == 0) {
             pdl_wait();
         } else if (tid == 0) {
-            unsigned int spins = 0;                            // bounded: a protocol error traps instead of hanging the GPU
-            while (ld_acquire_gpu(p.bar + ip - 1) < gridDim.x) { if (++spins > (1u << 24)) __trap(); }
+            gs_wait_counter<PEER>(p.bar + ip - 1, PEER ? sh.target : gridDim.x);
         }
         named_bar_sync(1, GS_CON_THREADS);
         if (CHAIN && tid == 0) GS_STAMP(ip, 0);
@@ -804,10 +846,10 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
                 const gs_seg & sg = ph.seg[s];
                 int r0, r1; gs_row_range(sg, lo, hi, r0, r1);
                 if (r0 >= r1) continue;
-                if (sg.type == T0) consume_dispatch<T0, CHAIN>(c, ph, sg, r0, r1, pos, warp, lane);
-                else               consume_dispatch<T1, CHAIN>(c, ph, sg, r0, r1, pos, warp, lane);
+                if (sg.type == T0) consume_dispatch<T0, CHAIN, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
+                else               consume_dispatch<T1, CHAIN, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
             }
-        } else if (CHAIN) {
+        } else if (CHAIN && ph.kind == 1) {
             for (int h = blockIdx.x; h < ph.attn.H; h += gridDim.x) {
                 if (ph.attn.D == 128) gs_attn_item<128>(ph.attn, h, c.attn, warp, lane);
                 else                  gs_attn_item<64>(ph.attn, h, c.attn, warp, lane);
@@ -816,10 +858,26 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
         if (CHAIN) {
             if (tid == 0) GS_STAMP(ip, 2);
             // ---- publish: this CTA's stores of the phase are visible device-wide, then count it in
-            __threadfence();
+            if (PEER) __threadfence_system(); else __threadfence();
             named_bar_sync(1, GS_CON_THREADS);
-            if (tid == 0) { GS_STAMP(ip, 4); atomicAdd(p.bar + ip, 1u); GS_STAMP(ip, 3); }
+            if (tid == 0) {
+                GS_STAMP(ip, 4);
+                atomicAdd(p.bar + ip, 1u);
+                if (PEER) {
+#pragma unroll
+                    for (int r = 0; r < B200_MAX_RANKS - 1; ++r)
+                        if (r < p.n_peers) atomicAdd_system((unsigned int *) ((char *) (p.bar + ip) + p.peer_delta[r]), 1u);
+                }
+                GS_STAMP(ip, 3);
+            }
         }
+    }
+    if (PEER && blockIdx.x == 0 && tid == 0) {
+        // the launch ends only when every rank has delivered its rows of the last phase (the logits) into this rank's
+        // buffers; then the launch is counted.  No CTA of this launch reads the epoch after its first instructions,
+        // and no CTA of the next launch starts before this one has exited (same stream).
+        gs_wait_counter<true>(p.bar + n_phases - 1, sh.target);
+        *p.epoch = __ldcg(p.epoch) + 1u;
     }
 }
 
@@ -927,14 +985,15 @@ static bool gs_make_config(int flags, int64_t need, int act_qs, int attn_floats,
     return true;
 }
 
-template <int T0, int T1, bool CHAIN>
+template <int T0, int T1, int MODE>
 static int gs_launch(const gs_params & p, size_t smem, int grid, cudaStream_t st) {
+    constexpr bool CHAIN = MODE >= 1;
     static bool attr_set[64] = {};
     int dev = 0;
     B200_CUDA_TRY(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64) return B200_ERR_ARG;
     if (!attr_set[dev]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(gemv_stream_kernel<T0, T1, CHAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, GS_SMEM_MAX));
+        B200_CUDA_TRY(cudaFuncSetAttribute(gemv_stream_kernel<T0, T1, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, GS_SMEM_MAX));
         attr_set[dev] = true;
     }
     cudaLaunchConfig_t cfg{};
@@ -943,28 +1002,28 @@ static int gs_launch(const gs_params & p, size_t smem, int grid, cudaStream_t st
     if (CHAIN) { at[0].id = cudaLaunchAttributeCooperative; at[0].val.cooperative = 1; }     // all CTAs co-resident: the grid barriers need it
     else       { at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[0].val.programmaticStreamSerializationAllowed = 1; }
     cfg.attrs = at; cfg.numAttrs = 1;
-    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, gemv_stream_kernel<T0, T1, CHAIN>, p));
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, gemv_stream_kernel<T0, T1, MODE>, p));
     count_launch();
     return B200_OK;
 }
 
-template <bool CHAIN>
+template <int MODE>
 static int gs_launch_types(const gs_params & p, size_t smem, int grid, cudaStream_t st, int t0, int t1) {
     if (t1 < 0) t1 = t0;
     if (t0 == t1) {
         switch (t0) {
-            case B200_Q4_K:  return gs_launch<B200_Q4_K, B200_Q4_K, CHAIN>(p, smem, grid, st);
-            case B200_Q6_K:  return gs_launch<B200_Q6_K, B200_Q6_K, CHAIN>(p, smem, grid, st);
-            case B200_Q4_0:  return gs_launch<B200_Q4_0, B200_Q4_0, CHAIN>(p, smem, grid, st);
-            case B200_Q8_0:  return gs_launch<B200_Q8_0, B200_Q8_0, CHAIN>(p, smem, grid, st);
-            case B200_MXFP4: return gs_launch<B200_MXFP4, B200_MXFP4, CHAIN>(p, smem, grid, st);
+            case B200_Q4_K:  return gs_launch<B200_Q4_K, B200_Q4_K, MODE>(p, smem, grid, st);
+            case B200_Q6_K:  return gs_launch<B200_Q6_K, B200_Q6_K, MODE>(p, smem, grid, st);
+            case B200_Q4_0:  return gs_launch<B200_Q4_0, B200_Q4_0, MODE>(p, smem, grid, st);
+            case B200_Q8_0:  return gs_launch<B200_Q8_0, B200_Q8_0, MODE>(p, smem, grid, st);
+            case B200_MXFP4: return gs_launch<B200_MXFP4, B200_MXFP4, MODE>(p, smem, grid, st);
         }
     }
     const int lo = t0 < t1 ? t0 : t1, hi = t0 < t1 ? t1 : t0;
-    if (lo == B200_Q4_K && hi == B200_Q6_K)  return gs_launch<B200_Q4_K, B200_Q6_K, CHAIN>(p, smem, grid, st);
-    if (lo == B200_Q4_0 && hi == B200_Q6_K)  return gs_launch<B200_Q4_0, B200_Q6_K, CHAIN>(p, smem, grid, st);
-    if (lo == B200_Q4_0 && hi == B200_Q8_0)  return gs_launch<B200_Q4_0, B200_Q8_0, CHAIN>(p, smem, grid, st);
-    if (lo == B200_Q8_0 && hi == B200_MXFP4) return gs_launch<B200_Q8_0, B200_MXFP4, CHAIN>(p, smem, grid, st);
+    if (lo == B200_Q4_K && hi == B200_Q6_K)  return gs_launch<B200_Q4_K, B200_Q6_K, MODE>(p, smem, grid, st);
+    if (lo == B200_Q4_0 && hi == B200_Q6_K)  return gs_launch<B200_Q4_0, B200_Q6_K, MODE>(p, smem, grid, st);
+    if (lo == B200_Q4_0 && hi == B200_Q8_0)  return gs_launch<B200_Q4_0, B200_Q8_0, MODE>(p, smem, grid, st);
+    if (lo == B200_Q8_0 && hi == B200_MXFP4) return gs_launch<B200_Q8_0, B200_MXFP4, MODE>(p, smem, grid, st);
     set_error("b200 streaming GEMV: unsupported type pair (%d, %d)", t0, t1);
     return B200_ERR_UNSUPPORTED;
 }
@@ -1008,7 +1067,7 @@ extern "C" int b200_gemv_fused(const b200_gemv_fused_args * a, void * stream) {
     for (int s = 0; s < p.inl.n_ws; ++s) rows += p.inl.seg[s].M;
     int grid = a->n_sm > 0 ? a->n_sm : gs_sm_count();
     if (grid > rows) grid = (int) rows;                // never launch more CTAs than there are rows
-    return gs_launch_types<false>(p, smem, grid, (cudaStream_t) stream, types[0], types[1]);
+    return gs_launch_types<0>(p, smem, grid, (cudaStream_t) stream, types[0], types[1]);
 }
 
 // ---------------------------------------------------------------- decode chain
@@ -1020,6 +1079,8 @@ struct b200_chain {
     unsigned int * d_bar = nullptr;
     int n_gemv = 0, n_attn = 0;
     unsigned long long * d_dbg = nullptr;
+    bool peer = false;                 // row split over peer memory: d_bar belongs to the caller's arena
+    unsigned int * d_epoch = nullptr;
 };
 
 static bool gs_build_attn(const b200_attn_phase * a, gs_phase & ph, int & attn_floats) {
@@ -1053,7 +1114,22 @@ static bool gs_build_attn(const b200_attn_phase * a, gs_phase & ph, int & attn_f
     return true;
 }
 
-extern "C" b200_chain * b200_chain_create(const b200_phase * phases, int n_phases, int flags) {
+static b200_chain * gs_chain_create(const b200_phase * phases, int n_phases, int flags, const b200_peer_group * pg) {
+    if (pg) {
+        if (pg->n_ranks < 1 || pg->n_ranks > B200_MAX_RANKS || pg->rank < 0 || pg->rank >= pg->n_ranks || pg->delta[pg->rank] != 0 ||
+            pg->total_ctas < 1 || !pg->arena || !pg->sync) { set_error("b200_chain_create_peer: bad peer group"); return nullptr; }
+        const uintptr_t a0 = (uintptr_t) pg->arena, a1 = a0 + pg->arena_bytes, s0 = (uintptr_t) pg->sync;
+        if (s0 < a0 || s0 + sizeof(unsigned int) * (size_t) std::max(n_phases, 0) > a1 || s0 % 4) { set_error("b200_chain_create_peer: sync counters outside the arena"); return nullptr; }
+        for (int i = 0; i < n_phases; ++i) {
+            if (phases[i].kind != B200_PHASE_GEMV) continue;
+            const b200_gemv_fused_args & g = phases[i].gemv;
+            for (int k = 0; k < g.n_seg && k < B200_GEMV_MAX_SEG; ++k) {
+                if (g.glu_op != B200_GLU_NONE && k == 0) continue;                 // the gate segment has no dst of its own
+                const uintptr_t d0 = (uintptr_t) g.seg[k].dst.data, d1 = d0 + 4 * (size_t) g.seg[k].dst.ne[0];
+                if (d0 < a0 || d1 > a1) { set_error("b200_chain_create_peer: phase %d segment %d: dst outside the symmetric arena", i, k); return nullptr; }
+            }
+        }
+    }
     if (!phases || n_phases < 1 || n_phases > GS_MAX_PHASES) { set_error("b200_chain_create: bad phase count"); return nullptr; }
     std::vector<gs_phase> ph((size_t) n_phases);
     int64_t need = 0; int act_qs = 64, attn_floats = 0; int types[2] = {-1, -1};
@@ -1062,6 +1138,7 @@ extern "C" b200_chain * b200_chain_create(const b200_phase * phases, int n_phase
         bool ok;
         if (phases[i].kind == B200_PHASE_GEMV) { ok = gs_build_phase(&phases[i].gemv, ph[i], need, act_qs, types); ch->n_gemv++; }
         else if (phases[i].kind == B200_PHASE_ATTN) { ok = gs_build_attn(&phases[i].attn, ph[i], attn_floats); ch->n_attn++; }
+        else if (phases[i].kind == B200_PHASE_NOP)  { memset(&ph[i], 0, sizeof(gs_phase)); ph[i].kind = 2; ok = true; }
         else ok = false;
         if (!ok) { set_error("b200_chain_create: phase %d is not supported", i); delete ch; return nullptr; }
     }
@@ -1070,14 +1147,22 @@ extern "C" b200_chain * b200_chain_create(const b200_phase * phases, int n_phase
     for (int i = 0; i < n_phases; ++i)
         if (ph[i].kind == 0 && !gs_finish_phase(ph[i], cfg.stage_payload)) { set_error("b200_chain_create: phase %d: row does not fit a stage", i); delete ch; return nullptr; }
     cudaGetDevice(&ch->device);
+    ch->peer = pg != nullptr;
     if (cudaMalloc((void **) &ch->d_phases, sizeof(gs_phase) * (size_t) n_phases) != cudaSuccess ||
-        cudaMalloc((void **) &ch->d_bar, sizeof(unsigned int) * (size_t) n_phases) != cudaSuccess ||
+        (!pg && cudaMalloc((void **) &ch->d_bar, sizeof(unsigned int) * (size_t) n_phases) != cudaSuccess) ||
+        (pg && (cudaMalloc((void **) &ch->d_epoch, sizeof(unsigned int)) != cudaSuccess || cudaMemset(ch->d_epoch, 0, sizeof(unsigned int)) != cudaSuccess)) ||
         cudaMemcpy(ch->d_phases, ph.data(), sizeof(gs_phase) * (size_t) n_phases, cudaMemcpyHostToDevice) != cudaSuccess) {
         set_error("b200_chain_create: device allocation failed"); cudaGetLastError();
-        if (ch->d_phases) cudaFree(ch->d_phases); if (ch->d_bar) cudaFree(ch->d_bar);
+        if (ch->d_phases) cudaFree(ch->d_phases); if (ch->d_bar) cudaFree(ch->d_bar); if (ch->d_epoch) cudaFree(ch->d_epoch);
         delete ch; return nullptr;
     }
     memset(&ch->p, 0, sizeof(ch->p));
+    if (pg) {
+        ch->d_bar = pg->sync;
+        ch->p.epoch = ch->d_epoch; ch->p.total_ctas = pg->total_ctas;
+        for (int r = 0; r < pg->n_ranks; ++r)
+            if (r != pg->rank) ch->p.peer_delta[ch->p.n_peers++] = pg->delta[r];
+    }
     ch->p.phases = ch->d_phases; ch->p.bar = ch->d_bar; ch->p.n_phases = n_phases;
     ch->p.act_qs_bytes = cfg.act_qs; ch->p.stage_stride = cfg.stage_payload + GS_STAGE_SLACK; ch->p.n_stages = cfg.n_stages;
     ch->p.attn_floats = cfg.attn_floats; ch->p.flags = flags;
@@ -1090,11 +1175,45 @@ extern "C" b200_chain * b200_chain_create(const b200_phase * phases, int n_phase
     return ch;
 }
 
+extern "C" b200_chain * b200_chain_create(const b200_phase * phases, int n_phases, int flags) {
+    return gs_chain_create(phases, n_phases, flags, nullptr);
+}
+extern "C" b200_chain * b200_chain_create_peer(const b200_phase * phases, int n_phases, int flags, const b200_peer_group * pg) {
+    if (!pg) { set_error("b200_chain_create_peer: no peer group"); return nullptr; }
+    return gs_chain_create(phases, n_phases, flags, pg);
+}
+extern "C" int b200_chain_grid(void) { return gs_sm_count(); }
+
+// ---------------------------------------------------------------- symmetric arena (CUDA IPC)
+extern "C" int b200_peer_alloc(size_t bytes, void ** ptr) {
+    if (!ptr || !bytes) return B200_ERR_ARG;
+    B200_CUDA_TRY(cudaMalloc(ptr, bytes));
+    B200_CUDA_TRY(cudaMemset(*ptr, 0, bytes));
+    B200_CUDA_TRY(cudaDeviceSynchronize());
+    return B200_OK;
+}
+extern "C" int b200_peer_free(void * ptr) { B200_CUDA_TRY(cudaFree(ptr)); return B200_OK; }
+extern "C" int b200_peer_export(void * ptr, unsigned char handle[64]) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size is part of the ABI");
+    cudaIpcMemHandle_t h;
+    B200_CUDA_TRY(cudaIpcGetMemHandle(&h, ptr));
+    memcpy(handle, &h, 64);
+    return B200_OK;
+}
+extern "C" int b200_peer_open(const unsigned char handle[64], void ** ptr) {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    B200_CUDA_TRY(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return B200_OK;
+}
+extern "C" int b200_peer_close(void * ptr) { B200_CUDA_TRY(cudaIpcCloseMemHandle(ptr)); return B200_OK; }
+
 extern "C" int b200_chain_launch(b200_chain * ch, void * stream) {
     if (!ch) return B200_ERR_ARG;
     cudaStream_t st = (cudaStream_t) stream;
+    if (ch->peer) return gs_launch_types<2>(ch->p, ch->smem, ch->grid, st, ch->t0, ch->t1);   // counters accumulate: no reset
     B200_CUDA_TRY(cudaMemsetAsync(ch->d_bar, 0, sizeof(unsigned int) * (size_t) ch->p.n_phases, st));
-    return gs_launch_types<true>(ch->p, ch->smem, ch->grid, st, ch->t0, ch->t1);
+    return gs_launch_types<1>(ch->p, ch->smem, ch->grid, st, ch->t0, ch->t1);
 }
 
 // debug (flags bit 2): copies the globaltimer stamps [phase][cta 0 | last cta][barrier passed, prologue done, consumed, published]
@@ -1106,6 +1225,6 @@ extern "C" int b200_chain_debug_read(b200_chain * ch, unsigned long long * out, 
 
 extern "C" void b200_chain_destroy(b200_chain * ch) {
     if (!ch) return;
-    cudaFree(ch->d_phases); cudaFree(ch->d_bar); if (ch->d_dbg) cudaFree(ch->d_dbg);
+    cudaFree(ch->d_phases); if (!ch->peer) cudaFree(ch->d_bar); if (ch->d_dbg) cudaFree(ch->d_dbg); if (ch->d_epoch) cudaFree(ch->d_epoch);
     delete ch;
 }

@@ -41,7 +41,7 @@ def row_split(n_rows: int, world: int, rank: int) -> tuple[int, int]:
 
 class DecodeSession:
     def __init__(self, shape: gguf_synth.ModelShape, n_ctx: int = 256, kv_type: int = F16, seed: int = 1234,
-                 rank: int = 0, world: int = 1, device=None, fused: bool = True, gather=None):
+                 rank: int = 0, world: int = 1, device=None, fused: bool = True, gather=None, peer_dist=None):
         import torch
         self.torch = torch
         self.s = shape
@@ -51,6 +51,12 @@ class DecodeSession:
         self.n_ctx = n_ctx
         self.fused = fused
         self.gather = gather            # callable(local [n_loc] f32, full [n] f32, lo, hi) for world > 1
+        # row split over peer memory (fused == "chain", world > 1): activations live in a symmetric arena that the
+        # other ranks' GEMV epilogues write into; peer_dist = torch.distributed (handle exchange + barrier only)
+        self.arena = None
+        if fused == "chain" and (world > 1 or peer_dist is not None):
+            assert peer_dist is not None, "row-split decode chain needs peer_dist (torch.distributed) for the arena exchange"
+            self.arena = capi.PeerArena(16 << 20, peer_dist, rank, world, self.dev)
         self.L = capi.lib()
         self._bind()
         self.keep = []                  # descriptors / arrays that must outlive captured launches
@@ -119,17 +125,22 @@ class DecodeSession:
         self.resident_tokens = True      # False: the caller writes self.tok before every replay (host-fed tokens)
         self.pos = torch.zeros(1, dtype=torch.int32, device=self.dev)
         self.slot = torch.zeros(1, dtype=torch.int64, device=self.dev)
-        self.x = torch.zeros(1, E, **f32)
-        self.x2 = torch.zeros(1, E, **f32)
+
+        def act(n):      # matmul outputs: in the symmetric arena when the chain runs row-split over peer memory
+            if self.arena is not None:
+                return self.arena.carve(n, torch.float32).view(1, n)
+            return torch.zeros(1, n, **f32)
+        self.x = act(E)
+        self.x2 = act(E)
         self.h = torch.zeros(1, E, **f32)
-        self.q = torch.zeros(1, QD, **f32)
-        self.k = torch.zeros(1, KVD, **f32)
-        self.v = torch.zeros(1, KVD, **f32)
+        self.q = act(QD)
+        self.k = act(KVD)
+        self.v = act(KVD)
         self.qr = torch.zeros(1, QD, **f32)
         self.kr = torch.zeros(1, KVD, **f32)
-        self.att = torch.zeros(1, QD, **f32)
-        self.ff = torch.zeros(1, Fd, **f32)
-        self.logits = torch.zeros(1, s.n_vocab, **f32)
+        self.att = act(QD)
+        self.ff = act(Fd)
+        self.logits = act(s.n_vocab)
         # per-rank slices of matmul outputs before the gather (world > 1)
         self.loc = torch.zeros(max(s.n_vocab, Fd, QD), **f32) if self.world > 1 else None
         # KV cache: per layer [n_ctx rows of n_head_kv*head_dim], f16 or q8_0 (reference src/llama-kv-cache.cpp)
@@ -258,22 +269,35 @@ class DecodeSession:
         """The whole token as ONE cooperative launch: per layer [QKV | attention | wo | gate/up | down], then the logits."""
         s = self.s
         D, H, Hkv = s.head_dim, s.n_head, s.n_head_kv
-        assert self.world == 1 and self.kv_type == F16, "decode chain: single GPU, f16 KV"
+        assert self.kv_type == F16, "decode chain: f16 KV"
         keep, phases = self.chain_keep, []
         x, x2 = self.x, self.x2
+        world, rank = self.world, self.rank
 
-        def seg(name, bias, dst):
+        def seg(name, bias, dst, n_full=None):
+            """(weights, type, rows, bias, dst) of this rank's row slice (the whole matrix on one GPU)."""
             wd, t, (K, M) = self.w[name]
+            if world > 1:
+                lo, hi = row_split(dst.numel() if dst is not None else n_full, world, rank)
+                assert hi - lo == M
+                bias = bias.view(-1)[lo:hi] if bias is not None else None
+                dst = dst.view(-1)[lo:hi] if dst is not None else None
             return (wd, t, M, bias, dst)
+
+        def gemv(xin, segs, **kw):
+            segs = [g for g in segs if g[2] > 0]          # a rank may own no rows of a small matrix
+            if not segs:
+                return capi.nop_phase()
+            return capi.gemv_phase(xin.view(-1), segs, keep=keep, **kw)
 
         hb = gguf_synth.row_bytes(self.kv_type, D)
         mode = 2 if s.arch == "qwen2" else 0
         for il in range(s.n_layer):
             p = f"blk.{il}."
-            phases.append(capi.gemv_phase(x.view(-1), [seg(p + "attn_q.weight", self._full_bias(p + "attn_q.bias"), self.q.view(-1)),
-                                                       seg(p + "attn_k.weight", self._full_bias(p + "attn_k.bias"), self.k.view(-1)),
-                                                       seg(p + "attn_v.weight", self._full_bias(p + "attn_v.bias"), self.v.view(-1))],
-                                          norm_w=self.w[p + "attn_norm.weight"][0], eps=s.rms_eps, keep=keep))
+            phases.append(gemv(x, [seg(p + "attn_q.weight", self._full_bias(p + "attn_q.bias"), self.q.view(-1)),
+                                   seg(p + "attn_k.weight", self._full_bias(p + "attn_k.bias"), self.k.view(-1)),
+                                   seg(p + "attn_v.weight", self._full_bias(p + "attn_v.bias"), self.v.view(-1))],
+                               norm_w=self.w[p + "attn_norm.weight"][0], eps=s.rms_eps))
             ph = capi.Phase(); ph.kind = capi.PHASE_ATTN
             a = ph.attn
             a.q = capi.make_tensor(self.q.data_ptr(), F32, [D * H, 1, 1, 1])
@@ -290,13 +314,19 @@ class DecodeSession:
             a.scale = 1.0 / math.sqrt(D)
             a.dst = capi.make_tensor(self.att.data_ptr(), F32, [D * H, 1, 1, 1])
             phases.append(ph)
-            phases.append(capi.gemv_phase(self.att.view(-1), [seg(p + "attn_output.weight", x.view(-1), x2.view(-1))], keep=keep))
-            phases.append(capi.gemv_phase(x2.view(-1), [seg(p + "ffn_gate.weight", None, None), seg(p + "ffn_up.weight", None, self.ff.view(-1))],
-                                          norm_w=self.w[p + "ffn_norm.weight"][0], eps=s.rms_eps, glu_op=capi.GLU_SWIGLU, keep=keep))
-            phases.append(capi.gemv_phase(self.ff.view(-1), [seg(p + "ffn_down.weight", x2.view(-1), x.view(-1))], keep=keep))
-        phases.append(capi.gemv_phase(x.view(-1), [seg("output.weight", None, self.logits.view(-1))],
-                                      norm_w=self.w["output_norm.weight"][0], eps=s.rms_eps, keep=keep))
-        return capi.Chain(phases, flags=self.chain_flags, keep=keep)
+            phases.append(gemv(self.att, [seg(p + "attn_output.weight", x.view(-1), x2.view(-1))]))
+            phases.append(gemv(x2, [seg(p + "ffn_gate.weight", None, None, n_full=s.n_ff), seg(p + "ffn_up.weight", None, self.ff.view(-1))],
+                               norm_w=self.w[p + "ffn_norm.weight"][0], eps=s.rms_eps, glu_op=capi.GLU_SWIGLU))
+            phases.append(gemv(self.ff, [seg(p + "ffn_down.weight", x2.view(-1), x.view(-1))]))
+        phases.append(gemv(x, [seg("output.weight", None, self.logits.view(-1))],
+                           norm_w=self.w["output_norm.weight"][0], eps=s.rms_eps))
+        peer = None
+        if self.arena is not None:
+            # barrier counters of this chain: fresh (zero) words of the arena, at the same offset on every rank
+            sync = self.arena.carve(len(phases), self.torch.int32)
+            keep.append(sync)
+            peer = self.arena.group(sync)
+        return capi.Chain(phases, flags=self.chain_flags, keep=keep, peer=peer)
 
     def _issue_token_chain(self, n_kv):
         torch = self.torch

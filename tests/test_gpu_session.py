@@ -120,3 +120,48 @@ def test_graph_replay_matches_eager():
         lb = b.decode(t).clone()
         torch.cuda.synchronize()
         assert torch.equal(la, lb), f"token {i}"
+
+
+class _OneRankDist:
+    """torch.distributed stand-in for a single-rank peer group (handle exchange and barrier are trivial)."""
+
+    @staticmethod
+    def all_gather_object(out, obj):
+        out[0] = obj
+
+    @staticmethod
+    def barrier():
+        pass
+
+
+@pytest.mark.parametrize("key", ["tiny-q4_k_m", "tiny-q8_0"])
+@pytest.mark.parametrize("graph", [False, True])
+def test_peer_chain_single_rank_matches_chain(key, graph):
+    """The row-split kernel variant (system-scope barriers on never-reset counters, symmetric arena) with one rank
+    must reproduce the single-GPU chain bit for bit, over many launches (the counters accumulate per launch)."""
+    import torch
+    from llama_mi50_b200 import gguf_synth as gs
+    from llama_mi50_b200.session import DecodeSession
+    shape = gs.SHAPES[key]
+    a = DecodeSession(shape, n_ctx=256, fused="chain")
+    b = DecodeSession(shape, n_ctx=256, fused="chain", peer_dist=_OneRankDist())
+    assert b.arena is not None and b.arena.total_ctas == torch.cuda.get_device_properties(0).multi_processor_count
+    a.resident_tokens = b.resident_tokens = False
+    if graph:
+        b.capture(256)
+    for i, t in enumerate([1, 2, 3, 4, 250, 17, 99, 5, 6, 7]):
+        la = a.decode_eager(t, i).clone()
+        lb = (b.decode(t) if graph else b.decode_eager(t, i)).clone()
+        torch.cuda.synchronize()
+        assert torch.equal(la, lb), f"token {i}"
+
+
+def test_peer_chain_rejects_dst_outside_arena():
+    import ctypes as C
+    import torch
+    from llama_mi50_b200 import capi, gguf_synth as gs
+    from llama_mi50_b200.session import DecodeSession
+    b = DecodeSession(gs.SHAPES["tiny-q4_k_m"], n_ctx=256, fused="chain", peer_dist=_OneRankDist())
+    b.logits = torch.zeros_like(b.logits)          # an ordinary allocation: other ranks could not reach it
+    with pytest.raises(RuntimeError, match="outside the symmetric arena"):
+        b._build_chain(256)
