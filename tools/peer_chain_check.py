@@ -69,7 +69,8 @@ def main():
         dist.barrier()
         sp = DecodeSession(shape, n_ctx=256, rank=rank, world=world, fused="chain", peer_dist=dist)
         sp.resident_tokens = False
-        log("8B peer session built")
+        sp.chain_flags = int(os.environ.get("CHAIN_FLAGS", "0"), 0)
+        log("8B peer session built, chain flags", sp.chain_flags)
         got = [sp.decode_eager(t, i).clone() for i, t in enumerate(tokens[:4])]
         torch.cuda.synchronize(); log("8B eager peer decode done")
         one = DecodeSession(shape, n_ctx=256, fused="chain")
