@@ -267,7 +267,7 @@ def main_b200(a):
     traffic = None
     try:   # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch from the committed ncu --set full capture (profiles/)
         with open(os.path.join(ROOT, "profiles", "r01_chain_ncu_summary.json")) as f:
-            traffic = json.load(f).get("dram_bytes_per_launch") if chain_mode else None
+            traffic = json.load(f).get("dram_bytes_per_launch") if chain_mode and world == 1 else None   # the capture is the 1-GPU chain
     except Exception:
         traffic = None
     if chain_mode:

@@ -168,10 +168,14 @@ B200_API int          b200_chain_debug_read(b200_chain * chain, unsigned long lo
  * Replaces the reference's row-split matmul (ggml-cuda.cu:791-804 get_row_split, :1497-1700 ggml_cuda_op_mul_mat:
  * per matmul, the main device quantizes the activation, copies it to every device, each device runs its row slice,
  * and the slices are copied back behind events).  Here one process per GPU runs the SAME chain over its own row
- * slices (each rank passes its slice of every weight, bias and dst); the GEMV epilogue stores every output value into
- * the activation buffers of ALL ranks (plain peer stores over NVLink), and the in-kernel barrier between phases counts
- * the CTAs of all ranks (system-scope reductions on every rank's counter).  No collective, no extra launch: the
- * exchange is part of the matmul.  Attention phases are computed by every rank (replicated KV cache).
+ * slices (each rank passes its slice of every weight, bias and dst; a slice may have 0 rows).  The GEMV epilogue
+ * stores every output value to ALL other ranks over NVLink as ONE 64-bit word {f32 bits, tag of (launch, phase)} in a
+ * shadow of the activation arena; the consuming phase reads its own rows from plain memory behind the local grid
+ * barrier and spins on the tags of the others' rows — one NVLink traversal per dependency, no fence round trip, no
+ * counter (the idea of NCCL's LL protocol, inside the matmul).  Outputs nobody in the chain consumes (the logits) go
+ * out as plain stores followed by one system-scope fence and an arrival on every rank, which the launch waits for
+ * before it ends.  No collective, no extra launch.  Attention phases are computed by every rank (replicated KV cache).
+ * Epilogue operands (bias / residual) must be rows the rank computed itself.
  *
  * Requirements: every rank allocates a "symmetric arena" of the same size with the same layout (b200_peer_alloc),
  * maps the arenas of the others (b200_peer_export / b200_peer_open) and passes delta[r] = arena of rank r - own arena
@@ -186,6 +190,8 @@ typedef struct b200_peer_group {
     void *  arena; size_t arena_bytes;
     int64_t delta[B200_MAX_RANKS];   /* bytes; delta[rank] == 0 */
     unsigned int * sync;
+    size_t  act_bytes;               /* [arena, arena + act_bytes): activations (every GEMV dst and every x / q / k / v a row-split matmul produced) */
+    size_t  ll_offset;               /* [arena + ll_offset, + 2 * act_bytes): shadow of tagged 64-bit words, zero before the first launch */
 } b200_peer_group;
 B200_API b200_chain * b200_chain_create_peer(const b200_phase * phases, int n_phases, int flags, const b200_peer_group * pg);
 B200_API int  b200_chain_grid(void);                                       /* CTAs the chain uses on the current device */

@@ -323,7 +323,8 @@ MAX_RANKS = 8
 class PeerGroup(C.Structure):
     """b200_peer_group (include/b200_kernels.h)."""
     _fields_ = [("rank", C.c_int32), ("n_ranks", C.c_int32), ("total_ctas", C.c_int32), ("_pad", C.c_int32),
-                ("arena", C.c_void_p), ("arena_bytes", C.c_size_t), ("delta", C.c_int64 * MAX_RANKS), ("sync", C.c_void_p)]
+                ("arena", C.c_void_p), ("arena_bytes", C.c_size_t), ("delta", C.c_int64 * MAX_RANKS), ("sync", C.c_void_p),
+                ("act_bytes", C.c_size_t), ("ll_offset", C.c_size_t)]
 
 
 class _RawCuda:
@@ -336,9 +337,12 @@ class _RawCuda:
 class PeerArena:
     """Symmetric activation arena of the row-split decode chain: the same allocation, with the same layout, on every
     rank; each rank maps the arenas of the others over CUDA IPC (NVLink peer access).  `dist` is an initialised
-    torch.distributed (plumbing: it only carries the 64-byte handles and a barrier)."""
+    torch.distributed (plumbing: it only carries the 64-byte handles and a barrier).
+    Layout: [0, nbytes/4) activations and barrier counters (carve), [nbytes/2, nbytes) the shadow of tagged words."""
 
     def __init__(self, nbytes: int, dist, rank: int, world: int, device):
+        assert nbytes % 1024 == 0
+        self.act_bytes, self.ll_offset = nbytes // 4, nbytes // 2
         import torch
         L = lib()
         vp = C.c_void_p
@@ -376,7 +380,7 @@ class PeerArena:
         import torch
         size = n * torch.empty((), dtype=dtype).element_size()
         off = (self.off + 255) & ~255
-        assert off + size <= self.nbytes, "peer arena exhausted"
+        assert off + size <= self.act_bytes, "peer arena exhausted"
         self.off = off + size
         return self.bytes_t[off:off + size].view(dtype)
 
@@ -387,6 +391,7 @@ class PeerArena:
         for r in range(MAX_RANKS):
             g.delta[r] = self.delta[r]
         g.sync = sync.data_ptr()
+        g.act_bytes, g.ll_offset = self.act_bytes, self.ll_offset
         return g
 
 

@@ -60,6 +60,10 @@ struct gs_attn {
     int64_t k_nb1, k_nb2, v_nb1, v_nb2;
     int32_t D, H, H_kv, n_kv, rope_mode, n_dims;
     float scale, theta_scale, freq_scale;
+    // row split: elements [lo, hi) of q / k_new / v_new were computed by this rank (plain memory, after the local
+    // barrier); the rest arrives from the other ranks as tagged words.  *_tag: index of the producing phase
+    int32_t q_lo, q_hi, k_lo, k_hi, v_lo, v_hi;
+    uint32_t q_tag, k_tag, v_tag;
 };
 struct alignas(16) gs_phase {
     int32_t kind;                  // 0 = GEMV, 1 = attention
@@ -69,6 +73,11 @@ struct alignas(16) gs_phase {
     const float * x; const float * norm_w; float eps; int32_t K;
     blk_q8_1 * xq_out;
     int64_t total_bytes;
+    // row split: x[x_lo, x_hi) is local, the rest are tagged words written by the other ranks in phase x_tag.
+    // peer_mode: how this phase's outputs reach the other ranks: 0 not at all, 1 tagged words (read by a later phase),
+    // 2 plain stores + system-scope arrival (read after the launch: the logits)
+    int32_t x_lo, x_hi; uint32_t x_tag; int32_t peer_mode;
+    uint32_t self_tag; int32_t _pad2[3];      // index of this phase (added to the launch tag for its own tagged stores)
     gs_attn attn;
 };
 struct gs_params {
@@ -86,7 +95,11 @@ struct gs_params {
     int32_t n_peers;               // other ranks
     int32_t total_ctas;            // CTAs of all ranks: arrivals per phase and launch
     int64_t peer_delta[B200_MAX_RANKS - 1];   // byte offset from a local arena address to the same location on peer r
-    unsigned int * epoch;          // launches completed so far on this rank (the counters are never reset)
+    unsigned int * epoch;          // launches completed so far on this rank: tags of different launches differ
+    unsigned int * sync;           // arena: arrival counters of the peer_mode 2 phases (all ranks' CTAs)
+    const char * arena;            // local arena base and its shadow of tagged words: the word of the f32 at arena + o
+    char * ll_base;                //   is at ll_base + 2 * o
+    int32_t n_final; int32_t final_phase[4];   // peer_mode 2 phases the launch waits for before it ends
 };
 
 // ---------------------------------------------------------------- PTX helpers
@@ -119,6 +132,42 @@ __device__ __forceinline__ uint64_t policy_evict_first() {
     return p;
 }
 __device__ __forceinline__ void named_bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+
+// ---- tagged words (row split over peer memory): a value and the tag of the (launch, phase) that produced it travel in
+// ONE 64-bit store, so a reader that sees the tag has the value: one NVLink traversal, no fence round trip, no counter
+// (the idea of NCCL's LL protocol).  Spins are bounded: a rank that never delivers becomes a trap, not a hung GPU.
+__device__ __forceinline__ void ll_store(void * p, float v, unsigned int tag) {
+    const unsigned long long w = (unsigned long long) __float_as_uint(v) | ((unsigned long long) tag << 32);
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
+}
+__device__ __forceinline__ unsigned long long ll_load1(const void * p) {
+    unsigned long long w;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+    return w;
+}
+__device__ __forceinline__ ulonglong2 ll_load2(const void * p) {      // two elements, 16 B aligned
+    ulonglong2 r;
+    asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(r.x), "=l"(r.y) : "l"(p) : "memory");
+    return r;
+}
+__device__ __forceinline__ bool ll_ok(unsigned long long w, unsigned int tag) { return (unsigned int) (w >> 32) == tag; }
+__device__ __forceinline__ void ll_spin_check(unsigned int & spins, unsigned long long & t0) {
+    if ((++spins & 0x3FFu) == 0) {
+        unsigned long long now;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (!t0) t0 = now; else if (now - t0 > 20000000000ull) __trap();          // 20 s
+    }
+}
+__device__ __forceinline__ float ll_read(const void * p, unsigned int tag) {
+    unsigned long long w = ll_load1(p);
+    unsigned int spins = 0; unsigned long long t0 = 0;
+    while (!ll_ok(w, tag)) { ll_spin_check(spins, t0); w = ll_load1(p); }
+    return __uint_as_float((unsigned int) w);
+}
+__device__ __forceinline__ void ll_settle2(ulonglong2 & a, const void * p, unsigned int tag) {
+    unsigned int spins = 0; unsigned long long t0 = 0;
+    while (!ll_ok(a.x, tag) || !ll_ok(a.y, tag)) { ll_spin_check(spins, t0); a = ll_load2(p); }
+}
 
 // N consecutive little-endian u32 words starting at an arbitrarily aligned shared-memory byte address
 template <int N>
@@ -361,7 +410,7 @@ struct gs_shared {
     uint64_t full[GS_MAX_STAGES], empty[GS_MAX_STAGES];
     float part[GS_NW];
     float slots[2][GS_NW][GS_RB];  // per-warp row sums of a pass, combined across the KS warps of a row group
-    unsigned int target;           // value a phase counter reaches when every CTA (of every rank) has arrived
+    unsigned int tag;              // row split: tag of this launch (phase index is added)
 };
 
 struct gs_ctx {                    // per-thread view of the launch-wide shared memory carve-up
@@ -380,12 +429,20 @@ __device__ __forceinline__ void gs_row_range(const gs_seg & sg, int64_t lo, int6
 // named barrier of their own; warp ks == 0 sums the KS values in fixed order, applies the epilogue and stores.
 // one output value: the local store and, under row split, the same store into every peer's copy of the buffer
 template <bool PEER>
-__device__ __forceinline__ void gs_put(const gs_params & p, float * d, float v) {
+__device__ __forceinline__ void gs_put(const gs_params & p, const gs_phase & ph, const gs_shared & sh, float * d, float v) {
     *d = v;
     if (PEER) {
+        if (ph.peer_mode == 1) {
+            char * l = p.ll_base + 2 * ((const char *) d - p.arena);
+            const unsigned int tag = sh.tag + ph.self_tag;
 #pragma unroll
-        for (int r = 0; r < B200_MAX_RANKS - 1; ++r)
-            if (r < p.n_peers) *(float *) ((char *) d + p.peer_delta[r]) = v;
+            for (int r = 0; r < B200_MAX_RANKS - 1; ++r)
+                if (r < p.n_peers) ll_store(l + p.peer_delta[r], v, tag);
+        } else if (ph.peer_mode == 2) {
+#pragma unroll
+            for (int r = 0; r < B200_MAX_RANKS - 1; ++r)
+                if (r < p.n_peers) *(float *) ((char *) d + p.peer_delta[r]) = v;
+        }
     }
 }
 
@@ -457,11 +514,11 @@ __device__ __forceinline__ void consume_segment(const gs_params & p, const gs_ct
             }
             if (ks == 0 && lane == 0) {
                 if (pair) {
-                    gs_put<PEER>(p, dst + row + jb, gs_glu(glu_op, acc[0], acc[1], glu_alpha, glu_limit) + bv[0]);
+                    gs_put<PEER>(p, ph, sh, dst + row + jb, gs_glu(glu_op, acc[0], acc[1], glu_alpha, glu_limit) + bv[0]);
                 } else {
 #pragma unroll
                     for (int j = 0; j < GS_RB; ++j)
-                        if (j < rpp && jb + j < nr) gs_put<PEER>(p, dst + row + jb + j, acc[j] + bv[j]);
+                        if (j < rpp && jb + j < nr) gs_put<PEER>(p, ph, sh, dst + row + jb + j, acc[j] + bv[j]);
                 }
             }
         }
@@ -487,9 +544,21 @@ template <bool COHERENT>
 __device__ __forceinline__ float4 gs_ld4(const float * p) {
     return COHERENT ? __ldcg((const float4 *) p) : *(const float4 *) p;
 }
-template <bool COHERENT>
-__device__ __forceinline__ void gs_prologue(const gs_ctx & c, const gs_phase & ph, int warp, int lane) {
+// four consecutive elements of a row-split activation that another rank computed: spin on their tags
+__device__ __forceinline__ float4 ll_read4(const char * l, unsigned int tag) {
+    ulonglong2 a = ll_load2(l), b = ll_load2(l + 16);
+    ll_settle2(a, l, tag); ll_settle2(b, l + 16, tag);
+    return make_float4(__uint_as_float((unsigned int) a.x), __uint_as_float((unsigned int) a.y),
+                       __uint_as_float((unsigned int) b.x), __uint_as_float((unsigned int) b.y));
+}
+template <bool COHERENT, bool PEER>
+__device__ __forceinline__ void gs_prologue(const gs_params & p, const gs_ctx & c, const gs_phase & ph, int warp, int lane) {
     const int K = ph.K, nblk = K >> 5;
+    // row split: elements outside [x_lo, x_hi) come from the other ranks as tagged words
+    const bool has_remote = PEER && (ph.x_lo > 0 || ph.x_hi < K);
+    const char * xl = PEER ? p.ll_base + 2 * ((const char *) ph.x - p.arena) : nullptr;
+    const unsigned int xtag = PEER ? c.sh->tag + ph.x_tag : 0u;
+    auto remote = [&](int e) { return has_remote && (e < ph.x_lo || e >= ph.x_hi); };
     const float * __restrict__ x = ph.x;
     const float * __restrict__ nw = ph.norm_w;
     blk_q8_1 * xq_out = blockIdx.x == 0 ? ph.xq_out : nullptr;
@@ -532,8 +601,29 @@ __device__ __forceinline__ void gs_prologue(const gs_ctx & c, const gs_phase & p
             const int blk = pw * 4 + bw + it * BPP;
             xv[it] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); wv[it] = xv[it];
             if (blk < nblk) {
-                xv[it] = gs_ld4<COHERENT>(x + blk * 32 + sub * 4);
+                if (!remote(blk * 32 + sub * 4)) xv[it] = gs_ld4<COHERENT>(x + blk * 32 + sub * 4);
                 if (nw) wv[it] = *(const float4 *) (nw + blk * 32 + sub * 4);
+            }
+        }
+        if (has_remote) {
+#pragma unroll
+            for (int it0 = 0; it0 < NV; it0 += 2) {                        // two passes (four 16 B loads) in flight per thread
+                ulonglong2 a[2], b[2];
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    const int e = (pw * 4 + bw + (it0 + u) * BPP) * 32 + sub * 4;
+                    a[u] = make_ulonglong2(0, 0); b[u] = a[u];
+                    if (e < K && remote(e)) { a[u] = ll_load2(xl + 8 * (int64_t) e); b[u] = ll_load2(xl + 8 * (int64_t) e + 16); }
+                }
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    const int e = (pw * 4 + bw + (it0 + u) * BPP) * 32 + sub * 4;
+                    if (e < K && remote(e)) {
+                        ll_settle2(a[u], xl + 8 * (int64_t) e, xtag); ll_settle2(b[u], xl + 8 * (int64_t) e + 16, xtag);
+                        xv[it0 + u] = make_float4(__uint_as_float((unsigned int) a[u].x), __uint_as_float((unsigned int) a[u].y),
+                                                  __uint_as_float((unsigned int) b[u].x), __uint_as_float((unsigned int) b[u].y));
+                    }
+                }
             }
         }
         float scale = 1.0f;
@@ -561,7 +651,7 @@ __device__ __forceinline__ void gs_prologue(const gs_ctx & c, const gs_phase & p
         if (nw) {
             float ss = 0.0f;
             for (int i = ptid * 4; i < K; i += GS_PRO_THREADS * 4) {
-                const float4 v = gs_ld4<COHERENT>(x + i);
+                const float4 v = remote(i) ? ll_read4(xl + 8 * (int64_t) i, xtag) : gs_ld4<COHERENT>(x + i);
                 ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
             }
             ss = warp_sum(ss);
@@ -576,7 +666,11 @@ __device__ __forceinline__ void gs_prologue(const gs_ctx & c, const gs_phase & p
             const int blk = b0 + bw;
             const bool act = blk < nblk;
             float4 t = make_float4(0.0f, 0.0f, 0.0f, 0.0f), w = t;
-            if (act) { t = gs_ld4<COHERENT>(x + blk * 32 + sub * 4); if (nw) w = *(const float4 *) (nw + blk * 32 + sub * 4); }
+            if (act) {
+                const int e = blk * 32 + sub * 4;
+                t = remote(e) ? ll_read4(xl + 8 * (int64_t) e, xtag) : gs_ld4<COHERENT>(x + e);
+                if (nw) w = *(const float4 *) (nw + e);
+            }
             quant_store(blk, act, t, w, scale);
         }
     }
@@ -588,8 +682,14 @@ __device__ __forceinline__ void gs_prologue(const gs_ctx & c, const gs_phase & p
 // FLASH_ATTN_EXT nodes (rope.cu:563, set-rows.cu:318, fattn-vec.cuh:19-507).  The current token's K/V rows are taken
 // from the raw projections (RoPE applied, rounded to f16 exactly as the cache stores them) and written to the cache by
 // the first query head of each KV group; all other positions are read from the cache.
-template <int D>
-__device__ __forceinline__ void gs_attn_item(const gs_attn & a, int h, float * sm, int warp, int lane) {
+// one element of q / k_new / v_new: plain when this rank computed it, else the tagged word another rank stored
+template <bool PEER>
+__device__ __forceinline__ float gs_attn_ld(const gs_params & p, const float * base, int64_t i, int lo, int hi, unsigned int tag) {
+    if (!PEER || (i >= lo && i < hi)) return __ldcg(base + i);
+    return ll_read(p.ll_base + 2 * ((const char *) (base + i) - p.arena), tag);
+}
+template <int D, bool PEER>
+__device__ __forceinline__ void gs_attn_item(const gs_params & p, unsigned int ltag, const gs_attn & a, int h, float * sm, int warp, int lane) {
     constexpr int LPP = D / 32, PPB = 32 / LPP, DPL = D / 32;     // lanes per position, positions per batch, dims per lane (V)
     const int tid = warp * 32 + lane;
     const int gqa = a.H / a.H_kv, g = h / gqa;
@@ -601,25 +701,28 @@ __device__ __forceinline__ void gs_attn_item(const gs_attn & a, int h, float * s
         if (tid < D) {                                            // threads 0..D/2-1: q pairs, D/2..D-1: k pairs
             const bool isk = tid >= D / 2;
             const int i = isk ? tid - D / 2 : tid;
-            const float * src = isk ? a.k_new + (int64_t) g * D : a.q + (int64_t) h * D;
+            const float * src = isk ? a.k_new : a.q;
+            const int64_t so = isk ? (int64_t) g * D : (int64_t) h * D;
+            const int slo = isk ? a.k_lo : a.q_lo, shi = isk ? a.k_hi : a.q_hi;
+            const unsigned int stag = ltag + (isk ? a.k_tag : a.q_tag);
             float * dst = isk ? s_k : s_q;
             if (i < half_d) {
                 const int i0 = a.rope_mode == 2 ? i : 2 * i, i1 = a.rope_mode == 2 ? i + half_d : 2 * i + 1;
                 const float theta = (float) pos * powf(a.theta_scale, (float) i) * a.freq_scale;
                 float sn, cs; sincosf(theta, &sn, &cs);
-                const float x0 = __ldcg(src + i0), x1 = __ldcg(src + i1);
+                const float x0 = gs_attn_ld<PEER>(p, src, so + i0, slo, shi, stag), x1 = gs_attn_ld<PEER>(p, src, so + i1, slo, shi, stag);
                 float y0 = x0 * cs - x1 * sn, y1 = x0 * sn + x1 * cs;
                 if (isk) { y0 = __half2float(__float2half_rn(y0)); y1 = __half2float(__float2half_rn(y1)); }
                 else     { y0 *= a.scale; y1 *= a.scale; }
                 dst[i0] = y0; dst[i1] = y1;
             }
             for (int d = a.n_dims + i; d < D; d += D / 2) {       // dims beyond n_dims pass through
-                const float y = __ldcg(src + d);
+                const float y = gs_attn_ld<PEER>(p, src, so + d, slo, shi, stag);
                 dst[d] = isk ? __half2float(__float2half_rn(y)) : y * a.scale;
             }
         } else if (tid < 2 * D) {
             const int d = tid - D;
-            s_v[d] = __half2float(__float2half_rn(__ldcg(a.v_new + (int64_t) g * D + d)));
+            s_v[d] = __half2float(__float2half_rn(gs_attn_ld<PEER>(p, a.v_new, (int64_t) g * D + d, a.v_lo, a.v_hi, ltag + a.v_tag)));
         }
     }
     named_bar_sync(3, GS_CON_THREADS);
@@ -773,8 +876,8 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
         for (int s = 0; s < p.n_stages; ++s) { mbar_init(&sh.full[s], 1); mbar_init(&sh.empty[s], GS_NW); }
-        // PEER: the counters are shared with the other ranks and never reset; arrivals accumulate over launches
-        sh.target = PEER ? (__ldcg(p.epoch) + 1u) * (unsigned int) p.total_ctas : gridDim.x;
+        // row split: tags of this launch = (launches so far + 1) * 1024 + phase index (never 0, the value of fresh memory)
+        sh.tag = PEER ? (__ldcg(p.epoch) + 1u) << 10 : 0u;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -834,12 +937,12 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
         if (ip == 0) {
             pdl_wait();
         } else if (tid == 0) {
-            gs_wait_counter<PEER>(p.bar + ip - 1, PEER ? sh.target : gridDim.x);
+            gs_wait_counter<false>(p.bar + ip - 1, gridDim.x);       // this GPU's CTAs; rows of other ranks carry their own tags
         }
         named_bar_sync(1, GS_CON_THREADS);
         if (CHAIN && tid == 0) GS_STAMP(ip, 0);
         if (ph.kind == 0) {
-            gs_prologue<CHAIN>(c, ph, warp, lane);
+            gs_prologue<CHAIN, PEER>(p, c, ph, warp, lane);
             if (CHAIN && tid == 0) GS_STAMP(ip, 1);
             const int64_t lo = ph.total_bytes * (int64_t) blockIdx.x / gridDim.x, hi = ph.total_bytes * (int64_t) (blockIdx.x + 1) / gridDim.x;
             for (int s = 0; s < ph.n_ws; ++s) {
@@ -851,38 +954,41 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
             }
         } else if (CHAIN && ph.kind == 1) {
             for (int h = blockIdx.x; h < ph.attn.H; h += gridDim.x) {
-                if (ph.attn.D == 128) gs_attn_item<128>(ph.attn, h, c.attn, warp, lane);
-                else                  gs_attn_item<64>(ph.attn, h, c.attn, warp, lane);
+                if (ph.attn.D == 128) gs_attn_item<128, PEER>(p, sh.tag, ph.attn, h, c.attn, warp, lane);
+                else                  gs_attn_item<64, PEER>(p, sh.tag, ph.attn, h, c.attn, warp, lane);
             }
         }
         if (CHAIN) {
             if (tid == 0) GS_STAMP(ip, 2);
             // ---- publish: this CTA's stores of the phase are visible device-wide, then count it in
-            // The CTA barrier orders every consumer thread's stores before thread 0's fence; the fence is cumulative, so
-            // the arrival that follows it publishes all of them (the pattern of a cooperative-groups grid sync).
-            // Measured (2 x B200, 8B): one system-scope fence instead of 512 takes the row-split chain from 362 to 420 tok/s;
-            // at device scope the per-thread fences are marginally faster (460 vs 458 tok/s) and stay.  flags bit 3 swaps.
-            const bool fence_all = PEER ? (c.flags & 8) != 0 : (c.flags & 8) == 0;
-            if (fence_all) { if (PEER) __threadfence_system(); else __threadfence(); }
+            // flags bit 3: fence in thread 0 only, after the CTA barrier (the barrier orders every consumer thread's stores
+            // before it and the fence is cumulative — the pattern of a cooperative-groups grid sync).  Measured: at device
+            // scope 512 fences are marginally faster than one (460 vs 458 tok/s); at system scope one is much cheaper.
+            const bool fence_all = (c.flags & 8) == 0;
+            if (fence_all) __threadfence();
             named_bar_sync(1, GS_CON_THREADS);
             if (tid == 0) {
-                if (!fence_all) { if (PEER) __threadfence_system(); else __threadfence(); }
+                if (!fence_all) __threadfence();
                 GS_STAMP(ip, 4);
                 atomicAdd(p.bar + ip, 1u);
-                if (PEER) {
+                if (PEER && ph.peer_mode == 2) {
+                    // outputs read after the launch (the logits) went to the other ranks as plain stores: one system-scope
+                    // fence, then the arrival is counted on every rank
+                    __threadfence_system();
+                    atomicAdd_system(p.sync + ip, 1u);
 #pragma unroll
                     for (int r = 0; r < B200_MAX_RANKS - 1; ++r)
-                        if (r < p.n_peers) atomicAdd_system((unsigned int *) ((char *) (p.bar + ip) + p.peer_delta[r]), 1u);
+                        if (r < p.n_peers) atomicAdd_system((unsigned int *) ((char *) (p.sync + ip) + p.peer_delta[r]), 1u);
                 }
                 GS_STAMP(ip, 3);
             }
         }
     }
     if (PEER && blockIdx.x == 0 && tid == 0) {
-        // the launch ends only when every rank has delivered its rows of the last phase (the logits) into this rank's
-        // buffers; then the launch is counted.  No CTA of this launch reads the epoch after its first instructions,
-        // and no CTA of the next launch starts before this one has exited (same stream).
-        gs_wait_counter<true>(p.bar + n_phases - 1, sh.target);
+        // the launch ends only when every rank has delivered its plain-stored rows (the logits) into this rank's buffers;
+        // then the launch is counted.  No CTA of this launch reads the epoch after its first instructions, and no CTA of
+        // the next launch starts before this one has exited (same stream).
+        for (int k = 0; k < p.n_final; ++k) gs_wait_counter<true>(p.sync + p.final_phase[k], (unsigned int) p.total_ctas);
         *p.epoch = __ldcg(p.epoch) + 1u;
     }
 }
@@ -1085,7 +1191,7 @@ struct b200_chain {
     unsigned int * d_bar = nullptr;
     int n_gemv = 0, n_attn = 0;
     unsigned long long * d_dbg = nullptr;
-    bool peer = false;                 // row split over peer memory: d_bar belongs to the caller's arena
+    bool peer = false;                 // row split over peer memory
     unsigned int * d_epoch = nullptr;
 };
 
@@ -1120,23 +1226,109 @@ static bool gs_build_attn(const b200_attn_phase * a, gs_phase & ph, int & attn_f
     return true;
 }
 
-static b200_chain * gs_chain_create(const b200_phase * phases, int n_phases, int flags, const b200_peer_group * pg) {
+// ---- row split: who produced what.  Looks backwards from phase i for the matmul whose output lies inside the f32 range
+// [ptr, ptr + n): returns its phase index and the elements [lo, hi) THIS rank computed there (the rest of the range comes
+// from the other ranks); -1: not produced by a row-split matmul of this chain (graph input, attention output: local);
+// -2: an overlap this kernel cannot express.
+static int gs_find_producer(const b200_phase * phases, int i, const void * ptr, int64_t n, int & lo, int & hi) {
+    const char * p0 = (const char *) ptr, * p1 = p0 + 4 * n;
+    for (int j = i - 1; j >= 0; --j) {
+        if (phases[j].kind == B200_PHASE_ATTN) {
+            const b200_tensor & d = phases[j].attn.dst;
+            const char * d0 = (const char *) d.data, * d1 = d0 + 4 * nelements(d);
+            if (d0 < p1 && d1 > p0) return -1;
+            continue;
+        }
+        if (phases[j].kind != B200_PHASE_GEMV) continue;
+        const b200_gemv_fused_args & g = phases[j].gemv;
+        int hits = 0;
+        for (int k = 0; k < g.n_seg && k < B200_GEMV_MAX_SEG; ++k) {
+            if (g.glu_op != B200_GLU_NONE && k == 0) continue;                 // the gate segment has no dst of its own
+            const char * d0 = (const char *) g.seg[k].dst.data;
+            const int64_t M = g.seg[k].w.ne[1];
+            if (!d0) continue;
+            if (d0 >= p0 && d0 < p1 && d0 + 4 * M <= p1) { lo = (int) ((d0 - p0) / 4); hi = lo + (int) M; ++hits; }
+            else if (M > 0 && d0 < p1 && d0 + 4 * M > p0) return -2;
+        }
+        if (hits > 1) return -2;
+        if (hits == 1) return j;
+    }
+    return -1;
+}
+
+static b200_chain * gs_chain_create(const b200_phase * phases_in, int n_phases, int flags, const b200_peer_group * pg) {
+    if (!phases_in || n_phases < 1 || n_phases > GS_MAX_PHASES) { set_error("b200_chain_create: bad phase count"); return nullptr; }
+    std::vector<b200_phase> phv(phases_in, phases_in + n_phases);        // private copy: zero-row segments are removed below
+    struct peer_info { int x_lo = 0, x_hi = 0, x_tag = 0, q[3] = {0, 0, 0}, k[3] = {0, 0, 0}, v[3] = {0, 0, 0}; bool remote_x = false; };
+    std::vector<peer_info> pi((size_t) n_phases);
+    std::vector<char> consumed((size_t) n_phases, 0);
     if (pg) {
         if (pg->n_ranks < 1 || pg->n_ranks > B200_MAX_RANKS || pg->rank < 0 || pg->rank >= pg->n_ranks || pg->delta[pg->rank] != 0 ||
             pg->total_ctas < 1 || !pg->arena || !pg->sync) { set_error("b200_chain_create_peer: bad peer group"); return nullptr; }
         const uintptr_t a0 = (uintptr_t) pg->arena, a1 = a0 + pg->arena_bytes, s0 = (uintptr_t) pg->sync;
-        if (s0 < a0 || s0 + sizeof(unsigned int) * (size_t) std::max(n_phases, 0) > a1 || s0 % 4) { set_error("b200_chain_create_peer: sync counters outside the arena"); return nullptr; }
+        if (pg->act_bytes == 0 || pg->act_bytes % 16 || pg->ll_offset % 16 || pg->ll_offset < pg->act_bytes || pg->ll_offset + 2 * pg->act_bytes > pg->arena_bytes) {
+            set_error("b200_chain_create_peer: bad arena layout (act_bytes / ll_offset)"); return nullptr;
+        }
+        const uintptr_t act1 = a0 + pg->act_bytes;
+        if (s0 < a0 || s0 + sizeof(unsigned int) * (size_t) n_phases > a1 || s0 % 4 ||
+            (s0 < a0 + pg->ll_offset + 2 * pg->act_bytes && s0 + sizeof(unsigned int) * (size_t) n_phases > a0 + pg->ll_offset)) {
+            set_error("b200_chain_create_peer: sync counters outside the arena (or inside the tagged shadow)"); return nullptr;
+        }
         for (int i = 0; i < n_phases; ++i) {
-            if (phases[i].kind != B200_PHASE_GEMV) continue;
-            const b200_gemv_fused_args & g = phases[i].gemv;
-            for (int k = 0; k < g.n_seg && k < B200_GEMV_MAX_SEG; ++k) {
-                if (g.glu_op != B200_GLU_NONE && k == 0) continue;                 // the gate segment has no dst of its own
-                const uintptr_t d0 = (uintptr_t) g.seg[k].dst.data, d1 = d0 + 4 * (size_t) g.seg[k].dst.ne[0];
-                if (d0 < a0 || d1 > a1) { set_error("b200_chain_create_peer: phase %d segment %d: dst outside the symmetric arena", i, k); return nullptr; }
+            const b200_phase & P = phv[i];
+            int lo, hi;
+            if (P.kind == B200_PHASE_GEMV) {
+                const b200_gemv_fused_args & g = P.gemv;
+                if (g.n_seg < 1 || g.n_seg > B200_GEMV_MAX_SEG) { set_error("b200_chain_create_peer: phase %d: bad segment count", i); return nullptr; }
+                for (int k = 0; k < g.n_seg; ++k) {
+                    if (!(g.glu_op != B200_GLU_NONE && k == 0)) {
+                        const uintptr_t d0 = (uintptr_t) g.seg[k].dst.data, d1 = d0 + 4 * (size_t) g.seg[k].w.ne[1];
+                        if (d0 < a0 || d1 > act1) { set_error("b200_chain_create_peer: phase %d segment %d: dst outside the symmetric arena", i, k); return nullptr; }
+                    }
+                    if (g.seg[k].bias) {       // epilogue operands are read as plain memory: they must be rows this rank wrote itself
+                        const int r = gs_find_producer(phv.data(), i, g.seg[k].bias->data, g.seg[k].w.ne[1], lo, hi);
+                        if (r == -2 || (r >= 0 && (lo != 0 || hi != (int) g.seg[k].w.ne[1]))) {
+                            set_error("b200_chain_create_peer: phase %d segment %d: bias rows were not computed by this rank", i, k); return nullptr;
+                        }
+                    }
+                }
+                const int64_t K = g.x.ne[0];
+                const int r = gs_find_producer(phv.data(), i, g.x.data, K, lo, hi);
+                if (r == -2) { set_error("b200_chain_create_peer: phase %d: activation overlaps earlier outputs irregularly", i); return nullptr; }
+                pi[i].x_lo = 0; pi[i].x_hi = (int) K;
+                if (r >= 0) {
+                    if (lo % 4 || hi % 4) { set_error("b200_chain_create_peer: phase %d: row slice not a multiple of 4", i); return nullptr; }
+                    pi[i].x_lo = lo; pi[i].x_hi = hi; pi[i].x_tag = r; consumed[r] = 1;
+                    if ((uintptr_t) g.x.data < a0 || (uintptr_t) g.x.data + 4 * (size_t) K > act1) { set_error("b200_chain_create_peer: phase %d: x outside the arena", i); return nullptr; }
+                }
+            } else if (P.kind == B200_PHASE_ATTN) {
+                const b200_attn_phase & a = P.attn;
+                const b200_tensor * t[3] = {&a.q, &a.k_new, &a.v_new};
+                int * out[3] = {pi[i].q, pi[i].k, pi[i].v};
+                for (int u = 0; u < 3; ++u) {
+                    const int64_t n = nelements(*t[u]);
+                    const int r = gs_find_producer(phv.data(), i, t[u]->data, n, lo, hi);
+                    if (r == -2) { set_error("b200_chain_create_peer: phase %d: q/k/v overlap earlier outputs irregularly", i); return nullptr; }
+                    out[u][0] = 0; out[u][1] = (int) n; out[u][2] = 0;
+                    if (r >= 0) {
+                        out[u][0] = lo; out[u][1] = hi; out[u][2] = r; consumed[r] = 1;
+                        if ((uintptr_t) t[u]->data < a0 || (uintptr_t) t[u]->data + 4 * (size_t) n > act1) { set_error("b200_chain_create_peer: phase %d: q/k/v outside the arena", i); return nullptr; }
+                    }
+                }
             }
         }
+        // a rank may own no rows of a small matrix (split boundaries round down): the segment only described the slice
+        for (int i = 0; i < n_phases; ++i) {
+            if (phv[i].kind != B200_PHASE_GEMV) continue;
+            b200_gemv_fused_args & g = phv[i].gemv;
+            if (g.glu_op != B200_GLU_NONE) { if (g.seg[1].w.ne[1] == 0) phv[i].kind = B200_PHASE_NOP; continue; }
+            int n = 0;
+            for (int k = 0; k < g.n_seg; ++k) if (g.seg[k].w.ne[1] > 0) g.seg[n++] = g.seg[k];
+            g.n_seg = n;
+            if (n == 0) phv[i].kind = B200_PHASE_NOP;
+        }
     }
-    if (!phases || n_phases < 1 || n_phases > GS_MAX_PHASES) { set_error("b200_chain_create: bad phase count"); return nullptr; }
+    const b200_phase * phases = phv.data();
     std::vector<gs_phase> ph((size_t) n_phases);
     int64_t need = 0; int act_qs = 64, attn_floats = 0; int types[2] = {-1, -1};
     b200_chain * ch = new b200_chain;
@@ -1147,6 +1339,27 @@ static b200_chain * gs_chain_create(const b200_phase * phases, int n_phases, int
         else if (phases[i].kind == B200_PHASE_NOP)  { memset(&ph[i], 0, sizeof(gs_phase)); ph[i].kind = 2; ok = true; }
         else ok = false;
         if (!ok) { set_error("b200_chain_create: phase %d is not supported", i); delete ch; return nullptr; }
+        ph[i].x_lo = 0; ph[i].x_hi = ph[i].K; ph[i].self_tag = (uint32_t) i;
+        gs_attn & g = ph[i].attn;
+        if (ph[i].kind == 1) { g.q_lo = g.k_lo = g.v_lo = 0; g.q_hi = g.D * g.H; g.k_hi = g.v_hi = g.D * g.H_kv; }
+    }
+    int n_final = 0, final_phase[4] = {0, 0, 0, 0};
+    if (pg) {
+        for (int i = 0; i < n_phases; ++i) {
+            if (phases_in[i].kind == B200_PHASE_GEMV) {
+                ph[i].x_lo = pi[i].x_lo; ph[i].x_hi = pi[i].x_hi; ph[i].x_tag = (uint32_t) pi[i].x_tag;
+                ph[i].peer_mode = consumed[i] ? 1 : 2;
+                if (!consumed[i]) {
+                    if (n_final == 4) { set_error("b200_chain_create_peer: more than 4 phases whose outputs leave the chain"); delete ch; return nullptr; }
+                    final_phase[n_final++] = i;
+                }
+            } else if (ph[i].kind == 1) {
+                gs_attn & g = ph[i].attn;
+                g.q_lo = pi[i].q[0]; g.q_hi = pi[i].q[1]; g.q_tag = (uint32_t) pi[i].q[2];
+                g.k_lo = pi[i].k[0]; g.k_hi = pi[i].k[1]; g.k_tag = (uint32_t) pi[i].k[2];
+                g.v_lo = pi[i].v[0]; g.v_hi = pi[i].v[1]; g.v_tag = (uint32_t) pi[i].v[2];
+            }
+        }
     }
     gs_config cfg;
     if (types[0] < 0 || !gs_make_config(flags, need, act_qs, attn_floats, cfg)) { set_error("b200_chain_create: no ring configuration fits"); delete ch; return nullptr; }
@@ -1155,7 +1368,7 @@ static b200_chain * gs_chain_create(const b200_phase * phases, int n_phases, int
     cudaGetDevice(&ch->device);
     ch->peer = pg != nullptr;
     if (cudaMalloc((void **) &ch->d_phases, sizeof(gs_phase) * (size_t) n_phases) != cudaSuccess ||
-        (!pg && cudaMalloc((void **) &ch->d_bar, sizeof(unsigned int) * (size_t) n_phases) != cudaSuccess) ||
+        cudaMalloc((void **) &ch->d_bar, sizeof(unsigned int) * (size_t) n_phases) != cudaSuccess ||
         (pg && (cudaMalloc((void **) &ch->d_epoch, sizeof(unsigned int)) != cudaSuccess || cudaMemset(ch->d_epoch, 0, sizeof(unsigned int)) != cudaSuccess)) ||
         cudaMemcpy(ch->d_phases, ph.data(), sizeof(gs_phase) * (size_t) n_phases, cudaMemcpyHostToDevice) != cudaSuccess) {
         set_error("b200_chain_create: device allocation failed"); cudaGetLastError();
@@ -1164,8 +1377,10 @@ static b200_chain * gs_chain_create(const b200_phase * phases, int n_phases, int
     }
     memset(&ch->p, 0, sizeof(ch->p));
     if (pg) {
-        ch->d_bar = pg->sync;
-        ch->p.epoch = ch->d_epoch; ch->p.total_ctas = pg->total_ctas;
+        ch->p.epoch = ch->d_epoch; ch->p.total_ctas = pg->total_ctas; ch->p.sync = pg->sync;
+        ch->p.arena = (const char *) pg->arena; ch->p.ll_base = (char *) pg->arena + pg->ll_offset;
+        ch->p.n_final = n_final;
+        for (int k = 0; k < 4; ++k) ch->p.final_phase[k] = final_phase[k];
         for (int r = 0; r < pg->n_ranks; ++r)
             if (r != pg->rank) ch->p.peer_delta[ch->p.n_peers++] = pg->delta[r];
     }
@@ -1217,8 +1432,13 @@ extern "C" int b200_peer_close(void * ptr) { B200_CUDA_TRY(cudaIpcCloseMemHandle
 extern "C" int b200_chain_launch(b200_chain * ch, void * stream) {
     if (!ch) return B200_ERR_ARG;
     cudaStream_t st = (cudaStream_t) stream;
-    if (ch->peer) return gs_launch_types<2>(ch->p, ch->smem, ch->grid, st, ch->t0, ch->t1);   // counters accumulate: no reset
     B200_CUDA_TRY(cudaMemsetAsync(ch->d_bar, 0, sizeof(unsigned int) * (size_t) ch->p.n_phases, st));
+    if (ch->peer) {
+        // the arrivals of the other ranks for THIS launch cannot come before they have consumed rows this launch produces,
+        // and those of the previous launch were all counted before it ended: resetting here does not race with them
+        B200_CUDA_TRY(cudaMemsetAsync(ch->p.sync, 0, sizeof(unsigned int) * (size_t) ch->p.n_phases, st));
+        return gs_launch_types<2>(ch->p, ch->smem, ch->grid, st, ch->t0, ch->t1);
+    }
     return gs_launch_types<1>(ch->p, ch->smem, ch->grid, st, ch->t0, ch->t1);
 }
 
@@ -1231,6 +1451,6 @@ extern "C" int b200_chain_debug_read(b200_chain * ch, unsigned long long * out, 
 
 extern "C" void b200_chain_destroy(b200_chain * ch) {
     if (!ch) return;
-    cudaFree(ch->d_phases); if (!ch->peer) cudaFree(ch->d_bar); if (ch->d_dbg) cudaFree(ch->d_dbg); if (ch->d_epoch) cudaFree(ch->d_epoch);
+    cudaFree(ch->d_phases); cudaFree(ch->d_bar); if (ch->d_dbg) cudaFree(ch->d_dbg); if (ch->d_epoch) cudaFree(ch->d_epoch);
     delete ch;
 }

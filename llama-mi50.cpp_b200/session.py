@@ -29,6 +29,16 @@ from .gguf_synth import F16, F32, Q8_0
 ROW_ROUND = 128  # reference: split boundaries rounded down to mmq_y rows (ggml-cuda.cu:778-789)
 
 
+class _Addr:
+    """A bare device address where a tensor is expected (capi only calls data_ptr())."""
+
+    def __init__(self, ptr):
+        self._p = ptr
+
+    def data_ptr(self):
+        return self._p
+
+
 def row_split(n_rows: int, world: int, rank: int) -> tuple[int, int]:
     """[lo, hi) of the rows rank owns; equal tensor_split fractions, boundaries rounded down to 128."""
     def bound(r):
@@ -280,14 +290,14 @@ class DecodeSession:
             if world > 1:
                 lo, hi = row_split(dst.numel() if dst is not None else n_full, world, rank)
                 assert hi - lo == M
-                bias = bias.view(-1)[lo:hi] if bias is not None else None
-                dst = dst.view(-1)[lo:hi] if dst is not None else None
+                bias = bias.view(-1)[lo:hi] if bias is not None and M > 0 else None
+                if dst is not None:      # an empty torch slice has no address: a 0-row segment still names where its slice starts
+                    dst = dst.view(-1)[lo:hi] if M > 0 else _Addr(dst.data_ptr() + 4 * lo)
             return (wd, t, M, bias, dst)
 
         def gemv(xin, segs, **kw):
-            segs = [g for g in segs if g[2] > 0]          # a rank may own no rows of a small matrix
-            if not segs:
-                return capi.nop_phase()
+            # under row split a rank may own no rows of a small matrix: the 0-row segment still tells the library which
+            # slice of dst this rank does NOT get from itself
             return capi.gemv_phase(xin.view(-1), segs, keep=keep, **kw)
 
         hb = gguf_synth.row_bytes(self.kv_type, D)
