@@ -176,6 +176,11 @@ B200_API int          b200_chain_debug_read(b200_chain * chain, unsigned long lo
  * out as plain stores followed by one system-scope fence and an arrival on every rank, which the launch waits for
  * before it ends.  No collective, no extra launch.  Attention phases are computed by every rank (replicated KV cache).
  * Epilogue operands (bias / residual) must be rows the rank computed itself.
+ * Why buffers can be reused across layers and launches: a rank enters phase p+1 only after it has read, with matching
+ * tags, the rows every CTA of every other rank produced in phase p, so no rank is more than one phase ahead of the
+ * slowest CTA anywhere; a buffer and its shadow are rewritten five phases later at the earliest, and the next launch
+ * starts only after the final arrival of all ranks.  Tags differ per (launch, phase): a stale word never matches.
+ * Every spin is bounded by wall time (20 s) and traps.
  *
  * Requirements: every rank allocates a "symmetric arena" of the same size with the same layout (b200_peer_alloc),
  * maps the arenas of the others (b200_peer_export / b200_peer_open) and passes delta[r] = arena of rank r - own arena
