@@ -21,977 +21,38 @@
 //     attention phase with RoPE and the KV-cache write fused in) in ONE cooperative launch; phases are separated
 //     by in-kernel grid barriers that only the consumers wait on — the producer keeps streaming the next phase's
 //     weights into the ring, so HBM never drains at a matmul boundary.
-#include <algorithm>
-#include <cstring>
-#include <vector>
-
-#include "quantize.cuh"
-#include "vecdot.cuh"
+#include "gemv_stream.cuh"
 
 namespace b200 {
 
-constexpr int GS_NW          = 16;                     // consumer warps (4 per scheduler)
-constexpr int GS_THREADS     = (GS_NW + 1) * 32;       // + producer warp
-constexpr int GS_CON_THREADS = GS_NW * 32;
-constexpr int GS_PRO_THREADS = GS_CON_THREADS;         // warps that run the prologue (all but the producer)
-constexpr int GS_STAGES      = 3;                      // default ring depth
-constexpr int GS_MAX_STAGES  = 8;
-constexpr int GS_STAGE_BYTES = 56 * 1024;              // preferred stage payload: HBM efficiency needs >= ~32 KB per bulk copy
-constexpr int GS_STAGE_SLACK = 128;                    // slack for 16 B alignment of both ends / funnel over-read
-constexpr int GS_RED_FLOATS  = 2304;                   // per parity: rows * (KS*32 + 4) <= GS_RED_FLOATS
-constexpr int GS_SMEM_MAX    = 220 * 1024;             // dynamic; ~3 KB of static shared memory on top
-constexpr int GS_RB          = 2;                      // rows per warp pass (two independent dp4a chains)
-constexpr int GS_MAX_PHASES  = 1024;
-
-struct gs_seg {
-    const uint8_t * w[2];     // [1] = paired "up" matrix of a GLU work segment (else null)
-    const float *   bias;
-    float *         dst;
-    int64_t         byte_prefix;   // bytes of the work segments before this one
-    int32_t M, rb, type, nsub;     // rows, row bytes, ggml type, 1 (or 2 for a GLU pair)
-    int32_t R, KS, spr, ipr;       // rows per chunk, warps along K, steps per row, items per row
-    int32_t spw, _pad;             // K-steps per warp (1, 2 or 4): the per-step activation registers are hoisted
-};
-// attention phase of the decode chain: one query position, f16 KV cache, RoPE + KV-cache write fused in
-struct gs_attn {
-    const float * q; const float * k_new; const float * v_new;   // raw projections of the current token
-    char * k_cache; char * v_cache; const __half * mask; float * dst;
-    const int32_t * pos; const int64_t * slot; const int64_t * slot_v;
-    int64_t k_nb1, k_nb2, v_nb1, v_nb2;
-    int32_t D, H, H_kv, n_kv, rope_mode, n_dims;
-    float scale, theta_scale, freq_scale;
-    // row split: elements [lo, hi) of q / k_new / v_new were computed by this rank (plain memory, after the local
-    // barrier); the rest arrives from the other ranks as tagged words.  *_tag: index of the producing phase
-    int32_t q_lo, q_hi, k_lo, k_hi, v_lo, v_hi;
-    uint32_t q_tag, k_tag, v_tag;
-};
-struct alignas(16) gs_phase {
-    int32_t kind;                  // 0 = GEMV, 1 = attention
-    int32_t n_ws;                  // work segments (GEMV)
-    gs_seg seg[B200_GEMV_MAX_SEG];
-    int32_t glu_op; float glu_alpha, glu_limit;
-    const float * x; const float * norm_w; float eps; int32_t K;
-    blk_q8_1 * xq_out;
-    int64_t total_bytes;
-    // row split: x[x_lo, x_hi) is local, the rest are tagged words written by the other ranks in phase x_tag.
-    // peer_mode: how this phase's outputs reach the other ranks: 0 not at all, 1 tagged words (read by a later phase),
-    // 2 plain stores + system-scope arrival (read after the launch: the logits)
-    int32_t x_lo, x_hi; uint32_t x_tag; int32_t peer_mode;
-    uint32_t self_tag; int32_t _pad2[3];      // index of this phase (added to the launch tag for its own tagged stores)
-    gs_attn attn;
-};
-struct gs_params {
-    gs_phase inl;                  // the phase of a single-phase launch (b200_gemv_fused)
-    const gs_phase * phases;       // device array for a chain (null: use inl)
-    unsigned int * bar;            // one arrival counter per phase (zeroed before the launch)
-    int32_t n_phases;
-    int32_t act_qs_bytes;          // activation region sized for the largest K of the chain
-    int32_t stage_stride;          // bytes between ring stages (payload + GS_STAGE_SLACK, multiple of 128)
-    int32_t n_stages;              // ring depth
-    int32_t attn_floats;           // attention scratch (floats) after the activation scales
-    int32_t flags;                 // tuning/debug: bit 0 = consumers skip the dot products (bandwidth probe)
-    unsigned long long * dbg;      // flags bit 2: globaltimer stamps [phase][cta 0 | last cta][4]
-    // ---- row split over peer memory (MODE 2): outputs and barrier arrivals are mirrored to the other ranks
-    int32_t n_peers;               // other ranks
-    int32_t total_ctas;            // CTAs of all ranks: arrivals per phase and launch
-    int64_t peer_delta[B200_MAX_RANKS - 1];   // byte offset from a local arena address to the same location on peer r
-    unsigned int * epoch;          // launches completed so far on this rank: tags of different launches differ
-    unsigned int * sync;           // arena: arrival counters of the peer_mode 2 phases (all ranks' CTAs)
-    const char * arena;            // local arena base and its shadow of tagged words: the word of the f32 at arena + o
-    char * ll_base;                //   is at ll_base + 2 * o
-    int32_t n_final; int32_t final_phase[4];   // peer_mode 2 phases the launch waits for before it ends
-};
-
-// ---------------------------------------------------------------- PTX helpers
-__device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t * b, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t * b) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t * b, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t * b, uint32_t parity) {
-    const uint32_t a = smem_u32(b);
-    uint32_t ok;
-    do {
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(ok) : "r"(a), "r"(parity) : "memory");
-    } while (!ok);
-}
-// 1-D TMA bulk copy global -> shared, completion counted in bytes on an mbarrier; weights are read once: evict-first in L2
-__device__ __forceinline__ void bulk_g2s(void * dst, const void * src, uint32_t bytes, uint64_t * bar, uint64_t policy) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
-                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy) : "memory");
-}
-__device__ __forceinline__ uint64_t policy_evict_first() {
-    uint64_t p;
-    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
-    return p;
-}
-__device__ __forceinline__ void named_bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
-
-// ---- tagged words (row split over peer memory): a value and the tag of the (launch, phase) that produced it travel in
-// ONE 64-bit store, so a reader that sees the tag has the value: one NVLink traversal, no fence round trip, no counter
-// (the idea of NCCL's LL protocol).  Spins are bounded: a rank that never delivers becomes a trap, not a hung GPU.
-__device__ __forceinline__ void ll_store(void * p, float v, unsigned int tag) {
-    const unsigned long long w = (unsigned long long) __float_as_uint(v) | ((unsigned long long) tag << 32);
-    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
-}
-__device__ __forceinline__ unsigned long long ll_load1(const void * p) {
-    unsigned long long w;
-    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
-    return w;
-}
-__device__ __forceinline__ ulonglong2 ll_load2(const void * p) {      // two elements, 16 B aligned
-    ulonglong2 r;
-    asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(r.x), "=l"(r.y) : "l"(p) : "memory");
-    return r;
-}
-__device__ __forceinline__ bool ll_ok(unsigned long long w, unsigned int tag) { return (unsigned int) (w >> 32) == tag; }
-__device__ __forceinline__ void ll_spin_check(unsigned int & spins, unsigned long long & t0) {
-    if ((++spins & 0x3FFu) == 0) {
-        unsigned long long now;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-        if (!t0) t0 = now; else if (now - t0 > 20000000000ull) __trap();          // 20 s
-    }
-}
-__device__ __forceinline__ float ll_read(const void * p, unsigned int tag) {
-    unsigned long long w = ll_load1(p);
-    unsigned int spins = 0; unsigned long long t0 = 0;
-    while (!ll_ok(w, tag)) { ll_spin_check(spins, t0); w = ll_load1(p); }
-    return __uint_as_float((unsigned int) w);
-}
-__device__ __forceinline__ void ll_settle2(ulonglong2 & a, const void * p, unsigned int tag) {
-    unsigned int spins = 0; unsigned long long t0 = 0;
-    while (!ll_ok(a.x, tag) || !ll_ok(a.y, tag)) { ll_spin_check(spins, t0); a = ll_load2(p); }
-}
-
-// N consecutive little-endian u32 words starting at an arbitrarily aligned shared-memory byte address
-template <int N>
-__device__ __forceinline__ void lds_words(const uint8_t * p, uint32_t * out) {
-    const uint32_t a  = smem_u32(p);
-    const uint32_t sh = (a & 3u) * 8u;
-    const uint32_t * q = (const uint32_t *) (p - (a & 3u));
-    uint32_t w[N + 1];
-#pragma unroll
-    for (int i = 0; i <= N; ++i) w[i] = q[i];
-#pragma unroll
-    for (int i = 0; i < N; ++i) out[i] = __funnelshift_r(w[i], w[i + 1], sh);
-}
-
-// activation layout in shared memory: unit u (32 int8) at byte u*32 + (u/4)*16  (16 B pad every 128 B:
-// the 8 lanes of a quarter-warp then hit 8 distinct 16-byte bank groups for every item shape used below)
-__device__ __forceinline__ int act_off(int u) { return u * 32 + (u >> 2) * 16; }
-
-// ---------------------------------------------------------------- per-type ITEMS
-// An ITEM is the work of one lane in one K-step of a row: 64 weights (k-quants) or 32 weights.  The lane
-// handles the SAME item index for every row it ever sees in a segment, so everything that depends only on
-// the item — the q8_1 activation values, their scales, field offsets, scale-decode shifts — is loaded ONCE
-// per segment into registers (item<TYPE>::init); the per-row work is then loads of weight bytes + dp4a.
-__device__ __forceinline__ int dp4a_us(uint32_t a, int b, int c) {      // unsigned bytes x signed bytes
-    int d;
-    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
-    return d;
-}
-
-template <int TYPE> struct item;
-
-// ---- Q4_K: item = (super-block sb, 32-byte nibble group p): sub-blocks 2p (low nibbles) and 2p+1 (high nibbles)
-template <> struct item<B200_Q4_K> {
-    static constexpr int wpi = 64, max_spw = 2;
-    int au[16]; float d0, s0, d1, s1;     // d1 is pre-divided by 16: the high nibbles are used unshifted (x16)
-    int hoff, qoff; uint32_t shs, shm, m1, m2; bool hi, ok;
-    __device__ __forceinline__ void init(int it, int ipr, const uint8_t * aq, const float2 * ads) {
-        ok = it < ipr;
-        const int itc = ok ? it : 0;
-        const int sb = itc >> 2, p = itc & 3, u0 = sb * 8 + 2 * p;
-        const int4 a0 = *(const int4 *) (aq + act_off(u0)),      a1 = *(const int4 *) (aq + act_off(u0) + 16);
-        const int4 a2 = *(const int4 *) (aq + act_off(u0) + 32), a3 = *(const int4 *) (aq + act_off(u0) + 48);
-        au[0] = a0.x; au[1] = a0.y; au[2] = a0.z; au[3] = a0.w; au[4] = a1.x; au[5] = a1.y; au[6] = a1.z; au[7] = a1.w;
-        au[8] = a2.x; au[9] = a2.y; au[10] = a2.z; au[11] = a2.w; au[12] = a3.x; au[13] = a3.y; au[14] = a3.z; au[15] = a3.w;
-        const float4 ds = *(const float4 *) (ads + u0);
-        d0 = ds.x; s0 = ds.y; d1 = ds.z * 0.0625f; s1 = ds.w;
-        hoff = sb * 144; qoff = hoff + 16 + 32 * p;      // super-block header {dm, scales[12]}; this item's 32 nibble bytes
-        // 6-bit (scale, min) of sub-blocks 2p, 2p+1 (get_scale_min_k4, ggml-quants.c): branch-free per-lane constants
-        hi = p >= 2;
-        shs = hi ? 16 * (p - 2) : 16 * p;    // byte pair position inside the source word
-        shm = hi ? shs + 4 : shs;
-        m1 = hi ? 0x0F0Fu : 0x3F3Fu; m2 = hi ? 0x3030u : 0u;
-    }
-    template <int RB>
-    __device__ __forceinline__ void dot(const uint8_t * const * rowp, float * acc) const {
-#pragma unroll
-        for (int j = 0; j < RB; ++j) {
-            const uint4 hdr = *(const uint4 *) (rowp[j] + hoff);
-            const uint4 q0 = *(const uint4 *) (rowp[j] + qoff), q1 = *(const uint4 *) (rowp[j] + qoff + 16);
-            const uint32_t q[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
-            int sl = 0, sh = 0;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                sl = __dp4a((int) (q[i] & 0x0F0F0F0Fu), au[i], sl);
-                sh = dp4a_us(q[i] & 0xF0F0F0F0u, au[8 + i], sh);
-            }
-            const uint32_t xs = hi ? hdr.w : hdr.y, xm = hi ? hdr.w : hdr.z;
-            const uint32_t sc = ((xs >> shs) & m1) | ((hdr.y >> (shs + 2)) & m2);
-            const uint32_t mn = ((xm >> shm) & m1) | ((hdr.z >> (shs + 2)) & m2);
-            const float2 dm = __half22float2(*(const __half2 *) &hdr.x);
-            const float t = (float) ((int) (sc & 0xFF) * sl) * d0 + (float) ((int) (sc >> 8) * sh) * d1;
-            const float m = (float) (mn & 0xFF) * s0 + (float) (mn >> 8) * s1;
-            acc[j] += dm.x * t - dm.y * m;
-        }
-    }
-};
-
-// ---- Q6_K: item = (super-block, half h, 16-column group c): 16 weights of each of the 4 sub-blocks of the half.
-// q = lo4 | hi2<<4 (0..63), value q-32:  sum (q-32)u = sum lo4*u + 16*sum hi2*u - 32*sum u; nibbles / bit pairs are used
-// unshifted with unsigned dp4a and the power-of-two factors folded into per-item float constants.
-template <> struct item<B200_Q6_K> {
-    static constexpr int wpi = 64, max_spw = 2;
-    int a[4][4]; float dl[4], dh[4], su[4];   // per sub-block r: d8/16^(r>>1), d8*16/4^r, 32*d8*sum(u over the 16 columns)
-    int off_l, off_h, off_s, off_d; bool ok;
-    __device__ __forceinline__ void init(int it, int ipr, const uint8_t * aq, const float2 * ads) {
-        // lane -> quad (sb, h) in the low 4 lane bits, column group c in bit 4 (keeps activation reads conflict-free)
-        const int step = it >> 5, l = it & 31;
-        int quad = step * 16 + (l & 15);
-        const int c = l >> 4;
-        ok = quad < (ipr >> 1);
-        if (!ok) quad = 0;
-        const int sb = quad >> 1, h = quad & 1, u0 = sb * 8 + 4 * h;
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            const int4 t = *(const int4 *) (aq + act_off(u0 + r) + 16 * c);
-            a[r][0] = t.x; a[r][1] = t.y; a[r][2] = t.z; a[r][3] = t.w;
-            const float d8 = ads[u0 + r].x;
-            int s = 0;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) s = __dp4a(0x01010101, a[r][i], s);
-            dl[r] = (r >> 1) ? d8 * 0.0625f : d8;
-            dh[r] = d8 * 16.0f / (float) (1 << (2 * r));
-            su[r] = 32.0f * d8 * (float) s;
-        }
-        off_l = sb * 210 + 64 * h + 16 * c; off_h = sb * 210 + 128 + 32 * h + 16 * c;
-        off_s = sb * 210 + 192 + 8 * h + c; off_d = sb * 210 + 208;
-    }
-    template <int RB>
-    __device__ __forceinline__ void dot(const uint8_t * const * rowp, float * acc) const {
-#pragma unroll
-        for (int j = 0; j < RB; ++j) {
-            const uint8_t * b = rowp[j];
-            uint32_t la[4], lb[4], hh[4];
-            lds_words<4>(b + off_l, la);            // ql: low nibbles -> r=0, high -> r=2
-            lds_words<4>(b + off_l + 32, lb);       //                    r=1,         r=3
-            lds_words<4>(b + off_h, hh);            // qh: 2 bits per r
-            const int8_t * sc = (const int8_t *) (b + off_s);
-            const float d = __half2float(*(const __half *) (b + off_d));
-            float part = 0.0f;
-#pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                int sl = 0, sh = 0;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const uint32_t w = (r & 1) ? lb[i] : la[i];
-                    sl = dp4a_us(w & ((r >> 1) ? 0xF0F0F0F0u : 0x0F0F0F0Fu), a[r][i], sl);
-                    sh = dp4a_us(hh[i] & (0x03030303u << (2 * r)), a[r][i], sh);
-                }
-                part += (float) sc[2 * r] * ((float) sl * dl[r] + (float) sh * dh[r] - su[r]);
-            }
-            acc[j] += d * part;
-        }
-    }
-};
-
-// ---- 32-weight block formats: item = block index
-template <> struct item<B200_Q4_0> {
-    static constexpr int wpi = 32, max_spw = 4;
-    int au[8]; float d8, d8h, s8; int off; bool ok;
-    __device__ __forceinline__ void init(int it, int ipr, const uint8_t * aq, const float2 * ads) {
-        ok = it < ipr; const int u = ok ? it : 0;
-        const int4 a0 = *(const int4 *) (aq + act_off(u)), a1 = *(const int4 *) (aq + act_off(u) + 16);
-        au[0] = a0.x; au[1] = a0.y; au[2] = a0.z; au[3] = a0.w; au[4] = a1.x; au[5] = a1.y; au[6] = a1.z; au[7] = a1.w;
-        const float2 ds = ads[u];
-        d8 = ds.x; d8h = ds.x * 0.0625f; s8 = 8.0f * ds.y; off = u * 18;
-    }
-    template <int RB>
-    __device__ __forceinline__ void dot(const uint8_t * const * rowp, float * acc) const {
-#pragma unroll
-        for (int j = 0; j < RB; ++j) {
-            const uint8_t * b = rowp[j] + off;
-            uint32_t q[4];
-            lds_words<4>(b + 2, q);
-            int sl = 0, sh = 0;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                sl = __dp4a((int) (q[i] & 0x0F0F0F0Fu), au[i], sl);
-                sh = dp4a_us(q[i] & 0xF0F0F0F0u, au[4 + i], sh);
-            }
-            const float d = __half2float(*(const __half *) b);
-            acc[j] += d * ((float) sl * d8 + (float) sh * d8h - s8);      // sum (q-8)u = sum q*u - 8*sum u
-        }
-    }
-};
-
-template <> struct item<B200_Q8_0> {
-    static constexpr int wpi = 32, max_spw = 4;
-    int au[8]; float d8; int off; bool ok;
-    __device__ __forceinline__ void init(int it, int ipr, const uint8_t * aq, const float2 * ads) {
-        ok = it < ipr; const int u = ok ? it : 0;
-        const int4 a0 = *(const int4 *) (aq + act_off(u)), a1 = *(const int4 *) (aq + act_off(u) + 16);
-        au[0] = a0.x; au[1] = a0.y; au[2] = a0.z; au[3] = a0.w; au[4] = a1.x; au[5] = a1.y; au[6] = a1.z; au[7] = a1.w;
-        d8 = ads[u].x; off = u * 34;
-    }
-    template <int RB>
-    __device__ __forceinline__ void dot(const uint8_t * const * rowp, float * acc) const {
-#pragma unroll
-        for (int j = 0; j < RB; ++j) {
-            const uint8_t * b = rowp[j] + off;
-            uint32_t q[8];
-            lds_words<8>(b + 2, q);
-            int s = 0;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) s = __dp4a((int) q[i], au[i], s);
-            acc[j] += __half2float(*(const __half *) b) * (float) s * d8;
-        }
-    }
-};
-
-template <> struct item<B200_MXFP4> {
-    static constexpr int wpi = 32, max_spw = 4;
-    int au[8]; float d8; int off; bool ok;
-    __device__ __forceinline__ void init(int it, int ipr, const uint8_t * aq, const float2 * ads) {
-        ok = it < ipr; const int u = ok ? it : 0;
-        const int4 a0 = *(const int4 *) (aq + act_off(u)), a1 = *(const int4 *) (aq + act_off(u) + 16);
-        au[0] = a0.x; au[1] = a0.y; au[2] = a0.z; au[3] = a0.w; au[4] = a1.x; au[5] = a1.y; au[6] = a1.z; au[7] = a1.w;
-        d8 = ads[u].x; off = u * 17;
-    }
-    template <int RB>
-    __device__ __forceinline__ void dot(const uint8_t * const * rowp, float * acc) const {
-#pragma unroll
-        for (int j = 0; j < RB; ++j) {
-            const uint8_t * b = rowp[j] + off;
-            uint32_t q[4];
-            lds_words<4>(b + 1, q);
-            int s = 0;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                int lo, hi;
-                mxfp4_expand(q[i], lo, hi);
-                s = __dp4a(lo, au[i], s);
-                s = __dp4a(hi, au[4 + i], s);
-            }
-            acc[j] += e8m0_half_to_f32(b[0]) * (float) s * d8;
-        }
-    }
-};
-
-__device__ __forceinline__ float gs_glu(int op, float g, float x, float alpha, float limit) {
-    switch (op) {
-        case B200_GLU_REGLU:  return fmaxf(g, 0.0f) * x;
-        case B200_GLU_GEGLU: { const float c = 0.79788456080286535587989211986876f, a = 0.044715f;
-                               return 0.5f * g * (1.0f + tanhf(c * g * (1.0f + a * g * g))) * x; }
-        case B200_GLU_SWIGLU: return g / (1.0f + expf(-g)) * x;
-        case B200_GLU_SWIGLU_OAI: g = fminf(g, limit); x = fmaxf(fminf(x, limit), -limit); return g / (1.0f + expf(-g * alpha)) * (1.0f + x);
-        case B200_GLU_GEGLU_ERF:   return 0.5f * g * (1.0f + erff(g * 0.70710678118654752440f)) * x;
-        case B200_GLU_GEGLU_QUICK: return g / (1.0f + expf(-1.702f * g)) * x;
-        default: return x;
-    }
-}
-
-// ring position carried by the producer and the consumers across the segments and phases of a launch
-struct gs_pos {
-    int st = 0, full_par = 0;      // ring stage, parity of its "full" phase
-    int ns = GS_STAGES;
-    __device__ __forceinline__ void next() { if (++st == ns) { st = 0; full_par ^= 1; } }
-};
-
-struct gs_shared {
-    uint64_t full[GS_MAX_STAGES], empty[GS_MAX_STAGES];
-    float part[GS_NW];
-    float slots[2][GS_NW][GS_RB];  // per-warp row sums of a pass, combined across the KS warps of a row group
-    unsigned int tag;              // row split: tag of this launch (phase index is added)
-};
-
-struct gs_ctx {                    // per-thread view of the launch-wide shared memory carve-up
-    uint8_t * ring; uint8_t * aq; float2 * ads; float * attn; gs_shared * sh;
-    int stage_stride, flags;
-};
-
-__device__ __forceinline__ void gs_row_range(const gs_seg & sg, int64_t lo, int64_t hi, int & r0, int & r1) {
-    const int64_t rbw = (int64_t) sg.rb * sg.nsub, tot = rbw * sg.M;
-    const int64_t a = min(max(lo - sg.byte_prefix, (int64_t) 0), tot), b = min(max(hi - sg.byte_prefix, (int64_t) 0), tot);
-    r0 = (int) ((a + rbw - 1) / rbw); r1 = (int) ((b + rbw - 1) / rbw);
-}
-
-// consumer warps: all chunks of one work segment.  A pass of a warp covers GS_RB rows (for a GLU pair: the gate row and the
-// up row of ONE output row); the KS warps of a row group each own a K slice, reduce their lanes by shuffles and meet at a
-// named barrier of their own; warp ks == 0 sums the KS values in fixed order, applies the epilogue and stores.
-// one output value: the local store and, under row split, the same store into every peer's copy of the buffer
-template <bool PEER>
-__device__ __forceinline__ void gs_put(const gs_params & p, const gs_phase & ph, const gs_shared & sh, float * d, float v) {
-    *d = v;
-    if (PEER) {
-        if (ph.peer_mode == 1) {
-            char * l = p.ll_base + 2 * ((const char *) d - p.arena);
-            const unsigned int tag = sh.tag + ph.self_tag;
-#pragma unroll
-            for (int r = 0; r < B200_MAX_RANKS - 1; ++r)
-                if (r < p.n_peers) ll_store(l + p.peer_delta[r], v, tag);
-        } else if (ph.peer_mode == 2) {
-#pragma unroll
-            for (int r = 0; r < B200_MAX_RANKS - 1; ++r)
-                if (r < p.n_peers) *(float *) ((char *) d + p.peer_delta[r]) = v;
-        }
-    }
-}
-
-template <int TYPE, int SPW, bool COHERENT, bool PEER>
-__device__ __forceinline__ void consume_segment(const gs_params & p, const gs_ctx & c, const gs_phase & ph, const gs_seg & sg, int r0, int r1, gs_pos & pos, int warp, int lane) {
-    const int KS = sg.KS, ksl = 31 - __clz(KS), ks = warp & (KS - 1), rg = warp >> ksl, RG = GS_NW >> ksl;
-    item<TYPE> itm[SPW];
-#pragma unroll
-    for (int s = 0; s < SPW; ++s) itm[s].init((ks + s * KS) * 32 + lane, sg.ipr, c.aq, c.ads);
-    const int rb = sg.rb, R = sg.R;
-    const bool pair = sg.nsub == 2;
-    const int rpp = pair ? 1 : (R >= GS_RB ? GS_RB : 1);   // output rows per warp pass
-    const int RGP = RG * rpp;                              // output rows per CTA pass
-    int off = 0;                                           // (row - r0) mod RGP: row groups rotate through the chunks, so a
-                                                           // chunk shorter than a CTA pass does not leave the same warps idle
-    const float * __restrict__ bias = sg.bias;
-    float * __restrict__ dst = sg.dst;
-    const int glu_op = ph.glu_op; const float glu_alpha = ph.glu_alpha, glu_limit = ph.glu_limit;
-    uint32_t ga0 = (uint32_t) ((uintptr_t) (sg.w[0] + (int64_t) r0 * rb) & 15);
-    uint32_t ga1 = pair ? (uint32_t) ((uintptr_t) (sg.w[1] + (int64_t) r0 * rb) & 15) : 0u;
-    const uint32_t gstep = (uint32_t) R * (uint32_t) rb;
-    gs_shared & sh = *c.sh;
-    int par = 0;
-    for (int row = r0; row < r1; row += R) {
-        const int nr = min(R, r1 - row);
-        const uint8_t * sub0 = c.ring + pos.st * c.stage_stride + ga0;
-        const uint8_t * sub1 = sub0 - ga0 + ((ga0 + (uint32_t) nr * rb + 15u) & ~15u) + ga1;
-        mbar_wait(&sh.full[pos.st], pos.full_par);
-        int jb0 = rg * rpp - off; if (jb0 < 0) jb0 += RGP;
-        off += R; while (off >= RGP) off -= RGP;
-        for (int jb = jb0; jb < nr; jb += RGP) {
-            const uint8_t * rowp[GS_RB];
-            if (pair) { rowp[0] = sub0 + jb * rb; rowp[1] = sub1 + jb * rb; }
-            else {
-#pragma unroll
-                for (int j = 0; j < GS_RB; ++j) rowp[j] = sub0 + min(jb + j, nr - 1) * rb;     // clamp: a duplicate row is computed and dropped
-            }
-            float bv[GS_RB];                               // epilogue operand, requested before the dot products
-#pragma unroll
-            for (int j = 0; j < GS_RB; ++j) {
-                bv[j] = 0.0f;
-                if (bias && ks == 0 && lane == 0 && j < rpp && jb + j < nr) bv[j] = COHERENT ? __ldcg(bias + row + jb + j) : bias[row + jb + j];
-            }
-            float acc[GS_RB];
-#pragma unroll
-            for (int j = 0; j < GS_RB; ++j) acc[j] = 0.0f;
-            if (!(c.flags & 1)) {
-#pragma unroll
-                for (int s = 0; s < SPW; ++s)
-                    if (itm[s].ok) itm[s].template dot<GS_RB>(rowp, acc);
-            }
-#pragma unroll
-            for (int j = 0; j < GS_RB; ++j) acc[j] = warp_sum(acc[j]);
-            if (KS > 1) {
-                if (lane == 0) {
-#pragma unroll
-                    for (int j = 0; j < GS_RB; ++j) sh.slots[par][warp][j] = acc[j];
-                }
-                named_bar_sync(4 + rg, KS * 32);
-                if (ks == 0 && lane == 0) {
-#pragma unroll
-                    for (int j = 0; j < GS_RB; ++j) {
-                        float t = 0.0f;
-                        for (int k = 0; k < KS; ++k) t += sh.slots[par][warp + k][j];
-                        acc[j] = t;
-                    }
-                }
-                par ^= 1;
-            }
-            if (ks == 0 && lane == 0) {
-                if (pair) {
-                    gs_put<PEER>(p, ph, sh, dst + row + jb, gs_glu(glu_op, acc[0], acc[1], glu_alpha, glu_limit) + bv[0]);
-                } else {
-#pragma unroll
-                    for (int j = 0; j < GS_RB; ++j)
-                        if (j < rpp && jb + j < nr) gs_put<PEER>(p, ph, sh, dst + row + jb + j, acc[j] + bv[j]);
-                }
-            }
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&sh.empty[pos.st]);
-        pos.next();
-        ga0 = (ga0 + gstep) & 15u; ga1 = (ga1 + gstep) & 15u;
-    }
-}
-
-template <int TYPE, bool COHERENT, bool PEER>
-__device__ __forceinline__ void consume_dispatch(const gs_params & p, const gs_ctx & c, const gs_phase & ph, const gs_seg & sg, int r0, int r1, gs_pos & pos, int warp, int lane) {
-    if (sg.spw == 1)      consume_segment<TYPE, 1, COHERENT, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
-    else if (sg.spw == 2) consume_segment<TYPE, 2, COHERENT, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
-    else if (item<TYPE>::max_spw >= 4)
-        consume_segment<TYPE, (item<TYPE>::max_spw >= 4 ? 4 : 1), COHERENT, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
-}
-
-// ---------------------------------------------------------------- phase pieces
-// prologue of a GEMV phase (consumers + finalizer): x -> [rms norm * w] -> q8_1 in shared memory.
-// COHERENT selects L2-coherent loads: inside a chain x was written by other SMs during this launch.
-template <bool COHERENT>
-__device__ __forceinline__ float4 gs_ld4(const float * p) {
-    return COHERENT ? __ldcg((const float4 *) p) : *(const float4 *) p;
-}
-// four consecutive elements of a row-split activation that another rank computed: spin on their tags
-__device__ __forceinline__ float4 ll_read4(const char * l, unsigned int tag) {
-    ulonglong2 a = ll_load2(l), b = ll_load2(l + 16);
-    ll_settle2(a, l, tag); ll_settle2(b, l + 16, tag);
-    return make_float4(__uint_as_float((unsigned int) a.x), __uint_as_float((unsigned int) a.y),
-                       __uint_as_float((unsigned int) b.x), __uint_as_float((unsigned int) b.y));
-}
-template <bool COHERENT, bool PEER>
-__device__ __forceinline__ void gs_prologue(const gs_params & p, const gs_ctx & c, const gs_phase & ph, int warp, int lane) {
-    const int K = ph.K, nblk = K >> 5;
-    // row split: elements outside [x_lo, x_hi) come from the other ranks as tagged words
-    const bool has_remote = PEER && (ph.x_lo > 0 || ph.x_hi < K);
-    const char * xl = PEER ? p.ll_base + 2 * ((const char *) ph.x - p.arena) : nullptr;
-    const unsigned int xtag = PEER ? c.sh->tag + ph.x_tag : 0u;
-    auto remote = [&](int e) { return has_remote && (e < ph.x_lo || e >= ph.x_hi); };
-    const float * __restrict__ x = ph.x;
-    const float * __restrict__ nw = ph.norm_w;
-    blk_q8_1 * xq_out = blockIdx.x == 0 ? ph.xq_out : nullptr;
-    const int pw = warp;                                        // prologue warps = the consumer warps
-    gs_shared & sh = *c.sh;
-    const int sub = lane & 7, bw = lane >> 3;                   // 8 lanes per 32-element block, 4 blocks per warp pass
-    constexpr int BPP = GS_NW * 4;                              // blocks per pass of the prologue warps
-    constexpr int NV = 8;                                       // passes whose x values stay in registers
-
-    auto quant_store = [&](int blk, bool act, float4 t, float4 w, float scale) {
-        float v[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-        if (act) {
-            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-            if (nw) {                                           // same op order as rms_norm then mul: (x*scale)*w
-                v[0] = __fmul_rn(__fmul_rn(v[0], scale), w.x); v[1] = __fmul_rn(__fmul_rn(v[1], scale), w.y);
-                v[2] = __fmul_rn(__fmul_rn(v[2], scale), w.z); v[3] = __fmul_rn(__fmul_rn(v[3], scale), w.w);
-            }
-        }
-        float d; int sum;
-        const int q = quantize_block32_quad<8>(v, d, sum);
-        if (act) {
-            *(int *) (c.aq + act_off(blk) + sub * 4) = q;
-            if (sub == 0) {
-                const float dh = __half2float(__float2half_rn(d));          // the value a q8_1 block stores
-                c.ads[blk] = make_float2(dh, dh * (float) sum);
-            }
-            if (xq_out) {
-                int * out = (int *) (xq_out + blk);
-                out[1 + sub] = q;
-                if (sub == 0) *(__half2 *) out = q8_1_scales(d, sum);
-            }
-        }
-    };
-
-    if (nblk <= BPP * NV) {
-        // ---- all loads first (one L2 round trip), values stay in registers for both passes
-        float4 xv[NV], wv[NV];
-#pragma unroll
-        for (int it = 0; it < NV; ++it) {
-            const int blk = pw * 4 + bw + it * BPP;
-            xv[it] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); wv[it] = xv[it];
-            if (blk < nblk) {
-                if (!remote(blk * 32 + sub * 4)) xv[it] = gs_ld4<COHERENT>(x + blk * 32 + sub * 4);
-                if (nw) wv[it] = *(const float4 *) (nw + blk * 32 + sub * 4);
-            }
-        }
-        if (has_remote) {
-#pragma unroll
-            for (int it0 = 0; it0 < NV; it0 += 2) {                        // two passes (four 16 B loads) in flight per thread
-                ulonglong2 a[2], b[2];
-#pragma unroll
-                for (int u = 0; u < 2; ++u) {
-                    const int e = (pw * 4 + bw + (it0 + u) * BPP) * 32 + sub * 4;
-                    a[u] = make_ulonglong2(0, 0); b[u] = a[u];
-                    if (e < K && remote(e)) { a[u] = ll_load2(xl + 8 * (int64_t) e); b[u] = ll_load2(xl + 8 * (int64_t) e + 16); }
-                }
-#pragma unroll
-                for (int u = 0; u < 2; ++u) {
-                    const int e = (pw * 4 + bw + (it0 + u) * BPP) * 32 + sub * 4;
-                    if (e < K && remote(e)) {
-                        ll_settle2(a[u], xl + 8 * (int64_t) e, xtag); ll_settle2(b[u], xl + 8 * (int64_t) e + 16, xtag);
-                        xv[it0 + u] = make_float4(__uint_as_float((unsigned int) a[u].x), __uint_as_float((unsigned int) a[u].y),
-                                                  __uint_as_float((unsigned int) b[u].x), __uint_as_float((unsigned int) b[u].y));
-                    }
-                }
-            }
-        }
-        float scale = 1.0f;
-        if (nw) {
-            float ss = 0.0f;
-#pragma unroll
-            for (int it = 0; it < NV; ++it) ss += xv[it].x * xv[it].x + xv[it].y * xv[it].y + xv[it].z * xv[it].z + xv[it].w * xv[it].w;
-            ss = warp_sum(ss);
-            if (lane == 0) sh.part[pw] = ss;
-            named_bar_sync(1, GS_PRO_THREADS);
-            float tot = 0.0f;
-#pragma unroll
-            for (int i = 0; i < GS_NW; ++i) tot += sh.part[i];
-            scale = rsqrtf(tot / (float) K + ph.eps);
-        }
-#pragma unroll
-        for (int it = 0; it < NV; ++it) {
-            const int b0 = pw * 4 + it * BPP;                   // warp-uniform
-            if (b0 < nblk) quant_store(b0 + bw, b0 + bw < nblk, xv[it], wv[it], scale);
-        }
-    } else {
-        // ---- long rows: two passes over x
-        const int ptid = pw * 32 + lane;
-        float scale = 1.0f;
-        if (nw) {
-            float ss = 0.0f;
-            for (int i = ptid * 4; i < K; i += GS_PRO_THREADS * 4) {
-                const float4 v = remote(i) ? ll_read4(xl + 8 * (int64_t) i, xtag) : gs_ld4<COHERENT>(x + i);
-                ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
-            }
-            ss = warp_sum(ss);
-            if (lane == 0) sh.part[pw] = ss;
-            named_bar_sync(1, GS_PRO_THREADS);
-            float tot = 0.0f;
-#pragma unroll
-            for (int i = 0; i < GS_NW; ++i) tot += sh.part[i];
-            scale = rsqrtf(tot / (float) K + ph.eps);
-        }
-        for (int b0 = pw * 4; b0 < nblk; b0 += BPP) {
-            const int blk = b0 + bw;
-            const bool act = blk < nblk;
-            float4 t = make_float4(0.0f, 0.0f, 0.0f, 0.0f), w = t;
-            if (act) {
-                const int e = blk * 32 + sub * 4;
-                t = remote(e) ? ll_read4(xl + 8 * (int64_t) e, xtag) : gs_ld4<COHERENT>(x + e);
-                if (nw) w = *(const float4 *) (nw + e);
-            }
-            quant_store(blk, act, t, w, scale);
-        }
-    }
-    named_bar_sync(1, GS_PRO_THREADS);
-}
-
-// ---------------------------------------------------------------- attention phase (decode, one query position)
-// Item = one query head.  Replaces, for n_q = 1 and an f16 cache, the reference's ROPE(q), ROPE(k) (+SET_ROWS k, v) and
-// FLASH_ATTN_EXT nodes (rope.cu:563, set-rows.cu:318, fattn-vec.cuh:19-507).  The current token's K/V rows are taken
-// from the raw projections (RoPE applied, rounded to f16 exactly as the cache stores them) and written to the cache by
-// the first query head of each KV group; all other positions are read from the cache.
-// one element of q / k_new / v_new: plain when this rank computed it, else the tagged word another rank stored
-template <bool PEER>
-__device__ __forceinline__ float gs_attn_ld(const gs_params & p, const float * base, int64_t i, int lo, int hi, unsigned int tag) {
-    if (!PEER || (i >= lo && i < hi)) return __ldcg(base + i);
-    return ll_read(p.ll_base + 2 * ((const char *) (base + i) - p.arena), tag);
-}
-template <int D, bool PEER>
-__device__ __forceinline__ void gs_attn_item(const gs_params & p, unsigned int ltag, const gs_attn & a, int h, float * sm, int warp, int lane) {
-    constexpr int LPP = D / 32, PPB = 32 / LPP, DPL = D / 32;     // lanes per position, positions per batch, dims per lane (V)
-    const int tid = warp * 32 + lane;
-    const int gqa = a.H / a.H_kv, g = h / gqa;
-    const int pos = __ldcg(a.pos), slot = (int) __ldcg(a.slot), slot_v = (int) __ldcg(a.slot_v);
-    float * s_q = sm, * s_k = sm + D, * s_v = sm + 2 * D, * s_part = sm + 3 * D;      // s_part: [GS_NW][D + 2]
-    // ---- 1. RoPE(q[h]) * scale, RoPE(k_new[g]) and v_new[g] rounded to f16
-    {
-        const int half_d = a.n_dims / 2;
-        if (tid < D) {                                            // threads 0..D/2-1: q pairs, D/2..D-1: k pairs
-            const bool isk = tid >= D / 2;
-            const int i = isk ? tid - D / 2 : tid;
-            const float * src = isk ? a.k_new : a.q;
-            const int64_t so = isk ? (int64_t) g * D : (int64_t) h * D;
-            const int slo = isk ? a.k_lo : a.q_lo, shi = isk ? a.k_hi : a.q_hi;
-            const unsigned int stag = ltag + (isk ? a.k_tag : a.q_tag);
-            float * dst = isk ? s_k : s_q;
-            if (i < half_d) {
-                const int i0 = a.rope_mode == 2 ? i : 2 * i, i1 = a.rope_mode == 2 ? i + half_d : 2 * i + 1;
-                const float theta = (float) pos * powf(a.theta_scale, (float) i) * a.freq_scale;
-                float sn, cs; sincosf(theta, &sn, &cs);
-                const float x0 = gs_attn_ld<PEER>(p, src, so + i0, slo, shi, stag), x1 = gs_attn_ld<PEER>(p, src, so + i1, slo, shi, stag);
-                float y0 = x0 * cs - x1 * sn, y1 = x0 * sn + x1 * cs;
-                if (isk) { y0 = __half2float(__float2half_rn(y0)); y1 = __half2float(__float2half_rn(y1)); }
-                else     { y0 *= a.scale; y1 *= a.scale; }
-                dst[i0] = y0; dst[i1] = y1;
-            }
-            for (int d = a.n_dims + i; d < D; d += D / 2) {       // dims beyond n_dims pass through
-                const float y = gs_attn_ld<PEER>(p, src, so + d, slo, shi, stag);
-                dst[d] = isk ? __half2float(__float2half_rn(y)) : y * a.scale;
-            }
-        } else if (tid < 2 * D) {
-            const int d = tid - D;
-            s_v[d] = __half2float(__float2half_rn(gs_attn_ld<PEER>(p, a.v_new, (int64_t) g * D + d, a.v_lo, a.v_hi, ltag + a.v_tag)));
-        }
-    }
-    named_bar_sync(3, GS_CON_THREADS);
-    if (h % gqa == 0 && tid < 2 * D) {                            // KV-cache write of the current token (one writer per group)
-        const int d = tid < D ? tid : tid - D;
-        char * row = tid < D ? a.k_cache + (int64_t) slot * a.k_nb1 + (int64_t) g * a.k_nb2
-                             : a.v_cache + (int64_t) slot_v * a.v_nb1 + (int64_t) g * a.v_nb2;
-        ((__half *) row)[d] = __float2half_rn(tid < D ? s_k[d] : s_v[d]);
-    }
-    // ---- 2. scores + online softmax + V accumulation, KV positions strided over the warps
-    float qreg[32];
-    const int qsub = lane % LPP;
-#pragma unroll
-    for (int i = 0; i < 32; ++i) qreg[i] = s_q[qsub * 32 + i];
-    float m = -INFINITY, l = 0.0f, acc[DPL];
-#pragma unroll
-    for (int i = 0; i < DPL; ++i) acc[i] = 0.0f;
-    const char * kb = a.k_cache + (int64_t) g * a.k_nb2;
-    const char * vb = a.v_cache + (int64_t) g * a.v_nb2;
-    for (int base = warp * PPB; base < a.n_kv; base += GS_NW * PPB) {
-        const int p = base + lane / LPP;
-        const float mk = p < a.n_kv ? (a.mask ? __half2float(a.mask[p]) : 0.0f) : -INFINITY;
-        float s = 0.0f;
-        if (mk != -INFINITY) {
-            if (p == slot) {
-#pragma unroll
-                for (int i = 0; i < 32; ++i) s += qreg[i] * s_k[qsub * 32 + i];
-            } else {
-                const uint4 * kr = (const uint4 *) (kb + (int64_t) p * a.k_nb1 + qsub * 64);
-#pragma unroll
-                for (int c4 = 0; c4 < 4; ++c4) {
-                    const uint4 t = kr[c4];
-                    const __half2 * hp = (const __half2 *) &t;
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) { const float2 f = __half22float2(hp[i]); s += qreg[c4 * 8 + 2 * i] * f.x + qreg[c4 * 8 + 2 * i + 1] * f.y; }
-                }
-            }
-        }
-#pragma unroll
-        for (int o = 1; o < LPP; o <<= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        s = mk == -INFINITY ? -INFINITY : s + mk;
-        float bm = s;
-#pragma unroll
-        for (int o = LPP; o < 32; o <<= 1) bm = fmaxf(bm, __shfl_xor_sync(0xffffffffu, bm, o));
-        const float mn = fmaxf(m, bm);
-        if (mn == -INFINITY) continue;                            // whole batch masked (warp-uniform)
-        const float corr = __expf(m - mn);
-        const float pr = s == -INFINITY ? 0.0f : __expf(s - mn);
-        float psum = pr;
-#pragma unroll
-        for (int o = LPP; o < 32; o <<= 1) psum += __shfl_xor_sync(0xffffffffu, psum, o);
-        l = l * corr + psum; m = mn;
-#pragma unroll
-        for (int i = 0; i < DPL; ++i) acc[i] *= corr;
-#pragma unroll
-        for (int j = 0; j < PPB; ++j) {
-            const float pj = __shfl_sync(0xffffffffu, pr, j * LPP);
-            const int pp = base + j;
-            if (pj != 0.0f) {                                     // warp-uniform
-                if (pp == slot_v) {
-#pragma unroll
-                    for (int i = 0; i < DPL; ++i) acc[i] += pj * s_v[lane * DPL + i];
-                } else {
-                    const __half * vr = (const __half *) (vb + (int64_t) pp * a.v_nb1) + lane * DPL;
-                    if (DPL == 4) { const uint2 t = *(const uint2 *) vr; const __half2 * hp = (const __half2 *) &t;
-                                    const float2 f0 = __half22float2(hp[0]), f1 = __half22float2(hp[1]);
-                                    acc[0] += pj * f0.x; acc[1] += pj * f0.y; acc[2] += pj * f1.x; acc[3] += pj * f1.y; }
-                    else          { const float2 f0 = __half22float2(*(const __half2 *) vr); acc[0] += pj * f0.x; acc[1] += pj * f0.y; }
-                }
-            }
-        }
-    }
-    // ---- 3. combine the warps' states
-    float * mine = s_part + warp * (D + 2);
-#pragma unroll
-    for (int i = 0; i < DPL; ++i) mine[lane * DPL + i] = acc[i];
-    if (lane == 0) { mine[D] = m; mine[D + 1] = l; }
-    named_bar_sync(3, GS_CON_THREADS);
-    if (tid < D) {
-        float M = -INFINITY;
-#pragma unroll
-        for (int w = 0; w < GS_NW; ++w) M = fmaxf(M, s_part[w * (D + 2) + D]);
-        float A = 0.0f, L = 0.0f;
-#pragma unroll
-        for (int w = 0; w < GS_NW; ++w) {
-            const float mw = s_part[w * (D + 2) + D];
-            const float wgt = mw == -INFINITY ? 0.0f : __expf(mw - M);
-            A += wgt * s_part[w * (D + 2) + tid]; L += wgt * s_part[w * (D + 2) + D + 1];
-        }
-        a.dst[(int64_t) h * D + tid] = A / L;
-    }
-    named_bar_sync(3, GS_CON_THREADS);                            // scratch is reused by the next item
-}
-
-__device__ __forceinline__ unsigned long long gs_now() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
-#define GS_STAMP(ip, k) do { if (p.dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) \
-    p.dbg[((ip) * 2 + (blockIdx.x ? 1 : 0)) * 8 + (k)] = gs_now(); } while (0)
-#define GS_STAMP_MAX(ip, k) do { if (p.dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) \
-    atomicMax(p.dbg + ((ip) * 2 + (blockIdx.x ? 1 : 0)) * 8 + (k), gs_now()); } while (0)
-
-__device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int * p) {
-    unsigned int v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int * p) {
-    unsigned int v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-// thread 0 of a CTA: wait until counter `bar` has seen every arrival of this launch.  Bounded by wall time: a rank
-// that never arrives (crashed process, mismatched phase lists) becomes a trap, not a hung GPU.
-template <bool PEER>
-__device__ __forceinline__ void gs_wait_counter(const unsigned int * bar, unsigned int target) {
-    if (!PEER) {
-        unsigned int spins = 0;
-        while (ld_acquire_gpu(bar) < target) { if (++spins > (1u << 24)) __trap(); }
-    } else {
-        unsigned int spins = 0; unsigned long long t0 = 0;
-        while ((int) (ld_acquire_sys(bar) - target) < 0) {
-            if ((++spins & 0xFFFu) == 0) {
-                const unsigned long long now = gs_now();
-                if (!t0) t0 = now; else if (now - t0 > 20000000000ull) __trap();      // 20 s
-            }
-        }
-    }
-}
-
-// ---------------------------------------------------------------- the kernel
-// MODE 0: one phase (b200_gemv_fused, PDL); 1: decode chain on one GPU; 2: decode chain, row split over peer memory
-template <int T0, int T1, int MODE>
-__global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid_constant__ gs_params p) {
-    constexpr bool CHAIN = MODE >= 1, PEER = MODE == 2;
-    extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ gs_shared sh;
-    // phase descriptors are staged in shared memory: read from global inside the chunk loops they cost an L2 round
-    // trip per field per chunk (measured: 1.3 us per chunk in the finalizer)
-    __shared__ gs_phase s_ph[2];       // consumers + finalizer (double-buffered: the finalizer may trail by a phase)
-    __shared__ gs_phase s_pp;          // producer (runs ahead)
-    gs_ctx c;
-    c.ring = smem;                                                            // n_stages x stage_stride
-    c.aq   = smem + p.n_stages * p.stage_stride;                              // activation int8, padded layout
-    c.ads  = (float2 *) (c.aq + p.act_qs_bytes);                              // (d, d*sum) per unit; sized with act_qs_bytes/4
-    c.attn = (float *) ((uint8_t *) c.ads + (p.act_qs_bytes >> 2) + 64);      // attention scratch
-    c.sh = &sh; c.stage_stride = p.stage_stride; c.flags = p.flags;
-
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    if (tid == 0) {
-        for (int s = 0; s < p.n_stages; ++s) { mbar_init(&sh.full[s], 1); mbar_init(&sh.empty[s], GS_NW); }
-        // row split: tags of this launch = (launches so far + 1) * 1024 + phase index (never 0, the value of fresh memory)
-        sh.tag = PEER ? (__ldcg(p.epoch) + 1u) << 10 : 0u;
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    }
-    __syncthreads();
-    if (!CHAIN) pdl_launch_dependents();      // the next kernel in the stream may begin its own weight prefetch
-
-    const gs_phase * phases = CHAIN ? p.phases : &p.inl;
-    const int n_phases = CHAIN ? p.n_phases : 1;
-    gs_pos pos; pos.ns = p.n_stages;
-    constexpr int PH_VEC = (int) (sizeof(gs_phase) / 16);
-    static_assert(sizeof(gs_phase) % 16 == 0, "gs_phase is copied as uint4");
-
-    if (warp == GS_NW) {
-        // ================= producer: TMA bulk copies into the ring, straight through all phases
-        const uint64_t pol = policy_evict_first();
-        for (int ip = 0; ip < n_phases; ++ip) {
-            __syncwarp();
-            for (int i = lane; i < PH_VEC; i += 32) ((uint4 *) &s_pp)[i] = ((const uint4 *) (phases + ip))[i];
-            __syncwarp();
-            if (lane == 0) {
-                const gs_phase & ph = s_pp;
-                if (ph.kind != 0) continue;
-                const int64_t lo = ph.total_bytes * (int64_t) blockIdx.x / gridDim.x, hi = ph.total_bytes * (int64_t) (blockIdx.x + 1) / gridDim.x;
-                for (int s = 0; s < ph.n_ws; ++s) {
-                    const gs_seg & sg = ph.seg[s];
-                    int r0, r1; gs_row_range(sg, lo, hi, r0, r1);
-                    for (int row = r0; row < r1; row += sg.R) {
-                        const int nr = min(sg.R, r1 - row);
-                        mbar_wait(&sh.empty[pos.st], pos.full_par ^ 1);
-                        uint8_t * dstp = c.ring + pos.st * p.stage_stride;
-                        const uintptr_t g0 = (uintptr_t) (sg.w[0] + (int64_t) row * sg.rb);
-                        const uint32_t o0 = (uint32_t) (g0 & 15), b0 = (o0 + (uint32_t) nr * sg.rb + 15u) & ~15u;
-                        if (sg.nsub == 2) {
-                            const uintptr_t g1 = (uintptr_t) (sg.w[1] + (int64_t) row * sg.rb);
-                            const uint32_t o1 = (uint32_t) (g1 & 15), b1 = (o1 + (uint32_t) nr * sg.rb + 15u) & ~15u;
-                            mbar_expect_tx(&sh.full[pos.st], b0 + b1);
-                            bulk_g2s(dstp, (const void *) (g0 - o0), b0, &sh.full[pos.st], pol);
-                            bulk_g2s(dstp + b0, (const void *) (g1 - o1), b1, &sh.full[pos.st], pol);
-                        } else {
-                            mbar_expect_tx(&sh.full[pos.st], b0);
-                            bulk_g2s(dstp, (const void *) (g0 - o0), b0, &sh.full[pos.st], pol);
-                        }
-                        pos.next();
-                    }
-                }
-            }
-        }
-        return;
-    }
-
-    // ================= consumers (warps 0..GS_NW-1)
-    for (int ip = 0; ip < n_phases; ++ip) {
-        const gs_phase & ph = s_ph[ip & 1];
-        // static data: staged (and the norm weights requested into L2) before the dependency wait
-        for (int i = tid; i < PH_VEC; i += GS_CON_THREADS) ((uint4 *) &s_ph[ip & 1])[i] = ((const uint4 *) (phases + ip))[i];
-        // ---- dependency: everything this phase reads was produced by the previous phase (or earlier kernels)
-        if (ip == 0) {
-            pdl_wait();
-        } else if (tid == 0) {
-            gs_wait_counter<false>(p.bar + ip - 1, gridDim.x);       // this GPU's CTAs; rows of other ranks carry their own tags
-        }
-        named_bar_sync(1, GS_CON_THREADS);
-        if (CHAIN && tid == 0) GS_STAMP(ip, 0);
-        if (ph.kind == 0) {
-            gs_prologue<CHAIN, PEER>(p, c, ph, warp, lane);
-            if (CHAIN && tid == 0) GS_STAMP(ip, 1);
-            const int64_t lo = ph.total_bytes * (int64_t) blockIdx.x / gridDim.x, hi = ph.total_bytes * (int64_t) (blockIdx.x + 1) / gridDim.x;
-            for (int s = 0; s < ph.n_ws; ++s) {
-                const gs_seg & sg = ph.seg[s];
-                int r0, r1; gs_row_range(sg, lo, hi, r0, r1);
-                if (r0 >= r1) continue;
-                if (sg.type == T0) consume_dispatch<T0, CHAIN, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
-                else               consume_dispatch<T1, CHAIN, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
-            }
-        } else if (CHAIN && ph.kind == 1) {
-            for (int h = blockIdx.x; h < ph.attn.H; h += gridDim.x) {
-                if (ph.attn.D == 128) gs_attn_item<128, PEER>(p, sh.tag, ph.attn, h, c.attn, warp, lane);
-                else                  gs_attn_item<64, PEER>(p, sh.tag, ph.attn, h, c.attn, warp, lane);
-            }
-        }
-        if (CHAIN) {
-            if (tid == 0) GS_STAMP(ip, 2);
-            // ---- publish: this CTA's stores of the phase are visible device-wide, then count it in
-            // flags bit 3: fence in thread 0 only, after the CTA barrier (the barrier orders every consumer thread's stores
-            // before it and the fence is cumulative — the pattern of a cooperative-groups grid sync).  Measured: at device
-            // scope 512 fences are marginally faster than one (460 vs 458 tok/s); at system scope one is much cheaper.
-            const bool fence_all = (c.flags & 8) == 0;
-            if (fence_all) __threadfence();
-            named_bar_sync(1, GS_CON_THREADS);
-            if (tid == 0) {
-                if (!fence_all) __threadfence();
-                GS_STAMP(ip, 4);
-                atomicAdd(p.bar + ip, 1u);
-                if (PEER && ph.peer_mode == 2) {
-                    // outputs read after the launch (the logits) went to the other ranks as plain stores: one system-scope
-                    // fence, then the arrival is counted on every rank
-                    __threadfence_system();
-                    atomicAdd_system(p.sync + ip, 1u);
-#pragma unroll
-                    for (int r = 0; r < B200_MAX_RANKS - 1; ++r)
-                        if (r < p.n_peers) atomicAdd_system((unsigned int *) ((char *) (p.sync + ip) + p.peer_delta[r]), 1u);
-                }
-                GS_STAMP(ip, 3);
-            }
-        }
-    }
-    if (PEER && blockIdx.x == 0 && tid == 0) {
-        // the launch ends only when every rank has delivered its plain-stored rows (the logits) into this rank's buffers;
-        // then the launch is counted.  No CTA of this launch reads the epoch after its first instructions, and no CTA of
-        // the next launch starts before this one has exited (same stream).
-        for (int k = 0; k < p.n_final; ++k) gs_wait_counter<true>(p.sync + p.final_phase[k], (unsigned int) p.total_ctas);
-        *p.epoch = __ldcg(p.epoch) + 1u;
-    }
-}
+// the instantiations live in gemv_stream_i_*.cu
+extern template int gs_launch<12, 12, 0>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<12, 12, 1>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<12, 12, 2>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<14, 14, 0>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<14, 14, 1>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<14, 14, 2>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<2, 2, 0>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<2, 2, 1>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<2, 2, 2>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<8, 8, 0>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<8, 8, 1>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<8, 8, 2>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<39, 39, 0>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<39, 39, 1>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<39, 39, 2>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<12, 14, 0>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<12, 14, 1>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<12, 14, 2>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<2, 14, 0>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<2, 14, 1>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<2, 14, 2>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<2, 8, 0>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<2, 8, 1>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<2, 8, 2>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<8, 39, 0>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<8, 39, 1>(const gs_params &, size_t, int, cudaStream_t);
+extern template int gs_launch<8, 39, 2>(const gs_params &, size_t, int, cudaStream_t);
 
 // ---------------------------------------------------------------- host side
 static bool gs_type_ok(int t) { return t == B200_Q4_0 || t == B200_Q8_0 || t == B200_MXFP4 || t == B200_Q4_K || t == B200_Q6_K; }
@@ -1097,27 +158,6 @@ static bool gs_make_config(int flags, int64_t need, int act_qs, int attn_floats,
     return true;
 }
 
-template <int T0, int T1, int MODE>
-static int gs_launch(const gs_params & p, size_t smem, int grid, cudaStream_t st) {
-    constexpr bool CHAIN = MODE >= 1;
-    static bool attr_set[64] = {};
-    int dev = 0;
-    B200_CUDA_TRY(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= 64) return B200_ERR_ARG;
-    if (!attr_set[dev]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(gemv_stream_kernel<T0, T1, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, GS_SMEM_MAX));
-        attr_set[dev] = true;
-    }
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3((unsigned) grid); cfg.blockDim = dim3(GS_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
-    cudaLaunchAttribute at[1];
-    if (CHAIN) { at[0].id = cudaLaunchAttributeCooperative; at[0].val.cooperative = 1; }     // all CTAs co-resident: the grid barriers need it
-    else       { at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[0].val.programmaticStreamSerializationAllowed = 1; }
-    cfg.attrs = at; cfg.numAttrs = 1;
-    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, gemv_stream_kernel<T0, T1, MODE>, p));
-    count_launch();
-    return B200_OK;
-}
 
 template <int MODE>
 static int gs_launch_types(const gs_params & p, size_t smem, int grid, cudaStream_t st, int t0, int t1) {

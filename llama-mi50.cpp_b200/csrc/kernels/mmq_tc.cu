@@ -33,9 +33,12 @@ constexpr int TC_KSTEP = 256;                              // weights per raw st
 constexpr int TC_SUB = TC_KSTEP / TC_BK;
 
 template <int TYPE> struct tc_fmt;
-template <> struct tc_fmt<B200_Q4_K> { static constexpr int gbytes = 144, box = 144; };
-template <> struct tc_fmt<B200_Q6_K> { static constexpr int gbytes = 210, box = 240; };    // 16 B aligned window around the 210 B block
-template <> struct tc_fmt<B200_Q4_0> { static constexpr int gbytes = 144, box = 144; };    // 8 blocks of 18 B
+// gbytes: bytes of one 256-weight super-step of a row; box: bytes of the TMA box row; elem: tensor-map element size
+template <> struct tc_fmt<B200_Q4_K> { static constexpr int gbytes = 144, box = 144, elem = 1; };
+template <> struct tc_fmt<B200_Q6_K> { static constexpr int gbytes = 210, box = 240, elem = 1; };    // 16 B aligned window around the 210 B block
+template <> struct tc_fmt<B200_Q4_0> { static constexpr int gbytes = 144, box = 144, elem = 1; };    // 8 blocks of 18 B
+template <> struct tc_fmt<B200_Q8_0> { static constexpr int gbytes = 272, box = 272, elem = 2; };    // 8 blocks of 34 B (tensor map in 16-bit elements:
+                                                                                            // a box dimension holds at most 256 elements)
 
 // ---------------------------------------------------------------- PTX helpers
 __device__ __forceinline__ uint32_t tc_smem(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
@@ -195,6 +198,26 @@ template <> struct tc_expand<B200_Q4_0> {
     }
 };
 
+template <> struct tc_expand<B200_Q8_0> {
+    __device__ __forceinline__ static void run(const uint8_t * row, int sub, int r, int h, uint8_t * tile) {
+        const uint8_t * b = row + 34 * (2 * sub + h);            // block: half d, 32 int8 (2-byte aligned)
+        const __half2 s2 = __half2half2(*(const __half *) b);
+        uint32_t q[8];
+        tc_lds_words8(b + 2, q);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            uint32_t o[4];
+#pragma unroll
+            for (int w = 0; w < 2; ++w) {
+                __half2 lo, hi;
+                tc_bytes_to_half(q[2 * c + w] ^ 0x80808080u, 1152.0f, lo, hi);      // int8 + 128 = 0..255; 1024 + 128
+                o[2 * w] = tc_h2u(__hmul2(lo, s2)); o[2 * w + 1] = tc_h2u(__hmul2(hi, s2));
+            }
+            tc_store_chunk(tile, r, 4 * h + c, make_uint4(o[0], o[1], o[2], o[3]));
+        }
+    }
+};
+
 // ---------------------------------------------------------------- activations -> swizzled 16-bit tiles
 // out: tiles [n_tile][k_block] of 256 rows x 128 B, each already in the shared-memory image (16 B chunk c of row r at
 // (r/8)*1024 + (r%8)*128 + ((c ^ r%8) * 16)); columns beyond N are zero.  fmt 0 = f16 (clamped to +-65504), 1 = bf16.
@@ -275,7 +298,7 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmA, const uint8_t * __restric
                 const int rs = ks % TC_RAW_STAGES;
                 tc_mbar_wait(&sh.raw_empty[rs], ((ks / TC_RAW_STAGES) & 1) ^ 1);
                 tc_mbar_expect(&sh.raw_full[rs], RAW_BYTES);
-                tc_tma_2d(sR + rs * RAW_BYTES, &tmA, (ks * F::gbytes) & ~15, m0, &sh.raw_full[rs]);   // box starts are kept 16 B aligned (an unaligned start faulted)
+                tc_tma_2d(sR + rs * RAW_BYTES, &tmA, ((ks * F::gbytes) & ~15) / F::elem, m0, &sh.raw_full[rs]);   // box starts are kept 16 B aligned (an unaligned start faulted)
                 for (int sub = 0; sub < TC_SUB; ++sub) {
                     const int it = ks * TC_SUB + sub, s = it % TC_STAGES;
                     tc_mbar_wait(&sh.ab_empty[s], ((it / TC_STAGES) & 1) ^ 1);
@@ -360,9 +383,9 @@ static tc_encode_fn tc_encoder() {
     return fn;
 }
 
-static int tc_box(int t) { return t == B200_Q6_K ? 240 : 144; }
-static int tc_gbytes(int t) { return t == B200_Q6_K ? 210 : 144; }
-static bool tc_type_ok(int t) { return t == B200_Q4_K || t == B200_Q6_K || t == B200_Q4_0; }
+static int tc_box(int t) { return t == B200_Q6_K ? 240 : t == B200_Q8_0 ? 272 : 144; }
+static int tc_elem(int t) { return t == B200_Q8_0 ? 2 : 1; }
+static bool tc_type_ok(int t) { return t == B200_Q4_K || t == B200_Q6_K || t == B200_Q4_0 || t == B200_Q8_0; }
 static size_t tc_smem_bytes(int t) { return (size_t) TC_STAGES * (TC_A_BYTES + TC_B_BYTES) + (size_t) TC_RAW_STAGES * TC_BM * tc_box(t) + 1024; }
 
 static bool tc_args_ok(const b200_mmq_args * a) {
@@ -434,11 +457,12 @@ extern "C" int b200_mul_mat_q(const b200_mmq_args * a, void * stream) {
         const key k{a->w.data, a->w.nb[1], a->w.ne[1], a->w.type};
         auto it = cache.find(k);
         if (it == cache.end()) {
-            const cuuint64_t gdim[2] = {(cuuint64_t) a->w.nb[1], (cuuint64_t) a->w.ne[1]};
+            const int el = tc_elem(a->w.type);
+            const cuuint64_t gdim[2] = {(cuuint64_t) a->w.nb[1] / el, (cuuint64_t) a->w.ne[1]};
             const cuuint64_t gstr[1] = {(cuuint64_t) a->w.nb[1]};
-            const cuuint32_t box[2] = {(cuuint32_t) tc_box(a->w.type), (cuuint32_t) TC_BM};
+            const cuuint32_t box[2] = {(cuuint32_t) (tc_box(a->w.type) / el), (cuuint32_t) TC_BM};
             const cuuint32_t estr[2] = {1, 1};
-            const CUresult rc = enc(&map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, a->w.data, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            const CUresult rc = enc(&map, el == 2 ? CU_TENSOR_MAP_DATA_TYPE_UINT16 : CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, a->w.data, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
             if (rc != CUDA_SUCCESS) { set_error("b200_mul_mat_q: cuTensorMapEncodeTiled failed (%d)", (int) rc); return B200_ERR_CUDA; }
             if (cache.size() > 4096) cache.clear();
@@ -451,6 +475,7 @@ extern "C" int b200_mul_mat_q(const b200_mmq_args * a, void * stream) {
         case B200_Q4_K: return tc_launch<B200_Q4_K>(map, a, idesc, (cudaStream_t) stream);
         case B200_Q6_K: return tc_launch<B200_Q6_K>(map, a, idesc, (cudaStream_t) stream);
         case B200_Q4_0: return tc_launch<B200_Q4_0>(map, a, idesc, (cudaStream_t) stream);
+        case B200_Q8_0: return tc_launch<B200_Q8_0>(map, a, idesc, (cudaStream_t) stream);
     }
     return B200_ERR_UNSUPPORTED;
 }

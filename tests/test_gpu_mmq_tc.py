@@ -11,7 +11,7 @@ from conftest import ptr
 
 pytestmark = pytest.mark.gpu
 
-Q4_0, Q4_K, Q6_K = 2, 12, 14
+Q4_0, Q8_0, Q4_K, Q6_K = 2, 8, 12, 14
 
 
 def _dequant(orc, gs, raw, t, K, M):
@@ -24,7 +24,7 @@ def _dequant(orc, gs, raw, t, K, M):
 
 
 @pytest.mark.parametrize("act_fmt", [0])
-@pytest.mark.parametrize("t", [Q4_K, Q6_K, Q4_0])
+@pytest.mark.parametrize("t", [Q4_K, Q6_K, Q4_0, Q8_0])
 @pytest.mark.parametrize("M,K,N", [(256, 512, 300), (128, 256, 9), (384, 1024, 512), (200, 768, 64), (256, 2048, 40), (4096, 4096, 512)])
 def test_mul_mat_q_vs_float64(orc, t, M, K, N, act_fmt):
     import torch
