@@ -11,7 +11,14 @@
 namespace b200 {
 
 constexpr int GS_NW          = 16;                     // consumer warps (4 per scheduler)
-constexpr int GS_THREADS     = (GS_NW + 1) * 32;       // + producer warp
+constexpr int GS_THREADS     = (GS_NW + 4) * 32;       // + producer warpgroup: warp GS_NW streams, the other three exit at once.
+                                                       // A scheduler partition owns 16 K registers; a fifth warp on it caps every
+                                                       // thread at 96.  With a whole warpgroup the producer side can hand its
+                                                       // registers over (setmaxnreg.dec) and the consumers take them (setmaxnreg.inc).
+                                                       // The pool is what the CTA got at launch (96 per thread), not the register
+                                                       // file: an inc that does not fit WAITS FOREVER (measured: a hung launch)
+constexpr int GS_REG_LAUNCH = 96, GS_REG_PRODUCER = 32, GS_REG_CONSUMER = 112;
+static_assert(GS_NW * 32 * GS_REG_CONSUMER + 4 * 32 * GS_REG_PRODUCER <= GS_THREADS * GS_REG_LAUNCH, "setmaxnreg.inc would never be granted");
 constexpr int GS_CON_THREADS = GS_NW * 32;
 constexpr int GS_PRO_THREADS = GS_CON_THREADS;         // warps that run the prologue (all but the producer)
 constexpr int GS_STAGES      = 3;                      // default ring depth
@@ -105,13 +112,6 @@ __device__ __forceinline__ void mbar_wait(uint64_t * b, uint32_t parity) {
 __device__ __forceinline__ void bulk_g2s(void * dst, const void * src, uint32_t bytes, uint64_t * bar, uint64_t policy) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(policy) : "memory");
-}
-// L2 prefetch of weight bytes that a later bulk copy of this CTA will read (no shared memory, no completion tracking)
-__device__ __forceinline__ void bulk_prefetch_l2(const void * src, uint32_t bytes) {
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void prefetch_l2_line(const void * src) {
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(src));
 }
 __device__ __forceinline__ uint64_t policy_evict_first() {
     uint64_t p;
@@ -870,7 +870,6 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
     // trip per field per chunk (measured: 1.3 us per chunk in the finalizer)
     __shared__ gs_phase s_ph[2];       // consumers + finalizer (double-buffered: the finalizer may trail by a phase)
     __shared__ gs_phase s_pp;          // producer (runs ahead)
-    __shared__ gs_phase s_pf;          // producer's L2 prefetch walker (runs further ahead)
     gs_ctx c;
     c.ring = smem;                                                            // n_stages x stage_stride
     c.aq   = smem + p.n_stages * p.stage_stride;                              // activation int8, padded layout
@@ -895,30 +894,16 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
     constexpr int PH_VEC = (int) (sizeof(gs_phase) / 16);
     static_assert(sizeof(gs_phase) % 16 == 0, "gs_phase is copied as uint4");
 
-    if (warp == GS_NW) {
+    if (warp >= GS_NW) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(GS_REG_PRODUCER));
+        if (warp > GS_NW) return;
         // ================= producer: TMA bulk copies into the ring, straight through all phases.  The whole warp walks
-        // the chunk sequence (warp-uniform state); lane 0 issues the copies.  A second walker runs `pf_dist` chunks ahead
-        // and requests those chunks into L2 (flags bits 20-23): while the ring is full — consumers at a grid barrier, in
-        // a prologue or in an attention phase — HBM keeps streaming into L2, and the ring refills from L2 afterwards.
+        // the chunk sequence (warp-uniform state); lane 0 issues the copies.
+        // (Measured and dropped: a second walker requesting chunks into L2 2-8 chunks ahead of the ring — bulk prefetch
+        // or per-line prefetch.global.L2 — ran 1-4 % slower; the consume phases are not short of HBM bytes in flight.)
         const uint64_t pol = policy_evict_first();
-        const int pf_dist = (p.flags >> 20) & 0xF;
-        const bool pf_lines = (p.flags >> 24) & 1;        // per-line prefetch.global.L2 by all lanes instead of one bulk prefetch
-        gs_walk wt, wp;
-        bool pf_live = pf_dist > 0;
-        int ahead = 0;                                     // chunks requested into L2 beyond the next TMA copy
+        gs_walk wt;
         while (gs_walk_next(wt, &s_pp, phases, n_phases, blockIdx.x, gridDim.x, lane)) {
-            while (pf_live && ahead <= pf_dist) {
-                if (!gs_walk_next(wp, &s_pf, phases, n_phases, blockIdx.x, gridDim.x, lane)) { pf_live = false; break; }
-                const gs_seg & sg = s_pf.seg[wp.s];
-                const int nr = min(sg.R, wp.r1 - wp.row);
-                for (int u = 0; u < sg.nsub; ++u) {
-                    const uintptr_t g = (uintptr_t) (sg.w[u] + (int64_t) wp.row * sg.rb);
-                    const uint32_t o = (uint32_t) (g & 15), b = (o + (uint32_t) nr * sg.rb + 15u) & ~15u;
-                    if (pf_lines) { for (uint32_t off = lane * 128u; off < b; off += 32u * 128u) prefetch_l2_line((const void *) (g - o + off)); }
-                    else if (lane == 0) bulk_prefetch_l2((const void *) (g - o), b);
-                }
-                wp.row += sg.R; ++ahead;
-            }
             if (lane == 0) {
                 const gs_seg & sg = s_pp.seg[wt.s];
                 const int nr = min(sg.R, wt.r1 - wt.row);
@@ -938,13 +923,14 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
                 }
             }
             __syncwarp();
-            wt.row += s_pp.seg[wt.s].R; --ahead;
+            wt.row += s_pp.seg[wt.s].R;
             pos.next();
         }
         return;
     }
 
     // ================= consumers (warps 0..GS_NW-1)
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(GS_REG_CONSUMER));
     for (int ip = 0; ip < n_phases; ++ip) {
         const gs_phase & ph = s_ph[ip & 1];
         // static data: staged (and the norm weights requested into L2) before the dependency wait
