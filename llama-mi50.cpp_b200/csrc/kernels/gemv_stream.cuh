@@ -541,6 +541,16 @@ __device__ __forceinline__ void consume_dispatch(const gs_params & p, const gs_c
         consume_segment<TYPE, (item<TYPE>::max_spw >= 4 ? 4 : 1), COHERENT, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
 }
 
+__device__ __forceinline__ unsigned long long gs_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define GS_STAMP(ip, k) do { if (p.dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) \
+    p.dbg[((ip) * 2 + (blockIdx.x ? 1 : 0)) * 8 + (k)] = gs_now(); } while (0)
+#define GS_STAMP_MAX(ip, k) do { if (p.dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) \
+    atomicMax(p.dbg + ((ip) * 2 + (blockIdx.x ? 1 : 0)) * 8 + (k), gs_now()); } while (0)
+
 // ---------------------------------------------------------------- phase pieces
 // prologue of a GEMV phase (consumers + finalizer): x -> [rms norm * w] -> q8_1 in shared memory.
 // COHERENT selects L2-coherent loads: inside a chain x was written by other SMs during this launch.
@@ -642,12 +652,14 @@ __device__ __forceinline__ void gs_prologue(const gs_params & p, const gs_ctx & 
 #pragma unroll
             for (int i = 0; i < GS_NW; ++i) tot += sh.part[i];
             scale = rsqrtf(tot / (float) K + ph.eps);
+            if (COHERENT && warp == 0 && lane == 0) GS_STAMP(ph.self_tag, 5);
         }
 #pragma unroll
         for (int it = 0; it < NV; ++it) {
             const int b0 = pw * 4 + it * BPP;                   // warp-uniform
             if (b0 < nblk) quant_store(b0 + bw, b0 + bw < nblk, xv[it], wv[it], scale);
         }
+        if (COHERENT && warp == 0 && lane == 0) GS_STAMP(ph.self_tag, 6);
     } else {
         // ---- long rows: two passes over x
         const int ptid = pw * 32 + lane;
@@ -821,16 +833,6 @@ __device__ __forceinline__ void gs_attn_item(const gs_params & p, unsigned int l
     named_bar_sync(3, GS_CON_THREADS);                            // scratch is reused by the next item
 }
 
-__device__ __forceinline__ unsigned long long gs_now() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
-#define GS_STAMP(ip, k) do { if (p.dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) \
-    p.dbg[((ip) * 2 + (blockIdx.x ? 1 : 0)) * 8 + (k)] = gs_now(); } while (0)
-#define GS_STAMP_MAX(ip, k) do { if (p.dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) \
-    atomicMax(p.dbg + ((ip) * 2 + (blockIdx.x ? 1 : 0)) * 8 + (k), gs_now()); } while (0)
-
 __device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int * p) {
     unsigned int v;
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -963,16 +965,18 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
         if (CHAIN) {
             if (tid == 0) GS_STAMP(ip, 2);
             // ---- publish: this CTA's stores of the phase are visible device-wide, then count it in
-            // flags bit 3: fence in thread 0 only, after the CTA barrier (the barrier orders every consumer thread's stores
-            // before it and the fence is cumulative — the pattern of a cooperative-groups grid sync).  Measured: at device
-            // scope 512 fences are marginally faster than one (460 vs 458 tok/s); at system scope one is much cheaper.
-            const bool fence_all = (c.flags & 8) == 0;
+            // Default: thread 0 alone releases, after the CTA barrier (the barrier orders every consumer thread's stores before
+            // it and the release is cumulative — the pattern of a cooperative-groups grid sync).  flags bit 3: the older
+            // variant, __threadfence in every thread before the barrier (measured equal within 0.5 %).
+            const bool fence_all = (c.flags & 8) != 0;
             if (fence_all) __threadfence();
             named_bar_sync(1, GS_CON_THREADS);
             if (tid == 0) {
-                if (!fence_all) __threadfence();
                 GS_STAMP(ip, 4);
-                atomicAdd(p.bar + ip, 1u);
+                // release at device scope on the arrival itself (MEMBAR.ALL.GPU + RED; __threadfence would add an L1
+                // invalidate nobody needs: data of this launch is only ever read with ld.cg / ld.acquire)
+                if (fence_all) atomicAdd(p.bar + ip, 1u);
+                else asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p.bar + ip), "r"(1u) : "memory");
                 if (PEER && ph.peer_mode == 2) {
                     // outputs read after the launch (the logits) went to the other ranks as plain stores: one system-scope
                     // fence, then the arrival is counted on every rank

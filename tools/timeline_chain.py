@@ -34,14 +34,16 @@ for cta in (0, 1):
         nm = names[i % 5] if i < n - 1 else "logits"
         a = d[i, cta]
         a1 = a[1] if a[1] else a[0]
-        rows.setdefault(nm, []).append((a[0] - prev_pub, a1 - a[0], a[2] - a1, a[4] - a[2], a[3] - a[4]))
+        s5 = a[5] if a[5] else a[0]
+        s6 = a[6] if a[6] else a1
+        rows.setdefault(nm, []).append((a[0] - prev_pub, a1 - a[0], a[2] - a1, a[4] - a[2], a[3] - a[4], s5 - a[0], s6 - s5, a1 - s6))
         prev_pub = a[3]
     print(f"== CTA {'0' if cta == 0 else 'last'}: token {(d[n-1, cta, 3] - t0) / 1e3:.1f} us; mean ns per phase kind (first layer skipped)")
-    print("phase    wait-dep  prologue   consume  fence+bar    atomic     total")
+    print("phase    wait-dep  prologue   consume  fence+bar    atomic     total | prologue: load+norm  quantize  barrier")
     layer = 0.0
     for nm, v in rows.items():
         v = np.array(v[1:] if len(v) > 1 else v, dtype=np.float64)
         m = v.mean(axis=0)
-        if nm != "logits": layer += m.sum()
-        print(f"{nm:7s} {m[0]:9.0f} {m[1]:9.0f} {m[2]:9.0f} {m[3]:10.0f} {m[4]:9.0f} {m.sum():9.0f}")
+        if nm != "logits": layer += m[:5].sum()
+        print(f"{nm:7s} {m[0]:9.0f} {m[1]:9.0f} {m[2]:9.0f} {m[3]:10.0f} {m[4]:9.0f} {m[:5].sum():9.0f} | {m[5]:19.0f} {m[6]:9.0f} {m[7]:8.0f}")
     print(f"per layer {layer / 1e3:.2f} us")
