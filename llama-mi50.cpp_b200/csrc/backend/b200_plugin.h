@@ -57,6 +57,21 @@ bool                       b200_buft_is_b200(ggml_backend_buffer_type_t buft);
 bool                       b200_buft_is_split(ggml_backend_buffer_type_t buft);
 int                        b200_buft_device(ggml_backend_buffer_type_t buft);
 
+// ---- row-split tensors (split_buffer.cpp): tensor->extra of a tensor in a split buffer
+struct b200_split_extra {
+    void *  data[B200_MAX_DEVICES];                            // rows [row_lo, row_hi) of the tensor on each device (null: no rows)
+    int64_t row_lo[B200_MAX_DEVICES], row_hi[B200_MAX_DEVICES];
+};
+void b200_split_rows(ggml_backend_buffer_type_t split_buft, int64_t nrows, int device, int64_t & lo, int64_t & hi);
+void b200_enable_peer_access();
+// what a backend context keeps on each OTHER device to run its slice of a row-split matmul
+struct b200_split_dev {
+    cudaStream_t stream = nullptr; cudaEvent_t done = nullptr;
+    char * x = nullptr;  size_t x_size = 0;                    // copy of the f32 activations
+    char * q8 = nullptr; size_t q8_size = 0;                   // their q8_1 form (GEMV)
+    char * xb = nullptr; size_t xb_size = 0;                   // their 16-bit tiles (tensor-core GEMM)
+};
+
 // ---- backend context (exec.cpp)
 struct b200_graph_cache;
 struct b200_context {
@@ -70,6 +85,8 @@ struct b200_context {
     b200_graph_cache * cache = nullptr;
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
     bool timing = false, ev_pending = false;
+    b200_split_dev split[B200_MAX_DEVICES];               // row split: streams / scratch on the other devices
+    cudaEvent_t    split_fork = nullptr;
 };
 
 ggml_status b200_graph_compute(b200_context * ctx, ggml_cgraph * cgraph);

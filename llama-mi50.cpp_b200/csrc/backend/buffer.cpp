@@ -45,8 +45,12 @@ bool buf_cpy_tensor(ggml_backend_buffer_t b, const ggml_tensor * src, ggml_tenso
     if (!ggml_is_contiguous(src) || !ggml_is_contiguous(dst) || ggml_nbytes(src) != ggml_nbytes(dst)) return false;
     const int sd = ((buf_ctx *) sb->context)->device, dd = ((buf_ctx *) b->context)->device;
     b200_set_device(dd);
-    if (sd == dd) B200_CUDA_CHECK(cudaMemcpy(dst->data, src->data, ggml_nbytes(src), cudaMemcpyDeviceToDevice));
-    else          B200_CUDA_CHECK(cudaMemcpyPeer(dst->data, dd, src->data, sd, ggml_nbytes(src)));
+    // device-to-device copies return before they are done and the legacy stream they would run on does not order with
+    // the backend's non-blocking compute streams: copy on the per-thread stream and wait for it (found on a 2-GPU box:
+    // layer split fed the second device the previous token's activations once graph replay made the launch fast enough)
+    if (sd == dd) B200_CUDA_CHECK(cudaMemcpyAsync(dst->data, src->data, ggml_nbytes(src), cudaMemcpyDeviceToDevice, cudaStreamPerThread));
+    else          B200_CUDA_CHECK(cudaMemcpyPeerAsync(dst->data, b200_device(dd).id, src->data, b200_device(sd).id, ggml_nbytes(src), cudaStreamPerThread));
+    B200_CUDA_CHECK(cudaStreamSynchronize(cudaStreamPerThread));
     return true;
 }
 void buf_clear(ggml_backend_buffer_t b, uint8_t v) {

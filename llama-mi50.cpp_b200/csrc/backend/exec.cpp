@@ -28,6 +28,7 @@ struct exec_state {
     const void * xb_src_data = nullptr;
     bool no_tc = env_flag("GGML_B200_DISABLE_TC");
     size_t need_q8 = 0, need_fa = 0, need_xb = 0;   // scratch high-water marks found during the sizing pass
+    size_t need_split_x = 0;           // row split: bytes of the largest activation copied to the other devices
     bool sizing = false;               // sizing pass: compute need_*, launch nothing
     uint64_t launches = 0, chain_phases = 0;
 };
@@ -52,12 +53,126 @@ int map_unary(ggml_unary_op op) {
     }
 }
 
+bool is_split_tensor(const ggml_tensor * t) {
+    ggml_backend_buffer_t buf = t ? (t->view_src ? t->view_src->buffer : t->buffer) : nullptr;
+    return buf && b200_buft_is_split(buf->buft);
+}
+
+// ---- MUL_MAT with a row-split weight -----------------------------------------------------------
+// Replaces ggml_cuda_op_mul_mat (reference ggml-cuda.cu:1452-1770): every device multiplies ITS rows of the weight with
+// the whole activation and the row slices of dst are concatenated on the device that owns dst (never summed).  Like the
+// reference this is driven from the host, once per matmul: the activation is copied to each other device behind an
+// event, the slice runs there on a side stream, and the main stream waits for it.  Unlike the reference there is no
+// copy back: the kernel of a slice stores straight into dst over NVLink peer memory (dst rows [lo, hi), stride of the
+// whole dst).  The decode fast path for row split is the peer-memory decode chain; this path is
+// what makes `--split-mode row` work for every graph shape.
+int run_mul_mat_split(exec_state & st, const ggml_tensor * dst) {
+    const ggml_tensor * w = dst->src[0]; const ggml_tensor * x = dst->src[1];
+    if (dst->op != GGML_OP_MUL_MAT || !is_quant_weight(w->type) || x->type != GGML_TYPE_F32 || dst->type != GGML_TYPE_F32) return B200_ERR_UNSUPPORTED;
+    if (w->ne[2] != 1 || w->ne[3] != 1 || x->ne[2] != 1 || x->ne[3] != 1 || x->ne[0] != w->ne[0]) return B200_ERR_UNSUPPORTED;
+    if (x->nb[0] != 4 || x->nb[1] != (size_t) x->ne[0] * 4 || dst->nb[0] != 4 || dst->nb[1] != (size_t) dst->ne[0] * 4) return B200_ERR_UNSUPPORTED;
+    if (x->ne[1] > 65535) return B200_ERR_UNSUPPORTED;
+    const int64_t K = x->ne[0], ncols = x->ne[1], M = w->ne[1];
+    const int n_dev = b200_n_devices();
+    ggml_backend_buffer_type_t sbt = w->buffer->buft;
+
+    // one slice: weight rows [lo, hi) on `id` (stored at wdata) times the activation at xdata -> dst rows [lo, hi)
+    auto slice = [&](void * wdata, int64_t lo, int64_t hi, void * xdata, char * q8, size_t q8_size, char * xbuf, size_t xb_size, void * stream, bool probe) -> int {
+        ggml_tensor wt = *w; wt.data = wdata; wt.ne[1] = hi - lo;
+        ggml_tensor xt = *x; xt.data = xdata;
+        ggml_tensor dt = *dst; dt.data = (char *) dst->data + (size_t) lo * 4; dt.ne[0] = hi - lo;
+        if (ncols > 8 && !st.no_tc) {
+            b200_mmq_args m{};
+            m.w = b200_desc(&wt); m.x = b200_desc(&xt); m.dst = b200_desc(&dt); m.act_fmt = 0;
+            if (b200_mmq_supported(&m)) {
+                const size_t need = b200_mmq_act_size(K, ncols) + 1024;
+                if (probe) { st.need_xb = std::max(st.need_xb, need); return B200_OK; }
+                GGML_ASSERT(need <= xb_size);
+                char * xb = (char *) (((uintptr_t) xbuf + 1023) & ~(uintptr_t) 1023);
+                B200_KCHECK(b200_mmq_convert_act(&m.x, xb, 0, stream));
+                m.xb = xb;
+                B200_KCHECK(b200_mul_mat_q(&m, stream));
+                st.launches += 2;
+                return B200_OK;
+            }
+        }
+        b200_mmvq_args a{};
+        a.w = b200_desc(&wt);
+        a.xq_ne0_padded = pad_to(K, B200_MATRIX_ROW_PADDING);
+        for (int i = 0; i < 4; ++i) a.x_ne[i] = x->ne[i];
+        a.dst = b200_desc(&dt);
+        a.glu_op = B200_GLU_NONE;
+        const int nwin = (int) ((ncols + 7) / 8);
+        for (int wi = 0; wi < nwin; ++wi) {
+            if (nwin > 1) { a.col_begin = wi * 8; a.col_count = (int) std::min<int64_t>(8, ncols - wi * 8); }
+            if (!b200_mmvq_supported(&a)) return B200_ERR_UNSUPPORTED;
+            if (wi > 0 && wi < nwin - 1) wi = nwin - 2;
+        }
+        const b200_tensor tx = b200_desc(&xt);
+        const size_t q8_bytes = b200_q8_1_buffer_size(&tx, a.xq_ne0_padded);
+        if (probe) { st.need_q8 = std::max(st.need_q8, q8_bytes); return B200_OK; }
+        GGML_ASSERT(q8_bytes <= q8_size);
+        B200_KCHECK(b200_quantize_q8_1(&tx, q8, a.xq_ne0_padded, stream));
+        a.xq = q8;
+        for (int wi = 0; wi < nwin; ++wi) {
+            if (nwin > 1) { a.col_begin = wi * 8; a.col_count = (int) std::min<int64_t>(8, ncols - wi * 8); }
+            B200_KCHECK(b200_mul_mat_vec_q(&a, stream));
+            st.launches++;
+        }
+        st.launches++;
+        return B200_OK;
+    };
+
+    if (st.validate || st.sizing) {
+        // shapes only: a slice of 128 rows (or the whole matrix) at a dummy 256 B-aligned address
+        int64_t lo = 0, hi = 0;
+        if (st.validate) {
+            // like the reference (ggml-cuda.cu:4568-4581): a device without rows of a small matrix declines the op
+            const int dev = st.ctx ? st.ctx->device : -1;
+            if (dev >= 0) { b200_split_rows(sbt, M, dev, lo, hi); if (lo == hi) return B200_ERR_UNSUPPORTED; }
+        }
+        const int rc = slice((void *) 0x1000, 0, M, (void *) 0x1000, nullptr, 0, nullptr, 0, B200_STREAM_VALIDATE, true);
+        if (rc == B200_OK && st.sizing) st.need_split_x = std::max(st.need_split_x, (size_t) K * (size_t) ncols * 4);
+        return rc;
+    }
+
+    const b200_split_extra * e = (const b200_split_extra *) w->extra;
+    GGML_ASSERT(e && "row-split weight without per-device slices");
+    b200_context * ctx = st.ctx;
+    const int main_dev = ctx->device;
+    st.q8_src = nullptr; st.xb_src = nullptr;                 // the main device's scratch arenas are reused below
+    bool remote = false;
+    for (int id = 0; id < n_dev; ++id) remote = remote || (id != main_dev && e->row_hi[id] > e->row_lo[id]);
+    if (remote) B200_CUDA_CHECK(cudaEventRecord(ctx->split_fork, (cudaStream_t) st.stream));
+    for (int id = 0; id < n_dev; ++id) {
+        const int64_t lo = e->row_lo[id], hi = e->row_hi[id];
+        if (hi == lo) continue;
+        if (id == main_dev) {
+            B200_KCHECK(slice(e->data[id], lo, hi, x->data, ctx->q8_scratch, ctx->q8_size, ctx->xb_scratch, ctx->xb_size, st.stream, false));
+            continue;
+        }
+        b200_split_dev & sd = ctx->split[id];
+        b200_set_device(id);
+        B200_CUDA_CHECK(cudaStreamWaitEvent(sd.stream, ctx->split_fork, 0));      // x is ready and the old contents of dst are dead
+        const size_t xbytes = (size_t) K * (size_t) ncols * 4;
+        GGML_ASSERT(xbytes <= sd.x_size);
+        B200_CUDA_CHECK(cudaMemcpyPeerAsync(sd.x, b200_device(id).id, x->data, b200_device(main_dev).id, xbytes, sd.stream));
+        B200_KCHECK(slice(e->data[id], lo, hi, sd.x, sd.q8, sd.q8_size, sd.xb, sd.xb_size, sd.stream, false));
+        B200_CUDA_CHECK(cudaEventRecord(sd.done, sd.stream));
+    }
+    b200_set_device(main_dev);
+    for (int id = 0; id < n_dev; ++id)
+        if (id != main_dev && e->row_hi[id] > e->row_lo[id]) B200_CUDA_CHECK(cudaStreamWaitEvent((cudaStream_t) st.stream, ctx->split[id].done, 0));
+    return B200_OK;
+}
+
 // ---- MUL_MAT / MUL_MAT_ID -------------------------------------------------------------------
 // quantize src1 into the q8_1 arena (unless it is already there) and run the GEMV in <= 8-column windows
 int run_mul_mat(exec_state & st, const ggml_tensor * dst, const ggml_tensor * bias, const ggml_tensor * gate,
                 const ggml_tensor * gate_bias, int glu_op, float alpha, float limit) {
     const ggml_tensor * w = dst->src[0]; const ggml_tensor * x = dst->src[1];
     const ggml_tensor * ids = dst->op == GGML_OP_MUL_MAT_ID ? dst->src[2] : nullptr;
+    if (is_split_tensor(w)) return (bias || gate || ids) ? B200_ERR_UNSUPPORTED : run_mul_mat_split(st, dst);
     if (!is_quant_weight(w->type) || x->type != GGML_TYPE_F32 || dst->type != GGML_TYPE_F32) return B200_ERR_UNSUPPORTED;
     if (x->nb[0] != sizeof(float) || x->ne[0] != w->ne[0]) return B200_ERR_UNSUPPORTED;
     if (x->ne[1] > 65535 || x->ne[2] * x->ne[3] > 65535) return B200_ERR_UNSUPPORTED;
@@ -217,6 +332,8 @@ bool b200_supports_op(int device, const ggml_tensor * op) {
         if (buf && b200_buft_is_split(buf->buft) && op->op != GGML_OP_MUL_MAT) return false;
     }
     exec_state st;   // validation mode
+    b200_context probe_ctx; probe_ctx.device = device;      // only the device id is read in validation mode
+    st.ctx = &probe_ctx;
     return run_node(st, op) == B200_OK;
 }
 
@@ -266,6 +383,8 @@ struct b200_graph_cache {
         chains.clear(); plan_built = false;
         if (redirect_buf) { cudaFree(redirect_buf); redirect_buf = nullptr; }
     }
+    bool has_split = false;            // the graph multiplies row-split weights: no chain, no CUDA-graph capture (like the
+                                       // reference, ggml-cuda.cu:2883) — the slices run on other devices' streams
     std::vector<node_key> keys;        // properties of the graph last seen
     cudaGraphExec_t exec = nullptr;    // instantiated capture of `keys` (or null)
     uint64_t kernels = 0;              // kernel nodes in `exec`
@@ -300,7 +419,7 @@ int run_fused(exec_state & st, ggml_cgraph * g, int i, bool fusion, int node_lim
             }
         }
         // {MUL_MAT(gate), MUL_MAT(up), GLU} on one activation column (reference: ggml-cuda.cu:3737-3771)
-        if (n->op == GGML_OP_MUL_MAT && i + 2 < node_limit && n->ne[1] == 1 && n->ne[2] == 1 && n->ne[3] == 1) {
+        if (n->op == GGML_OP_MUL_MAT && !is_split_tensor(n->src[0]) && i + 2 < node_limit && n->ne[1] == 1 && n->ne[2] == 1 && n->ne[3] == 1) {
             ggml_tensor * m2 = g->nodes[i + 1]; ggml_tensor * glu = g->nodes[i + 2];
             if (m2->op == GGML_OP_MUL_MAT && glu->op == GGML_OP_GLU && m2->src[1] == n->src[1] && glu->src[0] && glu->src[1] &&
                 ((glu->src[0] == n && glu->src[1] == m2) || (glu->src[0] == m2 && glu->src[1] == n)) &&
@@ -320,7 +439,7 @@ int run_fused(exec_state & st, ggml_cgraph * g, int i, bool fusion, int node_lim
             }
         }
         // {MUL_MAT, ADD} with a single column: the addend (bias or residual stream) rides in the GEMV epilogue
-        if (n->op == GGML_OP_MUL_MAT && i + 1 < node_limit && n->ne[1] == 1 && n->ne[2] == 1 && n->ne[3] == 1) {
+        if (n->op == GGML_OP_MUL_MAT && !is_split_tensor(n->src[0]) && i + 1 < node_limit && n->ne[1] == 1 && n->ne[2] == 1 && n->ne[3] == 1) {
             ggml_tensor * add = g->nodes[i + 1];
             if (add->op == GGML_OP_ADD && (add->src[0] == n || add->src[1] == n) && ggml_node_has_n_uses(g, i, 1) && same_shape(add, n)) {
                 const ggml_tensor * other = add->src[0] == n ? add->src[1] : add->src[0];
@@ -452,7 +571,11 @@ ggml_status b200_graph_compute(b200_context * ctx, ggml_cgraph * g) {
     for (int i = 0; same && i < g->n_nodes; ++i) same = key_matches(g->nodes[i], c.keys[(size_t) i]);
     if (!same) {
         c.keys.resize((size_t) g->n_nodes);
-        for (int i = 0; i < g->n_nodes; ++i) make_key(g->nodes[i], c.keys[(size_t) i]);
+        c.has_split = false;
+        for (int i = 0; i < g->n_nodes; ++i) {
+            make_key(g->nodes[i], c.keys[(size_t) i]);
+            c.has_split = c.has_split || (g->nodes[i]->op == GGML_OP_MUL_MAT && is_split_tensor(g->nodes[i]->src[0]));
+        }
         c.seen = 0;
         if (c.exec) { cudaGraphExecDestroy(c.exec); c.exec = nullptr; }
         if (!c.chains.empty()) B200_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));   // a chain of the previous graph may still be running
@@ -471,7 +594,8 @@ ggml_status b200_graph_compute(b200_context * ctx, ggml_cgraph * g) {
         launched = c.kernels; replay = true;
     } else {
         // 2. size the scratch arenas (no launches)
-        if (!no_chain && !c.plan_built) {
+        const bool use_chain = !no_chain && !c.has_split;
+        if (use_chain && !c.plan_built) {
             b200_plan_build(g, c.plan); c.plan_built = true;
             if (env_flag("GGML_B200_PRINT_PLAN")) {
                 int phases = 0, chains = 0, plain = 0; bool in_chain = false;
@@ -486,15 +610,38 @@ ggml_status b200_graph_compute(b200_context * ctx, ggml_cgraph * g) {
             }
             if (c.plan.redirect_bytes > 0) B200_CUDA_CHECK(cudaMalloc((void **) &c.redirect_buf, (size_t) c.plan.redirect_bytes));
         }
-        auto walk = [&](exec_state & s) { if (no_chain) walk_graph(s, g, !no_fusion); else walk_plan(s, g, c, true); };
+        auto walk = [&](exec_state & s) { if (!use_chain) walk_graph(s, g, !no_fusion); else walk_plan(s, g, c, true); };
         exec_state sz; sz.ctx = ctx; sz.validate = false; sz.sizing = true;
         walk(sz);
         grow(ctx, ctx->q8_scratch, ctx->q8_size, sz.need_q8, false);
         grow(ctx, ctx->fa_scratch, ctx->fa_size, sz.need_fa, true);
         grow(ctx, ctx->xb_scratch, ctx->xb_size, sz.need_xb, false);
+        if (sz.need_split_x > 0) {      // row split: a stream, an event and the same scratch arenas on every other device
+            if (!ctx->split_fork) B200_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->split_fork, cudaEventDisableTiming));
+            auto grow_on = [&](char *& p, size_t & cur, size_t need) {
+                if (need <= cur) return;
+                B200_CUDA_CHECK(cudaDeviceSynchronize());
+                if (p) B200_CUDA_CHECK(cudaFree(p));
+                cur = (need + (1u << 20)) & ~((size_t) (1u << 20) - 1);
+                B200_CUDA_CHECK(cudaMalloc((void **) &p, cur));
+            };
+            for (int id = 0; id < b200_n_devices(); ++id) {
+                if (id == ctx->device) continue;
+                b200_split_dev & sd = ctx->split[id];
+                b200_set_device(id);
+                if (!sd.stream) {
+                    B200_CUDA_CHECK(cudaStreamCreateWithFlags(&sd.stream, cudaStreamNonBlocking));
+                    B200_CUDA_CHECK(cudaEventCreateWithFlags(&sd.done, cudaEventDisableTiming));
+                }
+                grow_on(sd.x, sd.x_size, sz.need_split_x);
+                grow_on(sd.q8, sd.q8_size, sz.need_q8);
+                grow_on(sd.xb, sd.xb_size, sz.need_xb);
+            }
+            b200_set_device(ctx->device);
+        }
 
         // 3. run, capturing into a CUDA graph from the second identical submission on
-        const bool capture = !no_graphs && c.seen >= 2;
+        const bool capture = !no_graphs && !c.has_split && c.seen >= 2;
         exec_state st; st.ctx = ctx; st.validate = false; st.stream = ctx->stream;
         if (capture) B200_CUDA_CHECK(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed));
         walk(st);
@@ -532,6 +679,18 @@ void b200_context_free(b200_context * ctx) {
     if (ctx->q8_scratch) cudaFree(ctx->q8_scratch);
     if (ctx->fa_scratch) cudaFree(ctx->fa_scratch);
     if (ctx->xb_scratch) cudaFree(ctx->xb_scratch);
+    for (int id = 0; id < B200_MAX_DEVICES; ++id) {
+        b200_split_dev & sd = ctx->split[id];
+        if (!sd.stream) continue;
+        b200_set_device(id);
+        cudaStreamSynchronize(sd.stream);
+        if (sd.x) cudaFree(sd.x);
+        if (sd.q8) cudaFree(sd.q8);
+        if (sd.xb) cudaFree(sd.xb);
+        cudaEventDestroy(sd.done); cudaStreamDestroy(sd.stream);
+    }
+    b200_set_device(ctx->device);
+    if (ctx->split_fork) cudaEventDestroy(ctx->split_fork);
     if (ctx->ev_begin) cudaEventDestroy(ctx->ev_begin);
     if (ctx->ev_end) cudaEventDestroy(ctx->ev_end);
     cudaStreamDestroy(ctx->stream);

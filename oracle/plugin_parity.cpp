@@ -2,6 +2,7 @@
 // backend THROUGH the reference's own public API (llama.h): the same GGUF model decodes the same tokens once on the CPU
 // backend and once with every layer offloaded to the plugin; the logits of every step are compared (NMSE).
 // usage: plugin-parity model.gguf backend_dir plugin.so [n_prompt n_decode tol]
+// B200_PARITY_SPLIT_ROW=1: the plugin run uses --split-mode row (weights in the backend's split buffer type).
 #include "llama.h"
 #include "ggml.h"
 #include "ggml-backend.h"
@@ -14,6 +15,7 @@
 static std::vector<std::vector<float>> run(const char * path, int ngl, int n_prompt, int n_decode) {
     llama_model_params mp = llama_model_default_params();
     mp.n_gpu_layers = ngl;
+    if (ngl > 0 && getenv("B200_PARITY_SPLIT_ROW")) mp.split_mode = LLAMA_SPLIT_MODE_ROW;
     llama_model * m = llama_model_load_from_file(path, mp);
     if (!m) { fprintf(stderr, "model load failed\n"); exit(3); }
     const int n_vocab = llama_vocab_n_tokens(llama_model_get_vocab(m));
