@@ -525,6 +525,11 @@ void walk_plan(exec_state & st, ggml_cgraph * g, b200_graph_cache & c, bool fusi
             continue;
         }
         if (it.first_node < next_node) continue;                  // consumed by a fusion of the previous plain node
+        {   // nodes that launch nothing (views, reshapes, empty or non-compute tensors) must not cut the chain in two
+            const ggml_tensor * n = g->nodes[it.first_node];
+            if (it.n_nodes <= 1 && (n->op == GGML_OP_NONE || n->op == GGML_OP_VIEW || n->op == GGML_OP_RESHAPE || n->op == GGML_OP_PERMUTE ||
+                                    n->op == GGML_OP_TRANSPOSE || ggml_is_empty(n) || (n->flags & GGML_TENSOR_FLAG_COMPUTE) == 0)) continue;
+        }
         flush_chain(st, c, pending, seq);
         int limit = g->n_nodes;                                   // plain-node fusions stop where the next phase begins
         for (size_t j = k + 1; j < items.size(); ++j) if (items[j].kind == B200_ITEM_PHASE || items[j].hoisted) { limit = items[j].first_node; break; }
