@@ -277,7 +277,9 @@ def main_b200(a):
                   "bytes_per_launch_avg": int(wbytes / max(gemv_n, 1)), "us_per_launch_avg": round(gemv_ms * 1e3 / max(gemv_n, 1), 3)}
     traffic = None
     try:   # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch from the committed ncu --set full capture (profiles/)
-        with open(os.path.join(ROOT, "profiles", "r01_chain_ncu_summary.json")) as f:
+        # latest committed `ncu --set full` capture of the 1-GPU chain kernel (tools/ncu_summary.py)
+        caps = sorted(x for x in os.listdir(os.path.join(ROOT, "profiles")) if x.endswith("_chain_ncu_summary.json"))
+        with open(os.path.join(ROOT, "profiles", caps[-1])) as f:
             traffic = json.load(f).get("dram_bytes_per_launch") if chain_mode and world == 1 else None   # the capture is the 1-GPU chain
     except Exception:
         traffic = None
