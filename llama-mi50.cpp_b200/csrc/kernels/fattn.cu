@@ -8,6 +8,8 @@
 // once per group.  Inside a warp, LPR = D/8 lanes own one K/V row (each lane 8 consecutive
 // elements: one 128-bit load for f16, 8 B + scale for q8_0) and 32/LPR "row slots" run in parallel,
 // each with a private online-softmax state; states are merged once per block in shared memory.
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -21,32 +23,46 @@ struct fattn_params {
     float * part; int * counters;
 };
 
-template <int KVT> struct kvload;
-template <> struct kvload<B200_F16> {
-    static __device__ __forceinline__ void load(const char * row, int sub, float f[8]) {
-        const uint4 r = *(const uint4 *) (row + 16 * sub);
+// raw K/V bytes of one lane's 8 elements, kept unconverted while the loads are in flight
+template <int KVT> struct kvraw;
+template <> struct kvraw<B200_F16> {
+    uint4 r;
+    __device__ __forceinline__ void load(const char * row, int sub) { r = *(const uint4 *) (row + 16 * sub); }
+    __device__ __forceinline__ void zero() { r = make_uint4(0u, 0u, 0u, 0u); }
+    __device__ __forceinline__ void expand(float f[8]) const {
         const __half2 * h = (const __half2 *) &r;
 #pragma unroll
         for (int i = 0; i < 4; ++i) { const float2 t = __half22float2(h[i]); f[2 * i] = t.x; f[2 * i + 1] = t.y; }
     }
 };
-template <> struct kvload<B200_Q8_0> {
-    static __device__ __forceinline__ void load(const char * row, int sub, float f[8]) {
+template <> struct kvraw<B200_Q8_0> {
+    uint32_t q0, q1; float d;          // 8 int8 + the block scale
+    __device__ __forceinline__ void load(const char * row, int sub) {
         const char * b = row + (sub >> 2) * 34;
-        const float d = __half2float(*(const __half *) b);
-        const uint16_t * qs = (const uint16_t *) (b + 2 + 8 * (sub & 3));
+        d = __half2float(*(const __half *) b);
+        const uint16_t * qs = (const uint16_t *) (b + 2 + 8 * (sub & 3));      // 2-byte aligned
+        q0 = (uint32_t) qs[0] | ((uint32_t) qs[1] << 16); q1 = (uint32_t) qs[2] | ((uint32_t) qs[3] << 16);
+    }
+    __device__ __forceinline__ void zero() { q0 = q1 = 0u; d = 0.0f; }
+    __device__ __forceinline__ void expand(float f[8]) const {
+        // int8 -> f16 without I2F: (q ^ 0x80) | 0x6400 is exactly 1024 + 128 + q; minus 1152
+        const __half2 off = __float2half2_rn(1152.0f);
+        const uint32_t w[2] = {q0 ^ 0x80808080u, q1 ^ 0x80808080u};
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const uint16_t w = qs[i];
-            f[2 * i] = d * (float) (int8_t) (w & 0xff);
-            f[2 * i + 1] = d * (float) (int8_t) (w >> 8);
+        for (int i = 0; i < 2; ++i) {
+            const uint32_t lo = __byte_perm(w[i], 0x64646464u, 0x4140), hi = __byte_perm(w[i], 0x64646464u, 0x4342);
+            const float2 a = __half22float2(__hsub2(*(const __half2 *) &lo, off)), b = __half22float2(__hsub2(*(const __half2 *) &hi, off));
+            f[4 * i] = d * a.x; f[4 * i + 1] = d * a.y; f[4 * i + 2] = d * b.x; f[4 * i + 3] = d * b.y;
         }
     }
 };
 
+// U = row steps of a warp whose K / V / mask requests are issued together before any arithmetic (bytes in flight per
+// warp = U * 32 lanes * 32 B): the loop is bound by HBM latency otherwise.  One online-softmax update per U rows.
 template <int D, int KVT, int NCOLS>
 __global__ void __launch_bounds__(128) fattn_vec_kernel(const fattn_params p) {
     constexpr int LPR = D / 8, RPI = 32 / LPR, NW = 4, NSTATE = NW * RPI, ST = D + 2;
+    constexpr int U = NCOLS >= 5 ? 2 : 4;
     extern __shared__ float sm[];   // [NSTATE][NCOLS][ST]: acc[D], m, l
     __shared__ int s_last;
     pdl_launch_dependents();
@@ -58,6 +74,7 @@ __global__ void __launch_bounds__(128) fattn_vec_kernel(const fattn_params p) {
     // column c of this chunk -> (query position j, head)
     int cj[NCOLS], ch[NCOLS]; bool cact[NCOLS]; float slope[NCOLS];
     float qreg[NCOLS][8];
+    const char * mrow[NCOLS];        // mask row of the column (null: no mask)
     pdl_wait();
 #pragma unroll
     for (int c = 0; c < NCOLS; ++c) {
@@ -73,10 +90,18 @@ __global__ void __launch_bounds__(128) fattn_vec_kernel(const fattn_params p) {
             const uint32_t h = (uint32_t) ch[c];
             slope[c] = h < p.n_head_log2 ? powf(p.m0, (float) (h + 1)) : powf(p.m1, (float) (2 * (h - p.n_head_log2) + 1));
         }
+        mrow[c] = p.mask && cact[c] ? p.mask + (int64_t) cj[c] * p.m_nb1 + (int64_t) (ch[c] % p.m_ne2) * p.m_nb2 + (int64_t) (seq % p.m_ne3) * p.m_nb3 : nullptr;
     }
+    // decode (one query position, mask not per head): every column reads the same mask row -> one load per row step
+    bool mask_uniform = true;
+#pragma unroll
+    for (int c = 1; c < NCOLS; ++c) mask_uniform = mask_uniform && (!cact[c] || mrow[c] == mrow[0]);
+    // "nothing seen yet" is a large finite value, not -inf: exp(m_old - m_new) and exp(s - m) then need no special cases
+    // (a masked score is -inf and gives exp(-inf) = 0); the state written out below turns it back into -inf
+    constexpr float M_NONE = -1.0e30f;
     float m[NCOLS], l[NCOLS], acc[NCOLS][8];
 #pragma unroll
-    for (int c = 0; c < NCOLS; ++c) { m[c] = -INFINITY; l[c] = 0.0f;
+    for (int c = 0; c < NCOLS; ++c) { m[c] = M_NONE; l[c] = 0.0f;
 #pragma unroll
         for (int i = 0; i < 8; ++i) acc[c][i] = 0.0f; }
 
@@ -84,42 +109,88 @@ __global__ void __launch_bounds__(128) fattn_vec_kernel(const fattn_params p) {
     const char * kb = p.k + (int64_t) hkv * p.k_nb2 + (int64_t) seq * p.k_nb3;
     const char * vb = p.v + (int64_t) hkv * p.v_nb2 + (int64_t) seq * p.v_nb3;
 
-    for (int base = kv0 + warp * RPI; base < kv1; base += NW * RPI) {
-        const int r = base + rsel;
-        const bool valid = r < kv1;
-        float kf[8], vf[8];
-        if (valid) { kvload<KVT>::load(kb + (int64_t) r * p.k_nb1, sub, kf); kvload<KVT>::load(vb + (int64_t) r * p.v_nb1, sub, vf); }
-        else {
+    for (int base = kv0 + warp * (U * RPI); base < kv1; base += NW * U * RPI) {
+        // ---- all requests of the U row steps first.  A row step past the end re-reads the last row and is masked out.
+        kvraw<KVT> kr[U], vr[U];
+        float mk[U][NCOLS];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) { kf[i] = 0.0f; vf[i] = 0.0f; }
+        for (int u = 0; u < U; ++u) {
+            const int r0 = base + u * RPI + rsel;
+            const int r = min(r0, kv1 - 1);
+            kr[u].load(kb + (int64_t) r * p.k_nb1, sub); vr[u].load(vb + (int64_t) r * p.v_nb1, sub);
+            const float dead = r0 < kv1 ? 0.0f : -INFINITY;
+            if (p.mask) {
+                if (mask_uniform) {
+                    const float t = (mrow[0] ? __half2float(*(const __half *) (mrow[0] + (int64_t) r * 2)) : 0.0f) + dead;
+#pragma unroll
+                    for (int c = 0; c < NCOLS; ++c) mk[u][c] = slope[c] * t;
+                } else {
+#pragma unroll
+                    for (int c = 0; c < NCOLS; ++c) mk[u][c] = slope[c] * ((mrow[c] ? __half2float(*(const __half *) (mrow[c] + (int64_t) r * 2)) : 0.0f) + dead);
+                }
+            } else {
+#pragma unroll
+                for (int c = 0; c < NCOLS; ++c) mk[u][c] = dead;
+            }
         }
+        // ---- scores of the U x NCOLS (row, column) pairs
+        float s[U][NCOLS];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            float kf[8];
+            kr[u].expand(kf);
+#pragma unroll
+            for (int c = 0; c < NCOLS; ++c) {
+                float t = 0.0f;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) t += qreg[c][i] * kf[i];
+                s[u][c] = t;
+            }
+        }
+#pragma unroll
+        for (int o = LPR / 2; o > 0; o >>= 1) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+#pragma unroll
+                for (int c = 0; c < NCOLS; ++c) s[u][c] += __shfl_xor_sync(0xffffffffu, s[u][c], o);
+            }
+        }
+        // ---- one (branch-free) online-softmax update per column for the U rows; columns past ncols_total carry q = 0
+        // and are never written out
 #pragma unroll
         for (int c = 0; c < NCOLS; ++c) {
-            float s = 0.0f;
+            float mx = m[c];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) s += qreg[c][i] * kf[i];
-#pragma unroll
-            for (int o = LPR / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-            if (p.softcap != 0.0f) s = p.softcap * tanhf(s);
-            if (p.mask && valid && cact[c]) {
-                const __half mv = *(const __half *) (p.mask + (int64_t) r * 2 + (int64_t) cj[c] * p.m_nb1 +
-                                                     (int64_t) (ch[c] % p.m_ne2) * p.m_nb2 + (int64_t) (seq % p.m_ne3) * p.m_nb3);
-                s += slope[c] * __half2float(mv);
+            for (int u = 0; u < U; ++u) {
+                float t = s[u][c];
+                if (p.softcap != 0.0f) t = p.softcap * tanhf(t);
+                t += mk[u][c];
+                s[u][c] = t;
+                mx = fmaxf(mx, t);
             }
-            if (!valid || !cact[c]) s = -INFINITY;
-            if (s > m[c]) {
-                const float corr = expf(m[c] - s);   // m = -inf -> 0
-                l[c] *= corr;
+            const float corr = __expf(m[c] - mx);
+            m[c] = mx;
+            float ls = 0.0f;
 #pragma unroll
-                for (int i = 0; i < 8; ++i) acc[c][i] *= corr;
-                m[c] = s;
+            for (int u = 0; u < U; ++u) { s[u][c] = __expf(s[u][c] - mx); ls += s[u][c]; }
+            l[c] = l[c] * corr + ls;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) acc[c][i] *= corr;
+        }
+        // ---- V accumulation
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            float vf[8];
+            vr[u].expand(vf);
+#pragma unroll
+            for (int c = 0; c < NCOLS; ++c) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) acc[c][i] += s[u][c] * vf[i];
             }
-            const float pr = s == -INFINITY ? 0.0f : expf(s - m[c]);
-            l[c] += pr;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) acc[c][i] += pr * vf[i];
         }
     }
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) if (m[c] <= 0.5f * M_NONE) m[c] = -INFINITY;      // no unmasked row: the merges below test for -inf
 
     // ---- merge the NSTATE per-slot states of this block
     const int state = warp * RPI + rsel;
@@ -171,22 +242,62 @@ __global__ void __launch_bounds__(128) fattn_vec_kernel(const fattn_params p) {
     __syncthreads();
     if (!s_last) return;
     __threadfence();
+    // The partials of the n_split blocks are independent loads: a first pass (threads over splits) turns the per-split
+    // maxima into weights in shared memory, a second pass (threads over output elements) sums with 8 loads in flight.
+    // (The first version walked the splits one dependent L2 round trip at a time: ~40 us of an 87 us launch at 64 splits.)
     const float * all = p.part + grp_lin * p.n_split * NCOLS * ST;
+    float * s_w = sm;                                   // [NCOLS][n_split] weights; reuses the state area (all reads of it are done)
+    __shared__ float s_red[NCOLS][4], s_M[NCOLS], s_L[NCOLS];
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) {
+        float M = -INFINITY;
+        for (int sp = threadIdx.x; sp < p.n_split; sp += 128) M = fmaxf(M, all[((int64_t) sp * NCOLS + c) * ST + D]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
+        if (lane == 0) s_red[c][warp] = M;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) {
+        float M = fmaxf(fmaxf(s_red[c][0], s_red[c][1]), fmaxf(s_red[c][2], s_red[c][3]));
+        const int ci = chunk * NCOLS + c;
+        const int h = hkv * p.gqa + (ci < p.ncols_total ? ci % p.gqa : 0);
+        float Lsink = 0.0f;
+        if (p.sinks && ci < p.ncols_total) { const float sk = p.sinks[h]; const float Mn = fmaxf(M, sk); Lsink = expf(sk - Mn); M = Mn; }
+        float L = 0.0f;
+        for (int sp = threadIdx.x; sp < p.n_split; sp += 128) {
+            const float * o = all + ((int64_t) sp * NCOLS + c) * ST;
+            const float w = o[D] == -INFINITY ? 0.0f : expf(o[D] - M);
+            s_w[c * p.n_split + sp] = w;
+            L += w * o[D + 1];
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) L += __shfl_xor_sync(0xffffffffu, L, o);
+        __syncthreads();                                // s_red of this column has been read by everyone
+        if (lane == 0) s_red[c][warp] = L;
+        __syncthreads();
+        if (threadIdx.x == 0) { s_M[c] = M; s_L[c] = s_red[c][0] + s_red[c][1] + s_red[c][2] + s_red[c][3] + Lsink; }
+    }
+    __syncthreads();
     for (int e = threadIdx.x; e < NCOLS * D; e += 128) {
         const int c = e / D, d = e % D;
         const int ci = chunk * NCOLS + c;
         if (ci >= p.ncols_total) continue;
-        float M = -INFINITY;
-        for (int s = 0; s < p.n_split; ++s) M = fmaxf(M, all[((int64_t) s * NCOLS + c) * ST + D]);
         const int j = ci / p.gqa, h = hkv * p.gqa + ci % p.gqa;
-        float A = 0.0f, L = 0.0f;
-        if (p.sinks) { const float sk = p.sinks[h]; const float Mn = fmaxf(M, sk); L = expf(sk - Mn); M = Mn; }
-        for (int s = 0; s < p.n_split; ++s) {
-            const float * o = all + ((int64_t) s * NCOLS + c) * ST;
-            const float w = o[D] == -INFINITY ? 0.0f : expf(o[D] - M);
-            A += w * o[d]; L += w * o[D + 1];
+        const float * col = all + (int64_t) c * ST + d;
+        const float * w = s_w + c * p.n_split;
+        float A = 0.0f;
+        int sp = 0;
+        for (; sp + 8 <= p.n_split; sp += 8) {
+            float v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = col[(int64_t) (sp + u) * NCOLS * ST];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) A += w[sp + u] * v[u];
         }
-        ((float *) (p.dst + (int64_t) h * p.d_nb1 + (int64_t) j * p.d_nb2 + (int64_t) seq * p.d_nb3))[d] = A / L;
+        for (; sp < p.n_split; ++sp) A += w[sp] * col[(int64_t) sp * NCOLS * ST];
+        ((float *) (p.dst + (int64_t) h * p.d_nb1 + (int64_t) j * p.d_nb2 + (int64_t) seq * p.d_nb3))[d] = A / s_L[c];
     }
 }
 
@@ -215,15 +326,16 @@ static bool fattn_make_plan(const b200_fattn_args * a, fattn_plan & pl) {
     }
     if (a->sinks && (a->sinks->type != B200_F32 || a->sinks->ne[0] != H || a->sinks->nb[0] != 4)) return false;
     pl.ncols_total = (int) (gqa * n_q);
-    pl.ncols = pl.ncols_total >= 8 ? 8 : pl.ncols_total > 2 ? 4 : pl.ncols_total;   // 1, 2, 4, 8
+    pl.ncols = pl.ncols_total >= 8 ? 8 : pl.ncols_total;   // 1..8: a GQA group of 5 (Qwen2.5-32B) or 6 pays for no idle columns
     pl.n_chunks = (pl.ncols_total + pl.ncols - 1) / pl.ncols;
     pl.n_groups = (int64_t) H_kv * pl.n_chunks * n_seq;
     if (H_kv * pl.n_chunks > 65535 || n_seq > 65535) return false;
-    // enough blocks for ~4 per SM, at least 256 KV positions per split
-    const int64_t target = 4 * 148;
+    // enough blocks for ~6 per SM (bytes in flight), at least 256 KV positions per split
+    const int64_t target = 6 * 148;
     int64_t ns = (target + pl.n_groups - 1) / pl.n_groups;
     const int64_t max_ns = (n_kv + 255) / 256;
     if (ns > max_ns) ns = max_ns;
+    if (ns > 512) ns = 512;            // the combine keeps one weight per (column, split) in shared memory
     if (ns < 1) ns = 1;
     pl.kv_per_split = (int) (((n_kv + ns - 1) / ns + 31) / 32 * 32);
     pl.n_split = (int) ((n_kv + pl.kv_per_split - 1) / pl.kv_per_split);
@@ -235,11 +347,15 @@ static bool fattn_make_plan(const b200_fattn_args * a, fattn_plan & pl) {
 template <int D, int KVT>
 static void fattn_launch_nc(const fattn_params & p, int ncols, dim3 grid, cudaStream_t st) {
     constexpr int RPI = 32 / (D / 8);
-    const size_t smem = (size_t) 4 * RPI * ncols * (D + 2) * 4;
+    const size_t smem = std::max((size_t) 4 * RPI * ncols * (D + 2) * 4, (size_t) ncols * p.n_split * 4);
     switch (ncols) {
         case 1: fattn_vec_kernel<D, KVT, 1><<<grid, 128, smem, st>>>(p); break;
         case 2: fattn_vec_kernel<D, KVT, 2><<<grid, 128, smem, st>>>(p); break;
+        case 3: fattn_vec_kernel<D, KVT, 3><<<grid, 128, smem, st>>>(p); break;
         case 4: fattn_vec_kernel<D, KVT, 4><<<grid, 128, smem, st>>>(p); break;
+        case 5: fattn_vec_kernel<D, KVT, 5><<<grid, 128, smem, st>>>(p); break;
+        case 6: fattn_vec_kernel<D, KVT, 6><<<grid, 128, smem, st>>>(p); break;
+        case 7: fattn_vec_kernel<D, KVT, 7><<<grid, 128, smem, st>>>(p); break;
         default: fattn_vec_kernel<D, KVT, 8><<<grid, 128, smem, st>>>(p); break;
     }
 }
