@@ -62,7 +62,7 @@ template <> struct kvraw<B200_Q8_0> {
 template <int D, int KVT, int NCOLS>
 __global__ void __launch_bounds__(128) fattn_vec_kernel(const fattn_params p) {
     constexpr int LPR = D / 8, RPI = 32 / LPR, NW = 4, NSTATE = NW * RPI, ST = D + 2;
-    constexpr int U = NCOLS >= 5 ? 2 : 4;
+    constexpr int U = NCOLS >= 3 ? 2 : 4;
     extern __shared__ float sm[];   // [NSTATE][NCOLS][ST]: acc[D], m, l
     __shared__ int s_last;
     pdl_launch_dependents();
@@ -109,30 +109,40 @@ __global__ void __launch_bounds__(128) fattn_vec_kernel(const fattn_params p) {
     const char * kb = p.k + (int64_t) hkv * p.k_nb2 + (int64_t) seq * p.k_nb3;
     const char * vb = p.v + (int64_t) hkv * p.v_nb2 + (int64_t) seq * p.v_nb3;
 
+    // software pipeline: the requests of the NEXT U row steps are issued before the arithmetic of the current ones, so a
+    // warp always has 2 x U row steps of K/V bytes in flight (3 warps per scheduler do not hide HBM latency otherwise:
+    // ncu showed long-scoreboard as the top stall at 41 % issue utilisation)
+    kvraw<KVT> kn[U], vn[U];
+    float mn[U];                     // uniform mask value of the row (+ -inf past the end), fetched with the row
+    auto request = [&](int base) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int r0 = base + u * RPI + rsel;
+            const int r = max(min(r0, kv1 - 1), kv0);
+            kn[u].load(kb + (int64_t) r * p.k_nb1, sub); vn[u].load(vb + (int64_t) r * p.v_nb1, sub);
+            mn[u] = r0 < kv1 ? 0.0f : -INFINITY;
+            if (p.mask && mask_uniform && mrow[0]) mn[u] += __half2float(*(const __half *) (mrow[0] + (int64_t) r * 2));
+        }
+    };
+    if (kv0 < kv1) request(kv0 + warp * (U * RPI));
     for (int base = kv0 + warp * (U * RPI); base < kv1; base += NW * U * RPI) {
-        // ---- all requests of the U row steps first.  A row step past the end re-reads the last row and is masked out.
         kvraw<KVT> kr[U], vr[U];
         float mk[U][NCOLS];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const int r0 = base + u * RPI + rsel;
-            const int r = min(r0, kv1 - 1);
-            kr[u].load(kb + (int64_t) r * p.k_nb1, sub); vr[u].load(vb + (int64_t) r * p.v_nb1, sub);
-            const float dead = r0 < kv1 ? 0.0f : -INFINITY;
-            if (p.mask) {
-                if (mask_uniform) {
-                    const float t = (mrow[0] ? __half2float(*(const __half *) (mrow[0] + (int64_t) r * 2)) : 0.0f) + dead;
+            kr[u] = kn[u]; vr[u] = vn[u];
 #pragma unroll
-                    for (int c = 0; c < NCOLS; ++c) mk[u][c] = slope[c] * t;
-                } else {
+            for (int c = 0; c < NCOLS; ++c) mk[u][c] = slope[c] * mn[u];
+        }
+        if (p.mask && !mask_uniform) {       // prefill-style calls (several query positions / per-head masks): fetched here
 #pragma unroll
-                    for (int c = 0; c < NCOLS; ++c) mk[u][c] = slope[c] * ((mrow[c] ? __half2float(*(const __half *) (mrow[c] + (int64_t) r * 2)) : 0.0f) + dead);
-                }
-            } else {
+            for (int u = 0; u < U; ++u) {
+                const int r = max(min(base + u * RPI + rsel, kv1 - 1), kv0);
 #pragma unroll
-                for (int c = 0; c < NCOLS; ++c) mk[u][c] = dead;
+                for (int c = 0; c < NCOLS; ++c) if (mrow[c]) mk[u][c] += slope[c] * __half2float(*(const __half *) (mrow[c] + (int64_t) r * 2));
             }
         }
+        if (base + NW * U * RPI < kv1) request(base + NW * U * RPI);
         // ---- scores of the U x NCOLS (row, column) pairs
         float s[U][NCOLS];
 #pragma unroll
