@@ -311,6 +311,149 @@ __global__ void __launch_bounds__(128) fattn_vec_kernel(const fattn_params p) {
     }
 }
 
+// ---------------------------------------------------------------- prefill attention on the tensor cores
+// Replaces, for many query positions and an f16 cache, the reference's mma kernel (fattn-mma-f16.cuh; selector fattn.cu:371-393).
+// FlashAttention-2 forward: a CTA of 4 warps owns 64 query positions of one head (16 per warp, Q fragments in registers as
+// f16), K and V tiles of 64 positions are staged in shared memory (cp.async, rows padded by 16 B so ldmatrix is
+// conflict-free), S = Q.K^T and O += P.V run as mma.sync.m16n8k16 (f16 in, f32 accumulate), the accumulator fragment of S
+// is reused as the A operand of P.V, V fragments come from ldmatrix.trans.  Mask f16 (added to the scores), scale; softcap,
+// ALiBi and sinks stay on the vector kernel.  (tcgen05 would need M = 128 query rows per instruction and TMEM round trips
+// for the softmax; at 4.3 GFLOP per layer this op is not the tensor-pipe-bound one.)
+__device__ __forceinline__ void fa_ldsm4(uint32_t addr, uint32_t r[4]) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void fa_ldsm4_t(uint32_t addr, uint32_t r[4]) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void fa_mma(float c[4], const uint32_t a[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t fa_pack(float x, float y) { const __half2 h = __floats2half2_rn(x, y); return *(const uint32_t *) &h; }
+
+template <int D>
+__global__ void __launch_bounds__(128) fattn_mma_kernel(const fattn_params p) {
+    constexpr int BN = 64, ROW = D * 2 + 16, KS = D / 16, NT = BN / 8, DT = D / 8, CPR = D / 8;   // CPR: 16 B chunks per row
+    extern __shared__ __align__(16) uint8_t fsm[];
+    uint8_t * sK = fsm, * sV = fsm + BN * ROW;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
+    const int h = blockIdx.y, seq = blockIdx.z, hkv = h / p.gqa;
+    const int qa = blockIdx.x * 64 + warp * 16 + g, qb = qa + 8;
+    const int qa_c = min(qa, p.n_q - 1), qb_c = min(qb, p.n_q - 1);      // rows past n_q compute on a clamped row and are not stored
+
+    // ---- Q fragments (scaled, f16): A[kk] of m16n8k16, rows g / g+8, dims kk*16 + t*2 (+8)
+    uint32_t qf[KS][4];
+    {
+        const float * qpa = (const float *) (p.q + (int64_t) qa_c * p.q_nb1 + (int64_t) h * p.q_nb2 + (int64_t) seq * p.q_nb3);
+        const float * qpb = (const float *) (p.q + (int64_t) qb_c * p.q_nb1 + (int64_t) h * p.q_nb2 + (int64_t) seq * p.q_nb3);
+#pragma unroll
+        for (int kk = 0; kk < KS; ++kk) {
+            const int d = kk * 16 + t * 2;
+            const float2 a0 = *(const float2 *) (qpa + d), a1 = *(const float2 *) (qpb + d), a2 = *(const float2 *) (qpa + d + 8), a3 = *(const float2 *) (qpb + d + 8);
+            qf[kk][0] = fa_pack(a0.x * p.scale, a0.y * p.scale); qf[kk][1] = fa_pack(a1.x * p.scale, a1.y * p.scale);
+            qf[kk][2] = fa_pack(a2.x * p.scale, a2.y * p.scale); qf[kk][3] = fa_pack(a3.x * p.scale, a3.y * p.scale);
+        }
+    }
+    const char * mra = p.mask ? p.mask + (int64_t) qa_c * p.m_nb1 + (int64_t) (h % p.m_ne2) * p.m_nb2 + (int64_t) (seq % p.m_ne3) * p.m_nb3 : nullptr;
+    const char * mrb = p.mask ? p.mask + (int64_t) qb_c * p.m_nb1 + (int64_t) (h % p.m_ne2) * p.m_nb2 + (int64_t) (seq % p.m_ne3) * p.m_nb3 : nullptr;
+    const char * kb = p.k + (int64_t) hkv * p.k_nb2 + (int64_t) seq * p.k_nb3;
+    const char * vb = p.v + (int64_t) hkv * p.v_nb2 + (int64_t) seq * p.v_nb3;
+
+    constexpr float M_NONE = -1.0e30f;
+    float ma = M_NONE, mb = M_NONE, la = 0.0f, lb = 0.0f;       // l: this lane's share of the row sum (4 lanes per row)
+    float o[DT][4];
+#pragma unroll
+    for (int i = 0; i < DT; ++i) { o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.0f; }
+    const uint32_t sK_a = (uint32_t) __cvta_generic_to_shared(sK), sV_a = (uint32_t) __cvta_generic_to_shared(sV);
+
+    for (int kv0 = 0; kv0 < p.n_kv; kv0 += BN) {
+        __syncthreads();                                         // the previous tiles have been consumed
+        for (int i = tid; i < BN * CPR; i += 128) {
+            const int r = i / CPR, c = i % CPR, kr = kv0 + r;
+            const uint32_t dk = sK_a + r * ROW + c * 16, dv = sV_a + r * ROW + c * 16;
+            if (kr < p.n_kv) {
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dk), "l"(kb + (int64_t) kr * p.k_nb1 + c * 16) : "memory");
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dv), "l"(vb + (int64_t) kr * p.v_nb1 + c * 16) : "memory");
+            } else {
+                *(uint4 *) (sK + r * ROW + c * 16) = make_uint4(0u, 0u, 0u, 0u);
+                *(uint4 *) (sV + r * ROW + c * 16) = make_uint4(0u, 0u, 0u, 0u);
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncthreads();
+
+        // ---- S = Q . K^T  (16 query rows x 64 positions per warp)
+        float sc[NT][4];
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) { sc[nt][0] = sc[nt][1] = sc[nt][2] = sc[nt][3] = 0.0f; }
+#pragma unroll
+        for (int kk = 0; kk < KS; kk += 2) {
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+                uint32_t b[4];      // matrices: (positions nt*8.., dims kk*16 + 8j), j = 0..3
+                fa_ldsm4(sK_a + (nt * 8 + (lane & 7)) * ROW + (kk * 16 + 8 * (lane >> 3)) * 2, b);
+                fa_mma(sc[nt], qf[kk], b[0], b[1]);
+                fa_mma(sc[nt], qf[kk + 1], b[2], b[3]);
+            }
+        }
+        // ---- mask, online softmax (rows g and g+8; a row lives in the 4 lanes of a quad)
+        float mxa = ma, mxb = mb;
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            const int k = kv0 + nt * 8 + t * 2;
+            float2 fa = make_float2(0.0f, 0.0f), fb = fa;
+            if (mra) {                                          // positions past n_kv are discarded below: read an in-range pair
+                const int kc = min(k, p.n_kv - 2);
+                fa = __half22float2(*(const __half2 *) (mra + (int64_t) kc * 2)); fb = __half22float2(*(const __half2 *) (mrb + (int64_t) kc * 2));
+            }
+            sc[nt][0] = k     < p.n_kv ? sc[nt][0] + fa.x : -INFINITY; sc[nt][1] = k + 1 < p.n_kv ? sc[nt][1] + fa.y : -INFINITY;
+            sc[nt][2] = k     < p.n_kv ? sc[nt][2] + fb.x : -INFINITY; sc[nt][3] = k + 1 < p.n_kv ? sc[nt][3] + fb.y : -INFINITY;
+            mxa = fmaxf(mxa, fmaxf(sc[nt][0], sc[nt][1])); mxb = fmaxf(mxb, fmaxf(sc[nt][2], sc[nt][3]));
+        }
+        mxa = fmaxf(mxa, __shfl_xor_sync(0xffffffffu, mxa, 1)); mxa = fmaxf(mxa, __shfl_xor_sync(0xffffffffu, mxa, 2));
+        mxb = fmaxf(mxb, __shfl_xor_sync(0xffffffffu, mxb, 1)); mxb = fmaxf(mxb, __shfl_xor_sync(0xffffffffu, mxb, 2));
+        const float ca = __expf(ma - mxa), cb = __expf(mb - mxb);
+        ma = mxa; mb = mxb;
+        float sa = 0.0f, sb = 0.0f;
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            sc[nt][0] = __expf(sc[nt][0] - mxa); sc[nt][1] = __expf(sc[nt][1] - mxa);
+            sc[nt][2] = __expf(sc[nt][2] - mxb); sc[nt][3] = __expf(sc[nt][3] - mxb);
+            sa += sc[nt][0] + sc[nt][1]; sb += sc[nt][2] + sc[nt][3];
+        }
+        la = la * ca + sa; lb = lb * cb + sb;
+#pragma unroll
+        for (int i = 0; i < DT; ++i) { o[i][0] *= ca; o[i][1] *= ca; o[i][2] *= cb; o[i][3] *= cb; }
+        // ---- O += P . V  (the accumulator fragments of S are the A fragments of P)
+#pragma unroll
+        for (int j = 0; j < BN / 16; ++j) {
+            uint32_t pa[4];
+            pa[0] = fa_pack(sc[2 * j][0], sc[2 * j][1]);         pa[1] = fa_pack(sc[2 * j][2], sc[2 * j][3]);
+            pa[2] = fa_pack(sc[2 * j + 1][0], sc[2 * j + 1][1]); pa[3] = fa_pack(sc[2 * j + 1][2], sc[2 * j + 1][3]);
+#pragma unroll
+            for (int dn = 0; dn < DT; dn += 2) {
+                uint32_t b[4];      // matrices: (positions 16j + 8*(i&1).., dims (dn + (i>>1))*8..), transposed on load
+                const int mi = lane >> 3;
+                fa_ldsm4_t(sV_a + (16 * j + 8 * (mi & 1) + (lane & 7)) * ROW + ((dn + (mi >> 1)) * 8) * 2, b);
+                fa_mma(o[dn], pa, b[0], b[1]);
+                fa_mma(o[dn + 1], pa, b[2], b[3]);
+            }
+        }
+    }
+    // ---- normalise and store: dst f32 [D, H, n_q]
+    la += __shfl_xor_sync(0xffffffffu, la, 1); la += __shfl_xor_sync(0xffffffffu, la, 2);
+    lb += __shfl_xor_sync(0xffffffffu, lb, 1); lb += __shfl_xor_sync(0xffffffffu, lb, 2);
+    const float ia = la > 0.0f ? 1.0f / la : 0.0f, ib = lb > 0.0f ? 1.0f / lb : 0.0f;
+    float * da = (float *) (p.dst + (int64_t) h * p.d_nb1 + (int64_t) qa_c * p.d_nb2 + (int64_t) seq * p.d_nb3);
+    float * db = (float *) (p.dst + (int64_t) h * p.d_nb1 + (int64_t) qb_c * p.d_nb2 + (int64_t) seq * p.d_nb3);
+#pragma unroll
+    for (int i = 0; i < DT; ++i) {
+        if (qa < p.n_q) *(float2 *) (da + i * 8 + t * 2) = make_float2(o[i][0] * ia, o[i][1] * ia);
+        if (qb < p.n_q) *(float2 *) (db + i * 8 + t * 2) = make_float2(o[i][2] * ib, o[i][3] * ib);
+    }
+}
+
 struct fattn_plan { int ncols, n_chunks, n_split, kv_per_split, ncols_total; int64_t n_groups; size_t part_bytes, counter_bytes; };
 
 static bool fattn_make_plan(const b200_fattn_args * a, fattn_plan & pl) {
@@ -351,6 +494,19 @@ static bool fattn_make_plan(const b200_fattn_args * a, fattn_plan & pl) {
     pl.n_split = (int) ((n_kv + pl.kv_per_split - 1) / pl.kv_per_split);
     pl.part_bytes = pl.n_split > 1 ? (size_t) pl.n_groups * pl.n_split * pl.ncols * (D + 2) * 4 : 0;
     pl.counter_bytes = (size_t) ((pl.n_groups * 4 + 255) / 256 * 256);
+    return true;
+}
+
+// many query positions, f16 cache, plain scale + mask: the tensor-core kernel
+static bool fattn_use_mma(const b200_fattn_args * a) {
+    const b200_tensor & q = a->q; const b200_tensor & k = a->k; const b200_tensor & v = a->v; const b200_tensor & d = a->dst;
+    const int64_t D = q.ne[0], n_q = q.ne[1], n_kv = k.ne[1];
+    if (n_q < 16 || k.type != B200_F16 || (D != 64 && D != 128) || a->sinks || a->logit_softcap != 0.0f || a->max_bias != 0.0f) return false;
+    if (n_kv < 2 || n_kv % 2 || q.ne[2] > 65535 || q.ne[3] > 65535) return false;
+    if (((uintptr_t) q.data | (uintptr_t) d.data) % 8) return false;
+    for (int i = 1; i < 4; ++i) if (q.nb[i] % 8 || d.nb[i] % 8) return false;
+    (void) v;
+    if (a->mask && (((uintptr_t) a->mask->data) % 4 || a->mask->nb[1] % 4 || a->mask->nb[2] % 4 || a->mask->nb[3] % 4)) return false;
     return true;
 }
 
@@ -403,8 +559,16 @@ extern "C" int b200_flash_attn_ext(const b200_fattn_args * a, void * stream) {
     p.n_head_log2 = 1u << (uint32_t) floorf(log2f((float) p.H));
     p.m0 = powf(2.0f, -a->max_bias / p.n_head_log2); p.m1 = powf(2.0f, -(a->max_bias / 2.0f) / p.n_head_log2);
     p.counters = (int *) a->scratch; p.part = (float *) ((char *) a->scratch + pl.counter_bytes);
-    dim3 grid((unsigned) pl.n_split, (unsigned) (p.H_kv * pl.n_chunks), (unsigned) q.ne[3]);
     cudaStream_t st = (cudaStream_t) stream;
+    if (fattn_use_mma(a)) {
+        const int D = (int) q.ne[0];
+        dim3 grid((unsigned) ((p.n_q + 63) / 64), (unsigned) p.H, (unsigned) q.ne[3]);
+        const size_t smem = (size_t) 2 * 64 * (D * 2 + 16);
+        if (D == 64) fattn_mma_kernel<64><<<grid, 128, smem, st>>>(p); else fattn_mma_kernel<128><<<grid, 128, smem, st>>>(p);
+        count_launch();
+        return check_launch("flash_attn_ext (mma)");
+    }
+    dim3 grid((unsigned) pl.n_split, (unsigned) (p.H_kv * pl.n_chunks), (unsigned) q.ne[3]);
     if (pl.n_split > 1)   // arrival counters of the split-KV combine: zeroed per launch (a memset node under graph capture)
         B200_CUDA_TRY(cudaMemsetAsync(p.counters, 0, pl.counter_bytes, st));
     const int D = (int) q.ne[0];

@@ -112,7 +112,8 @@ def _kv_bytes(orc, capi, x, kv_type):
 
 @pytest.mark.parametrize("kv_type", ["f16", "q8_0"])
 @pytest.mark.parametrize("D,H,H_kv,n_q,n_kv", [(128, 32, 8, 1, 256), (64, 32, 4, 1, 300), (128, 40, 8, 1, 4096),
-                                                 (128, 8, 8, 2, 1000), (64, 16, 4, 35, 512), (256, 4, 1, 1, 700), (128, 64, 8, 1, 32768)])
+                                                 (128, 8, 8, 2, 1000), (64, 16, 4, 35, 512), (256, 4, 1, 1, 700), (128, 64, 8, 1, 32768),
+                                                 (128, 8, 2, 130, 600)])
 @pytest.mark.parametrize("extras", ["plain", "mask", "mask+sinks+softcap", "alibi"])
 def test_flash_attn_decode(orc, kv_type, D, H, H_kv, n_q, n_kv, extras):
     torch, capi, _ = _mods()
@@ -149,5 +150,7 @@ def test_flash_attn_decode(orc, kv_type, D, H, H_kv, n_q, n_kv, extras):
     orc.orc_flash_attn(ptr(q), ptr(np.ascontiguousarray(kd)), ptr(np.ascontiguousarray(vd)), None if mf is None else ptr(mf),
                        None if sinks is None else ptr(sinks), ptr(want), C.c_int64(D), C.c_int64(n_q), C.c_int64(H), C.c_int64(H_kv),
                        C.c_int64(n_kv), C.c_float(scale), C.c_float(max_bias), C.c_float(softcap))
-    # reference gate: NMSE <= 5e-4 (tests/test-backend-ops.cpp:6082-6084); f32 math here is far tighter
-    assert orc.orc_nmse(ptr(want), ptr(np.ascontiguousarray(got)), C.c_size_t(want.size)) < 1e-8
+    # reference gate: NMSE <= 5e-4 (tests/test-backend-ops.cpp:6082-6084); the f32 vector kernel is far tighter.  Many query
+    # positions over an f16 cache run on the tensor cores (Q and P rounded to f16, f32 accumulation): 2e-6
+    mma = n_q >= 16 and kv_type == "f16" and extras in ("plain", "mask") and n_kv % 2 == 0
+    assert orc.orc_nmse(ptr(want), ptr(np.ascontiguousarray(got)), C.c_size_t(want.size)) < (2e-6 if mma else 1e-8)
