@@ -259,7 +259,9 @@ struct tc_shared {
     uint32_t tmem_base;
 };
 
-template <int TYPE>
+// BN = columns of the CTA tile: 256, or 128 (half of a 256-column activation tile) when 256-wide tiles would leave most
+// SMs without a CTA (M = 4096 at N = 512: 64 CTAs on 148 SMs)
+template <int TYPE, int BN>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 mmq_tc_kernel(const __grid_constant__ CUtensorMap tmA, const uint8_t * __restrict__ xb, float * __restrict__ dst,
               int M, int N, int K, int64_t ldd, uint32_t idesc) {
@@ -268,10 +270,11 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmA, const uint8_t * __restric
     extern __shared__ uint8_t smem_raw[];
     __shared__ tc_shared sh;
     uint8_t * base = smem_raw + ((1024u - (tc_smem(smem_raw) & 1023u)) & 1023u);       // swizzled tiles need 1024 B alignment
-    uint8_t * sA = base, * sB = sA + TC_STAGES * TC_A_BYTES, * sR = sB + TC_STAGES * TC_B_BYTES;
+    constexpr int B_BYTES = BN * 128;
+    uint8_t * sA = base, * sB = sA + TC_STAGES * TC_A_BYTES, * sR = sB + TC_STAGES * B_BYTES;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int n_tile = blockIdx.x, m0 = blockIdx.y * TC_BM, n0 = n_tile * TC_BN;
+    const int n_tile = (int) blockIdx.x / (TC_BN / BN), n_half = (int) blockIdx.x % (TC_BN / BN), m0 = blockIdx.y * TC_BM, n0 = (int) blockIdx.x * BN;
     const int ksteps = K / TC_KSTEP, kb_n = K / TC_BK;
 
     if (tid == 0) {
@@ -282,7 +285,7 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmA, const uint8_t * __restric
         tc_fence_async();
     }
     if (warp == 1) {                                            // TMEM: 256 columns of f32 accumulators (128 lanes x 256)
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc_smem(&sh.tmem_base)), "r"(TC_BN) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc_smem(&sh.tmem_base)), "r"(BN) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     tc_fence_before();
@@ -293,7 +296,7 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmA, const uint8_t * __restric
     if (warp == 0) {
         // ================= producer: raw weight boxes (TMA 2-D) and activation tiles (bulk)
         if (lane == 0) {
-            const uint8_t * xt = xb + (size_t) n_tile * kb_n * TC_B_BYTES;
+            const uint8_t * xt = xb + (size_t) n_tile * kb_n * TC_B_BYTES + (size_t) n_half * B_BYTES;    // rows 128.. of a tile are its second half
             for (int ks = 0; ks < ksteps; ++ks) {
                 const int rs = ks % TC_RAW_STAGES;
                 tc_mbar_wait(&sh.raw_empty[rs], ((ks / TC_RAW_STAGES) & 1) ^ 1);
@@ -302,8 +305,8 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmA, const uint8_t * __restric
                 for (int sub = 0; sub < TC_SUB; ++sub) {
                     const int it = ks * TC_SUB + sub, s = it % TC_STAGES;
                     tc_mbar_wait(&sh.ab_empty[s], ((it / TC_STAGES) & 1) ^ 1);
-                    tc_mbar_expect(&sh.b_full[s], TC_B_BYTES);
-                    tc_bulk_g2s(sB + s * TC_B_BYTES, xt + (size_t) it * TC_B_BYTES, TC_B_BYTES, &sh.b_full[s]);
+                    tc_mbar_expect(&sh.b_full[s], B_BYTES);
+                    tc_bulk_g2s(sB + s * B_BYTES, xt + (size_t) it * TC_B_BYTES, B_BYTES, &sh.b_full[s]);
                 }
             }
         }
@@ -316,7 +319,7 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmA, const uint8_t * __restric
             tc_mbar_wait(&sh.b_full[s], par);
             tc_fence_after();
             if (lane == 0) {
-                const uint32_t a0 = tc_smem(sA + s * TC_A_BYTES), b0 = tc_smem(sB + s * TC_B_BYTES);
+                const uint32_t a0 = tc_smem(sA + s * TC_A_BYTES), b0 = tc_smem(sB + s * B_BYTES);
 #pragma unroll
                 for (int k = 0; k < TC_BK / 16; ++k)             // UMMA_K = 16 halves = 32 B inside the swizzle row
                     tc_mma_f16(tmem, tc_desc(a0 + k * 32), tc_desc(b0 + k * 32), idesc, (it | k) != 0);
@@ -349,9 +352,9 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmA, const uint8_t * __restric
         const int q = warp & 3, half = (warp - 2) >> 2;
         const int m = m0 + q * 32 + lane;
 #pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < BN / 64; ++c) {
             uint32_t v[32];
-            const int col = half * 128 + c * 32;
+            const int col = half * (BN / 2) + c * 32;
             tc_ld32(tmem + ((uint32_t) (q * 32) << 16) + (uint32_t) col, v);
             if (m < M) {
 #pragma unroll
@@ -364,7 +367,7 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmA, const uint8_t * __restric
         tc_fence_before();
     }
     __syncthreads();
-    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TC_BN) : "memory");
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(BN) : "memory");
 }
 
 // ---------------------------------------------------------------- host side
@@ -386,7 +389,7 @@ static tc_encode_fn tc_encoder() {
 static int tc_box(int t) { return t == B200_Q6_K ? 240 : t == B200_Q8_0 ? 272 : 144; }
 static int tc_elem(int t) { return t == B200_Q8_0 ? 2 : 1; }
 static bool tc_type_ok(int t) { return t == B200_Q4_K || t == B200_Q6_K || t == B200_Q4_0 || t == B200_Q8_0; }
-static size_t tc_smem_bytes(int t) { return (size_t) TC_STAGES * (TC_A_BYTES + TC_B_BYTES) + (size_t) TC_RAW_STAGES * TC_BM * tc_box(t) + 1024; }
+static size_t tc_smem_bytes(int t, int bn) { return (size_t) TC_STAGES * (TC_A_BYTES + bn * 128) + (size_t) TC_RAW_STAGES * TC_BM * tc_box(t) + 1024; }
 
 static bool tc_args_ok(const b200_mmq_args * a) {
     if (!a) return false;
@@ -400,21 +403,31 @@ static bool tc_args_ok(const b200_mmq_args * a) {
     return true;
 }
 
-template <int TYPE>
-static int tc_launch(const CUtensorMap & map, const b200_mmq_args * a, uint32_t idesc, cudaStream_t st) {
+template <int TYPE, int BN>
+static int tc_launch_bn(const CUtensorMap & map, const b200_mmq_args * a, cudaStream_t st) {
     static bool attr_set[64] = {};
     int dev = 0;
     B200_CUDA_TRY(cudaGetDevice(&dev));
-    const size_t smem = tc_smem_bytes(TYPE);
+    const size_t smem = tc_smem_bytes(TYPE, BN);
     if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(mmq_tc_kernel<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        B200_CUDA_TRY(cudaFuncSetAttribute(mmq_tc_kernel<TYPE, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
         attr_set[dev] = true;
     }
     const int M = (int) a->w.ne[1], N = (int) a->x.ne[1], K = (int) a->w.ne[0];
-    dim3 grid((unsigned) ((N + TC_BN - 1) / TC_BN), (unsigned) ((M + TC_BM - 1) / TC_BM));
-    mmq_tc_kernel<TYPE><<<grid, TC_THREADS, smem, st>>>(map, (const uint8_t *) a->xb, (float *) a->dst.data, M, N, K, a->dst.nb[1] / 4, idesc);
+    // instruction descriptor: D f32 (bits 4-5 = 1), A f16 (bits 7-9 = 0), B f16/bf16 (bits 10-12), both K-major, N >> 3 in 17-22, M >> 4 in 24-28
+    const uint32_t idesc = (1u << 4) | (0u << 7) | ((uint32_t) a->act_fmt << 10) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (TC_BM >> 4) << 24);
+    dim3 grid((unsigned) ((N + BN - 1) / BN), (unsigned) ((M + TC_BM - 1) / TC_BM));
+    mmq_tc_kernel<TYPE, BN><<<grid, TC_THREADS, smem, st>>>(map, (const uint8_t *) a->xb, (float *) a->dst.data, M, N, K, a->dst.nb[1] / 4, idesc);
     count_launch();
     return check_launch("mmq_tc_kernel");
+}
+template <int TYPE>
+static int tc_launch(const CUtensorMap & map, const b200_mmq_args * a, cudaStream_t st) {
+    // 256-column tiles unless they leave more than a third of the SMs idle and 128-column tiles fill more of them
+    const int64_t M = a->w.ne[1], N = a->x.ne[1];
+    const int64_t c256 = ((N + 255) / 256) * ((M + TC_BM - 1) / TC_BM), c128 = ((N + 127) / 128) * ((M + TC_BM - 1) / TC_BM);
+    if (N > 128 && c256 < 100 && c128 > c256) return tc_launch_bn<TYPE, 128>(map, a, st);
+    return tc_launch_bn<TYPE, 256>(map, a, st);
 }
 
 }  // namespace b200
@@ -469,13 +482,11 @@ extern "C" int b200_mul_mat_q(const b200_mmq_args * a, void * stream) {
             cache.emplace(k, map);
         } else map = it->second;
     }
-    // instruction descriptor: D f32 (bits 4-5 = 1), A f16 (bits 7-9 = 0), B f16/bf16 (bits 10-12), both K-major, N >> 3 in 17-22, M >> 4 in 24-28
-    const uint32_t idesc = (1u << 4) | (0u << 7) | ((uint32_t) a->act_fmt << 10) | ((uint32_t) (TC_BN >> 3) << 17) | ((uint32_t) (TC_BM >> 4) << 24);
     switch (a->w.type) {
-        case B200_Q4_K: return tc_launch<B200_Q4_K>(map, a, idesc, (cudaStream_t) stream);
-        case B200_Q6_K: return tc_launch<B200_Q6_K>(map, a, idesc, (cudaStream_t) stream);
-        case B200_Q4_0: return tc_launch<B200_Q4_0>(map, a, idesc, (cudaStream_t) stream);
-        case B200_Q8_0: return tc_launch<B200_Q8_0>(map, a, idesc, (cudaStream_t) stream);
+        case B200_Q4_K: return tc_launch<B200_Q4_K>(map, a, (cudaStream_t) stream);
+        case B200_Q6_K: return tc_launch<B200_Q6_K>(map, a, (cudaStream_t) stream);
+        case B200_Q4_0: return tc_launch<B200_Q4_0>(map, a, (cudaStream_t) stream);
+        case B200_Q8_0: return tc_launch<B200_Q8_0>(map, a, (cudaStream_t) stream);
     }
     return B200_ERR_UNSUPPORTED;
 }
