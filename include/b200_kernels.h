@@ -161,7 +161,9 @@ typedef struct b200_chain b200_chain;
 B200_API b200_chain * b200_chain_create(const b200_phase * phases, int n_phases, int flags);   /* NULL: see b200_last_error() */
 B200_API int          b200_chain_launch(b200_chain * chain, void * stream);
 B200_API void         b200_chain_destroy(b200_chain * chain);
-/* flags bit 2 at create time: per-phase globaltimer stamps of the first and last CTA (tools/timeline_chain.py) */
+/* flags at create time (tuning / debug): bit 0 consumers skip the dot products (bandwidth probe), bit 2 per-phase globaltimer
+ * stamps of the first and last CTA (tools/timeline_chain.py), bit 3 publish a phase with __threadfence in every thread before
+ * the CTA barrier instead of one release RED by thread 0 after it, bits 4-7 ring depth, bits 8-15 stage KiB */
 B200_API int          b200_chain_debug_read(b200_chain * chain, unsigned long long * out, int n_phases);
 
 /* ---- row split across GPUs: the decode chain over NVLink peer memory --------------------------------
@@ -222,6 +224,8 @@ typedef struct b200_mmq_args {
     const void * xb;      /* output of b200_mmq_convert_act for x */
     int32_t act_fmt;      /* must match the conversion */
     int32_t _pad;
+    const b200_tensor * addend;   /* optional f32 [M, N] added in the epilogue (the residual stream: replaces the ADD node that
+                                     follows the matmul, reference ggml-cuda/binbcast.cu); may alias dst */
 } b200_mmq_args;
 B200_API size_t b200_mmq_act_size(int64_t K, int64_t N);
 B200_API int    b200_mmq_supported(const b200_mmq_args * a);

@@ -28,7 +28,8 @@ class MmvqArgs(C.Structure):
 
 
 class MmqArgs(C.Structure):
-    _fields_ = [("w", Tensor), ("x", Tensor), ("dst", Tensor), ("xb", C.c_void_p), ("act_fmt", C.c_int32), ("_pad", C.c_int32)]
+    _fields_ = [("w", Tensor), ("x", Tensor), ("dst", Tensor), ("xb", C.c_void_p), ("act_fmt", C.c_int32), ("_pad", C.c_int32),
+                ("addend", C.POINTER(Tensor))]
 
 
 _lib = None
@@ -442,7 +443,7 @@ def gemv_phase(x, segs, **kw):
     return ph
 
 
-def mul_mat_q(w, wtype: int, K: int, M: int, x, dst, act_fmt: int = 1, xb=None):
+def mul_mat_q(w, wtype: int, K: int, M: int, x, dst, act_fmt: int = 1, xb=None, addend=None):
     """dst[N, M] (torch, ggml [M, N]) = W . x for x [N, K] f32 through the tensor-core prefill path.
     Returns the converted activation buffer so callers can reuse it for matmuls sharing x."""
     import torch
@@ -462,5 +463,8 @@ def mul_mat_q(w, wtype: int, K: int, M: int, x, dst, act_fmt: int = 1, xb=None):
     a.dst = from_torch(dst)
     a.xb = xb.data_ptr()
     a.act_fmt = act_fmt
+    if addend is not None:
+        ta = from_torch(addend)
+        a.addend = C.pointer(ta)
     check(L.b200_mul_mat_q(C.byref(a), C.c_void_p(stream_ptr())), "mul_mat_q")
     return xb

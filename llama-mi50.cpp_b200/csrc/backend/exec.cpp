@@ -191,9 +191,12 @@ int run_mul_mat(exec_state & st, const ggml_tensor * dst, const ggml_tensor * bi
 
     const int64_t ncols = ids ? 1 : x->ne[1];
     // ---- prefill: more than 8 columns go to the tensor cores (reference router: ggml_cuda_mul_mat, ggml-cuda.cu:2183-2266)
-    if (!ids && !bias && !gate && ncols > 8 && !st.no_tc) {
+    // a `bias` of dst's full shape (ncols > 1) is the residual stream of a {MUL_MAT, ADD} pair: only the tensor-core path takes it
+    const bool full_addend = bias && ncols > 1 && ggml_are_same_shape(bias, dst);
+    if (!ids && (!bias || full_addend) && !gate && ncols > 8 && !st.no_tc) {
         b200_mmq_args m{};
         m.w = b200_desc(w); m.x = b200_desc(x); m.dst = b200_desc(dst); m.act_fmt = 0;
+        if (full_addend) m.addend = &t_bias;
         if (b200_mmq_supported(&m)) {
             if (st.validate) return B200_OK;
             const size_t need = b200_mmq_act_size(x->ne[0], x->ne[1]) + 1024;
@@ -210,6 +213,7 @@ int run_mul_mat(exec_state & st, const ggml_tensor * dst, const ggml_tensor * bi
             return B200_OK;
         }
     }
+    if (full_addend) return B200_ERR_UNSUPPORTED;
     const int nwin = (int) ((ncols + 7) / 8);
     for (int wi = 0; wi < nwin; ++wi) {   // validate every window shape
         if (nwin > 1) { a.col_begin = wi * 8; a.col_count = (int) std::min<int64_t>(8, ncols - wi * 8); }
@@ -435,6 +439,22 @@ int run_fused(exec_state & st, ggml_cgraph * g, int i, bool fusion, int node_lim
                     run_mul_mat(st, &tmp, nullptr, gate_mm->src[0], nullptr, (int) ggml_get_glu_op(glu), alpha, limit);
                     if (st.q8_src == &tmp) st.q8_src = nullptr;
                     return 3;
+                }
+            }
+        }
+        // {MUL_MAT, ADD} with many columns: the residual stream rides in the epilogue of the tensor-core GEMM
+        if (n->op == GGML_OP_MUL_MAT && !is_split_tensor(n->src[0]) && i + 1 < node_limit && n->ne[1] > 8 && n->ne[2] == 1 && n->ne[3] == 1) {
+            ggml_tensor * add = g->nodes[i + 1];
+            if (add->op == GGML_OP_ADD && (add->src[0] == n || add->src[1] == n) && ggml_node_has_n_uses(g, i, 1) && same_shape(add, n)) {
+                const ggml_tensor * other = add->src[0] == n ? add->src[1] : add->src[0];
+                if (other != n && other->type == GGML_TYPE_F32 && same_shape(other, n) && other->nb[0] == 4) {
+                    ggml_tensor tmp = *add;
+                    tmp.op = GGML_OP_MUL_MAT; tmp.src[0] = n->src[0]; tmp.src[1] = n->src[1]; tmp.src[2] = nullptr;
+                    exec_state probe = st; probe.validate = true;
+                    if (run_mul_mat(probe, &tmp, other, nullptr, nullptr, B200_GLU_NONE, 0, 0) == B200_OK) {
+                        run_mul_mat(st, &tmp, other, nullptr, nullptr, B200_GLU_NONE, 0, 0);
+                        return 2;
+                    }
                 }
             }
         }

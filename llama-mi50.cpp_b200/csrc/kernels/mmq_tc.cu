@@ -263,8 +263,8 @@ struct tc_shared {
 // SMs without a CTA (M = 4096 at N = 512: 64 CTAs on 148 SMs)
 template <int TYPE, int BN>
 __global__ void __launch_bounds__(TC_THREADS, 1)
-mmq_tc_kernel(const __grid_constant__ CUtensorMap tmA, const uint8_t * __restrict__ xb, float * __restrict__ dst,
-              int M, int N, int K, int64_t ldd, uint32_t idesc) {
+mmq_tc_kernel(const __grid_constant__ CUtensorMap tmA, const uint8_t * __restrict__ xb, float * dst,
+              int M, int N, int K, int64_t ldd, uint32_t idesc, const float * add, int64_t lda) {
     using F = tc_fmt<TYPE>;
     constexpr int RAW_BYTES = TC_BM * F::box;
     extern __shared__ uint8_t smem_raw[];
@@ -360,7 +360,7 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmA, const uint8_t * __restric
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
                     const int n = n0 + col + j;
-                    if (n < N) dst[(int64_t) n * ldd + m] = __uint_as_float(v[j]);
+                    if (n < N) dst[(int64_t) n * ldd + m] = __uint_as_float(v[j]) + (add ? add[(int64_t) n * lda + m] : 0.0f);
                 }
             }
         }
@@ -399,6 +399,10 @@ static bool tc_args_ok(const b200_mmq_args * a) {
     if (w.nb[0] != (int64_t) b200_type_size(w.type) || w.nb[1] != (int64_t) b200_row_size(w.type, K) || w.nb[1] % 16 != 0 || ((uintptr_t) w.data) % 16 != 0) return false;
     if (x.type != B200_F32 || x.nb[0] != 4 || x.ne[0] != K || x.ne[2] != 1 || x.ne[3] != 1 || N < 1 || N > 65536 || x.nb[1] % 16 != 0 || ((uintptr_t) x.data) % 16 != 0) return false;
     if (d.type != B200_F32 || d.nb[0] != 4 || d.ne[0] != M || d.ne[1] != N || d.ne[2] != 1 || d.ne[3] != 1 || d.nb[1] % 4 != 0) return false;
+    if (a->addend) {
+        const b200_tensor & r = *a->addend;
+        if (r.type != B200_F32 || r.nb[0] != 4 || r.ne[0] != M || r.ne[1] != N || r.ne[2] != 1 || r.ne[3] != 1 || r.nb[1] % 4 != 0) return false;
+    }
     if (a->act_fmt != 0) return false;        // kind::f16 rejects an f16 A with a bf16 B (illegal instruction, measured): both operands f16
     return true;
 }
@@ -417,7 +421,8 @@ static int tc_launch_bn(const CUtensorMap & map, const b200_mmq_args * a, cudaSt
     // instruction descriptor: D f32 (bits 4-5 = 1), A f16 (bits 7-9 = 0), B f16/bf16 (bits 10-12), both K-major, N >> 3 in 17-22, M >> 4 in 24-28
     const uint32_t idesc = (1u << 4) | (0u << 7) | ((uint32_t) a->act_fmt << 10) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (TC_BM >> 4) << 24);
     dim3 grid((unsigned) ((N + BN - 1) / BN), (unsigned) ((M + TC_BM - 1) / TC_BM));
-    mmq_tc_kernel<TYPE, BN><<<grid, TC_THREADS, smem, st>>>(map, (const uint8_t *) a->xb, (float *) a->dst.data, M, N, K, a->dst.nb[1] / 4, idesc);
+    mmq_tc_kernel<TYPE, BN><<<grid, TC_THREADS, smem, st>>>(map, (const uint8_t *) a->xb, (float *) a->dst.data, M, N, K, a->dst.nb[1] / 4, idesc,
+                                                          a->addend ? (const float *) a->addend->data : nullptr, a->addend ? a->addend->nb[1] / 4 : 0);
     count_launch();
     return check_launch("mmq_tc_kernel");
 }

@@ -54,3 +54,22 @@ def test_mul_mat_q_vs_float64(orc, t, M, K, N, act_fmt):
     # per-row check too (a wrong row inside a big product would hide in the global NMSE)
     row_nmse = ((got - want) ** 2).sum(axis=1) / ((want ** 2).sum(axis=1) + 1e-30)
     assert row_nmse.max() <= 1e-3, f"worst column NMSE {row_nmse.max()} at {row_nmse.argmax()}"
+
+
+def test_mul_mat_q_residual_epilogue(orc):
+    """{MUL_MAT, ADD} of a prefill graph: the residual stream is added in the GEMM epilogue, also when it aliases dst."""
+    import torch
+    from llama_mi50_b200 import capi, gguf_synth as gs
+    M, K, N, t = 512, 1024, 300, Q4_K
+    rng = np.random.default_rng(5)
+    raw = gs.make_tensor_bytes(rng, t, (K, M), 0.02)
+    x = rng.standard_normal((N, K)).astype(np.float32)
+    res = rng.standard_normal((N, M)).astype(np.float32)
+    wd = torch.zeros(raw.nbytes + 64, dtype=torch.uint8, device="cuda"); wd[:raw.nbytes] = torch.from_numpy(raw).cuda()
+    xd = torch.from_numpy(x).cuda()
+    plain = torch.empty((N, M), device="cuda")
+    xb = capi.mul_mat_q(wd, t, K, M, xd, plain, act_fmt=0)
+    fused = torch.from_numpy(res).cuda()                       # in place: addend == dst
+    capi.mul_mat_q(wd, t, K, M, xd, fused, act_fmt=0, xb=xb, addend=fused)
+    torch.cuda.synchronize()
+    assert torch.equal(fused, plain + torch.from_numpy(res).cuda())
