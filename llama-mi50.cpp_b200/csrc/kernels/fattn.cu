@@ -367,6 +367,16 @@ __global__ void __launch_bounds__(128) fattn_mma_kernel(const fattn_params p) {
     const uint32_t sK_a = (uint32_t) __cvta_generic_to_shared(sK), sV_a = (uint32_t) __cvta_generic_to_shared(sV);
 
     for (int kv0 = 0; kv0 < p.n_kv; kv0 += BN) {
+        if (mra) {      // a tile that is masked for all 64 query positions of the CTA (causal prompt: about half of them) is skipped
+            bool alive = false;
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+                const int kc = min(kv0 + nt * 8 + t * 2, p.n_kv - 2);
+                const float2 fa = __half22float2(*(const __half2 *) (mra + (int64_t) kc * 2)), fb = __half22float2(*(const __half2 *) (mrb + (int64_t) kc * 2));
+                alive = alive || fa.x > -INFINITY || fa.y > -INFINITY || fb.x > -INFINITY || fb.y > -INFINITY;
+            }
+            if (!__syncthreads_or(alive)) continue;
+        }
         __syncthreads();                                         // the previous tiles have been consumed
         for (int i = tid; i < BN * CPR; i += 128) {
             const int r = i / CPR, c = i % CPR, kr = kv0 + r;
