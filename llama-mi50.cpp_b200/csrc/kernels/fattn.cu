@@ -331,7 +331,7 @@ __device__ __forceinline__ void fa_mma(float c[4], const uint32_t a[4], uint32_t
 }
 __device__ __forceinline__ uint32_t fa_pack(float x, float y) { const __half2 h = __floats2half2_rn(x, y); return *(const uint32_t *) &h; }
 
-template <int D>
+template <int D, int KVT>
 __global__ void __launch_bounds__(128) fattn_mma_kernel(const fattn_params p) {
     constexpr int BN = 64, ROW = D * 2 + 16, KS = D / 16, NT = BN / 8, DT = D / 8, CPR = D / 8;   // CPR: 16 B chunks per row
     extern __shared__ __align__(16) uint8_t fsm[];
@@ -378,6 +378,45 @@ __global__ void __launch_bounds__(128) fattn_mma_kernel(const fattn_params p) {
             if (!__syncthreads_or(alive)) continue;
         }
         __syncthreads();                                         // the previous tiles have been consumed
+        if (KVT == B200_Q8_0) {
+            // q8_0 cache: blocks (half d, 32 int8; 2-byte aligned) are expanded to f16 on the way into shared memory, so the
+            // MMA part is the same as for an f16 cache (the reference dequantises the whole cache to an f16 copy first,
+            // fattn-common.cuh:830-890)
+            constexpr int BPR = D / 32;
+            for (int i = tid; i < 2 * BN * BPR; i += 128) {
+                const bool isv = i >= BN * BPR;
+                const int ii = isv ? i - BN * BPR : i, r = ii / BPR, j = ii % BPR, kr = kv0 + r;
+                uint4 * dstp = (uint4 *) ((isv ? sV : sK) + r * ROW + j * 64);
+                if (kr < p.n_kv) {
+                    const uintptr_t a = (uintptr_t) ((isv ? vb + (int64_t) kr * p.v_nb1 : kb + (int64_t) kr * p.k_nb1) + 34 * j);
+                    const uint32_t sh = (uint32_t) (a & 3) * 8;
+                    const uint32_t * q = (const uint32_t *) (a & ~(uintptr_t) 3);
+                    uint32_t w[10], x[9];
+#pragma unroll
+                    for (int u = 0; u < 9; ++u) w[u] = q[u];
+                    w[9] = 0u;
+#pragma unroll
+                    for (int u = 0; u < 9; ++u) x[u] = __funnelshift_r(w[u], w[u + 1], sh);      // x: the block from its first byte
+                    const uint16_t dbits = (uint16_t) (x[0] & 0xFFFFu);
+                    const __half2 d2 = __half2half2(*(const __half *) &dbits), off = __float2half2_rn(1152.0f);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        uint32_t o[4];
+#pragma unroll
+                        for (int v = 0; v < 2; ++v) {
+                            const uint32_t y = __funnelshift_r(x[2 * u + v], x[2 * u + v + 1], 16) ^ 0x80808080u;    // 4 int8 + 128
+                            const uint32_t lo = __byte_perm(y, 0x64646464u, 0x4140), hi = __byte_perm(y, 0x64646464u, 0x4342);
+                            const __half2 hl = __hmul2(__hsub2(*(const __half2 *) &lo, off), d2), hh = __hmul2(__hsub2(*(const __half2 *) &hi, off), d2);
+                            o[2 * v] = *(const uint32_t *) &hl; o[2 * v + 1] = *(const uint32_t *) &hh;
+                        }
+                        dstp[u] = make_uint4(o[0], o[1], o[2], o[3]);
+                    }
+                } else {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) dstp[u] = make_uint4(0u, 0u, 0u, 0u);
+                }
+            }
+        } else
         for (int i = tid; i < BN * CPR; i += 128) {
             const int r = i / CPR, c = i % CPR, kr = kv0 + r;
             const uint32_t dk = sK_a + r * ROW + c * 16, dv = sV_a + r * ROW + c * 16;
@@ -511,11 +550,14 @@ static bool fattn_make_plan(const b200_fattn_args * a, fattn_plan & pl) {
 static bool fattn_use_mma(const b200_fattn_args * a) {
     const b200_tensor & q = a->q; const b200_tensor & k = a->k; const b200_tensor & v = a->v; const b200_tensor & d = a->dst;
     const int64_t D = q.ne[0], n_q = q.ne[1], n_kv = k.ne[1];
-    if (n_q < 16 || k.type != B200_F16 || (D != 64 && D != 128) || a->sinks || a->logit_softcap != 0.0f || a->max_bias != 0.0f) return false;
+    if (n_q < 16 || (D != 64 && D != 128) || a->sinks || a->logit_softcap != 0.0f || a->max_bias != 0.0f) return false;
+    if (k.type == B200_Q8_0) {          // blocks are read as aligned words around their 2-byte aligned start
+        if (((uintptr_t) k.data | (uintptr_t) v.data) % 4) return false;
+        for (int i = 1; i < 4; ++i) if (k.nb[i] % 4 || v.nb[i] % 4) return false;
+    } else if (k.type != B200_F16) return false;
     if (n_kv < 2 || n_kv % 2 || q.ne[2] > 65535 || q.ne[3] > 65535) return false;
     if (((uintptr_t) q.data | (uintptr_t) d.data) % 8) return false;
     for (int i = 1; i < 4; ++i) if (q.nb[i] % 8 || d.nb[i] % 8) return false;
-    (void) v;
     if (a->mask && (((uintptr_t) a->mask->data) % 4 || a->mask->nb[1] % 4 || a->mask->nb[2] % 4 || a->mask->nb[3] % 4)) return false;
     return true;
 }
@@ -574,7 +616,8 @@ extern "C" int b200_flash_attn_ext(const b200_fattn_args * a, void * stream) {
         const int D = (int) q.ne[0];
         dim3 grid((unsigned) ((p.n_q + 63) / 64), (unsigned) p.H, (unsigned) q.ne[3]);
         const size_t smem = (size_t) 2 * 64 * (D * 2 + 16);
-        if (D == 64) fattn_mma_kernel<64><<<grid, 128, smem, st>>>(p); else fattn_mma_kernel<128><<<grid, 128, smem, st>>>(p);
+        if (k.type == B200_F16) { if (D == 64) fattn_mma_kernel<64, B200_F16><<<grid, 128, smem, st>>>(p); else fattn_mma_kernel<128, B200_F16><<<grid, 128, smem, st>>>(p); }
+        else                    { if (D == 64) fattn_mma_kernel<64, B200_Q8_0><<<grid, 128, smem, st>>>(p); else fattn_mma_kernel<128, B200_Q8_0><<<grid, 128, smem, st>>>(p); }
         count_launch();
         return check_launch("flash_attn_ext (mma)");
     }
