@@ -222,11 +222,12 @@ typedef struct b200_mmq_args {
     b200_tensor x;        /* f32 [K, N] (shape / validation; the kernel reads xb) */
     b200_tensor dst;      /* f32 [M, N] */
     const void * xb;      /* output of b200_mmq_convert_act for x */
-    int32_t act_fmt;      /* must match the conversion */
+    int32_t act_fmt;      /* must match the conversion AND b200_mmq_act_fmt(w.type) */
     int32_t _pad;
     const b200_tensor * addend;   /* optional f32 [M, N] added in the epilogue (the residual stream: replaces the ADD node that
                                      follows the matmul, reference ggml-cuda/binbcast.cu); may alias dst */
 } b200_mmq_args;
+B200_API int    b200_mmq_act_fmt(int weight_type);   /* 16-bit format of both MMA operands for this weight type: 0 = f16, 1 = bf16 (MXFP4) */
 B200_API size_t b200_mmq_act_size(int64_t K, int64_t N);
 B200_API int    b200_mmq_supported(const b200_mmq_args * a);
 B200_API int    b200_mmq_convert_act(const b200_tensor * x, void * xb, int act_fmt, void * stream);

@@ -26,6 +26,7 @@ struct exec_state {
     const void * q8_src_data = nullptr;
     const ggml_tensor * xb_src = nullptr;     // same for the 16-bit activation tiles of the tensor-core GEMM
     const void * xb_src_data = nullptr;
+    int xb_fmt = -1;
     bool no_tc = env_flag("GGML_B200_DISABLE_TC");
     size_t need_q8 = 0, need_fa = 0, need_xb = 0;   // scratch high-water marks found during the sizing pass
     size_t need_split_x = 0;           // row split: bytes of the largest activation copied to the other devices
@@ -83,13 +84,13 @@ int run_mul_mat_split(exec_state & st, const ggml_tensor * dst) {
         ggml_tensor dt = *dst; dt.data = (char *) dst->data + (size_t) lo * 4; dt.ne[0] = hi - lo;
         if (ncols > 8 && !st.no_tc) {
             b200_mmq_args m{};
-            m.w = b200_desc(&wt); m.x = b200_desc(&xt); m.dst = b200_desc(&dt); m.act_fmt = 0;
+            m.w = b200_desc(&wt); m.x = b200_desc(&xt); m.dst = b200_desc(&dt); m.act_fmt = b200_mmq_act_fmt((int) w->type);
             if (b200_mmq_supported(&m)) {
                 const size_t need = b200_mmq_act_size(K, ncols) + 1024;
                 if (probe) { st.need_xb = std::max(st.need_xb, need); return B200_OK; }
                 GGML_ASSERT(need <= xb_size);
                 char * xb = (char *) (((uintptr_t) xbuf + 1023) & ~(uintptr_t) 1023);
-                B200_KCHECK(b200_mmq_convert_act(&m.x, xb, 0, stream));
+                B200_KCHECK(b200_mmq_convert_act(&m.x, xb, m.act_fmt, stream));
                 m.xb = xb;
                 B200_KCHECK(b200_mul_mat_q(&m, stream));
                 st.launches += 2;
@@ -195,7 +196,7 @@ int run_mul_mat(exec_state & st, const ggml_tensor * dst, const ggml_tensor * bi
     const bool full_addend = bias && ncols > 1 && ggml_are_same_shape(bias, dst);
     if (!ids && (!bias || full_addend) && !gate && ncols > 8 && !st.no_tc) {
         b200_mmq_args m{};
-        m.w = b200_desc(w); m.x = b200_desc(x); m.dst = b200_desc(dst); m.act_fmt = 0;
+        m.w = b200_desc(w); m.x = b200_desc(x); m.dst = b200_desc(dst); m.act_fmt = b200_mmq_act_fmt((int) w->type);
         if (full_addend) m.addend = &t_bias;
         if (b200_mmq_supported(&m)) {
             if (st.validate) return B200_OK;
@@ -203,9 +204,9 @@ int run_mul_mat(exec_state & st, const ggml_tensor * dst, const ggml_tensor * bi
             if (st.sizing) { st.need_xb = std::max(st.need_xb, need); return B200_OK; }
             GGML_ASSERT(need <= st.ctx->xb_size);
             char * xb = (char *) (((uintptr_t) st.ctx->xb_scratch + 1023) & ~(uintptr_t) 1023);
-            if (st.xb_src != x || st.xb_src_data != x->data) {      // q/k/v and gate/up share one conversion
-                B200_KCHECK(b200_mmq_convert_act(&m.x, xb, 0, st.stream));
-                st.xb_src = x; st.xb_src_data = x->data; st.launches++;
+            if (st.xb_src != x || st.xb_src_data != x->data || st.xb_fmt != m.act_fmt) {      // q/k/v and gate/up share one conversion
+                B200_KCHECK(b200_mmq_convert_act(&m.x, xb, m.act_fmt, st.stream));
+                st.xb_src = x; st.xb_src_data = x->data; st.xb_fmt = m.act_fmt; st.launches++;
             }
             m.xb = xb;
             B200_KCHECK(b200_mul_mat_q(&m, st.stream));

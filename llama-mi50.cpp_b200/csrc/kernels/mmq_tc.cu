@@ -21,6 +21,7 @@
 #include <unordered_map>
 
 #include "common.cuh"
+#include "vecdot.cuh"
 
 namespace b200 {
 
@@ -37,7 +38,8 @@ template <int TYPE> struct tc_fmt;
 template <> struct tc_fmt<B200_Q4_K> { static constexpr int gbytes = 144, box = 144, elem = 1; };
 template <> struct tc_fmt<B200_Q6_K> { static constexpr int gbytes = 210, box = 240, elem = 1; };    // 16 B aligned window around the 210 B block
 template <> struct tc_fmt<B200_Q4_0> { static constexpr int gbytes = 144, box = 144, elem = 1; };    // 8 blocks of 18 B
-template <> struct tc_fmt<B200_Q8_0> { static constexpr int gbytes = 272, box = 272, elem = 2; };    // 8 blocks of 34 B (tensor map in 16-bit elements:
+template <> struct tc_fmt<B200_Q8_0> { static constexpr int gbytes = 272, box = 272, elem = 2; };
+template <> struct tc_fmt<B200_MXFP4> { static constexpr int gbytes = 136, box = 144, elem = 1; };  // 8 blocks of 17 B; 16 B aligned window    // 8 blocks of 34 B (tensor map in 16-bit elements:
                                                                                             // a box dimension holds at most 256 elements)
 
 // ---------------------------------------------------------------- PTX helpers
@@ -218,6 +220,38 @@ template <> struct tc_expand<B200_Q8_0> {
     }
 };
 
+// MXFP4: e2m1 x 2^(e-127) does not fit f16's exponent range, so this type runs the MMA in bf16 — both
+// operands bf16 (kind::f16 takes f16 x f16 or bf16 x bf16), every weight exact (a 4-bit integer times a power of two), the
+// activations rounded to bf16.  The reference's B200 path (LUT -> int8, q8_1 activations, mmq.cuh:720-783) and its sm_120
+// block-scaled FP4 MMA (:785-827) are replaced; activations are NOT quantised to FP4, so the 5e-4 NMSE gate applies.
+template <> struct tc_expand<B200_MXFP4> {
+    __device__ __forceinline__ static void run(const uint8_t * row, int sub, int r, int h, uint8_t * tile) {
+        const uint8_t * b = row + 17 * (2 * sub + h);           // block: e8m0 e, 16 bytes: weight j = low nibble of qs[j], j+16 = high
+        const __nv_bfloat162 s2 = __float2bfloat162_rn(e8m0_half_to_f32(b[0])), off = __float2bfloat162_rn(144.0f);
+        const uint32_t a = tc_smem(b + 1), sh = (a & 3u) * 8u;
+        const uint32_t * qp = (const uint32_t *) (b + 1 - (a & 3u));
+        uint32_t w[5];
+#pragma unroll
+        for (int i = 0; i < 5; ++i) w[i] = qp[i];
+        int lo[4], hi[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) mxfp4_expand(__funnelshift_r(w[i], w[i + 1], sh), lo[i], hi[i]);      // int8: 2 x the e2m1 value
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            uint32_t o[4];
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                const int q = (c >> 1) ? hi[2 * (c & 1) + v] : lo[2 * (c & 1) + v];
+                const uint32_t x = __vadd4((uint32_t) q, 0x10101010u);                  // 4..28 per byte; 0x4300 | x is exactly 128 + x in bf16
+                const uint32_t p0 = __byte_perm(x, 0x43434343u, 0x4140), p1 = __byte_perm(x, 0x43434343u, 0x4342);
+                const __nv_bfloat162 v0 = __hmul2(__hsub2(*(const __nv_bfloat162 *) &p0, off), s2), v1 = __hmul2(__hsub2(*(const __nv_bfloat162 *) &p1, off), s2);
+                o[2 * v] = *(const uint32_t *) &v0; o[2 * v + 1] = *(const uint32_t *) &v1;
+            }
+            tc_store_chunk(tile, r, 4 * h + c, make_uint4(o[0], o[1], o[2], o[3]));
+        }
+    }
+};
+
 // ---------------------------------------------------------------- activations -> swizzled 16-bit tiles
 // out: tiles [n_tile][k_block] of 256 rows x 128 B, each already in the shared-memory image (16 B chunk c of row r at
 // (r/8)*1024 + (r%8)*128 + ((c ^ r%8) * 16)); columns beyond N are zero.  fmt 0 = f16 (clamped to +-65504), 1 = bf16.
@@ -387,8 +421,9 @@ static tc_encode_fn tc_encoder() {
 }
 
 static int tc_box(int t) { return t == B200_Q6_K ? 240 : t == B200_Q8_0 ? 272 : 144; }
+static int tc_act_fmt(int t) { return t == B200_MXFP4 ? 1 : 0; }      // 16-bit format of BOTH operands: 0 = f16, 1 = bf16
 static int tc_elem(int t) { return t == B200_Q8_0 ? 2 : 1; }
-static bool tc_type_ok(int t) { return t == B200_Q4_K || t == B200_Q6_K || t == B200_Q4_0 || t == B200_Q8_0; }
+static bool tc_type_ok(int t) { return t == B200_Q4_K || t == B200_Q6_K || t == B200_Q4_0 || t == B200_Q8_0 || t == B200_MXFP4; }
 static size_t tc_smem_bytes(int t, int bn) { return (size_t) TC_STAGES * (TC_A_BYTES + bn * 128) + (size_t) TC_RAW_STAGES * TC_BM * tc_box(t) + 1024; }
 
 static bool tc_args_ok(const b200_mmq_args * a) {
@@ -403,7 +438,7 @@ static bool tc_args_ok(const b200_mmq_args * a) {
         const b200_tensor & r = *a->addend;
         if (r.type != B200_F32 || r.nb[0] != 4 || r.ne[0] != M || r.ne[1] != N || r.ne[2] != 1 || r.ne[3] != 1 || r.nb[1] % 4 != 0) return false;
     }
-    if (a->act_fmt != 0) return false;        // kind::f16 rejects an f16 A with a bf16 B (illegal instruction, measured): both operands f16
+    if (a->act_fmt != tc_act_fmt(w.type)) return false;   // kind::f16 rejects an f16 A with a bf16 B (illegal instruction, measured): same format on both sides
     return true;
 }
 
@@ -419,7 +454,7 @@ static int tc_launch_bn(const CUtensorMap & map, const b200_mmq_args * a, cudaSt
     }
     const int M = (int) a->w.ne[1], N = (int) a->x.ne[1], K = (int) a->w.ne[0];
     // instruction descriptor: D f32 (bits 4-5 = 1), A f16 (bits 7-9 = 0), B f16/bf16 (bits 10-12), both K-major, N >> 3 in 17-22, M >> 4 in 24-28
-    const uint32_t idesc = (1u << 4) | (0u << 7) | ((uint32_t) a->act_fmt << 10) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (TC_BM >> 4) << 24);
+    const uint32_t idesc = (1u << 4) | ((uint32_t) a->act_fmt << 7) | ((uint32_t) a->act_fmt << 10) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (TC_BM >> 4) << 24);
     dim3 grid((unsigned) ((N + BN - 1) / BN), (unsigned) ((M + TC_BM - 1) / TC_BM));
     mmq_tc_kernel<TYPE, BN><<<grid, TC_THREADS, smem, st>>>(map, (const uint8_t *) a->xb, (float *) a->dst.data, M, N, K, a->dst.nb[1] / 4, idesc,
                                                           a->addend ? (const float *) a->addend->data : nullptr, a->addend ? a->addend->nb[1] / 4 : 0);
@@ -438,6 +473,8 @@ static int tc_launch(const CUtensorMap & map, const b200_mmq_args * a, cudaStrea
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" int b200_mmq_act_fmt(int type) { return tc_act_fmt(type); }
 
 extern "C" size_t b200_mmq_act_size(int64_t K, int64_t N) {
     if (K < TC_BK || N < 1) return 0;
@@ -492,6 +529,7 @@ extern "C" int b200_mul_mat_q(const b200_mmq_args * a, void * stream) {
         case B200_Q6_K: return tc_launch<B200_Q6_K>(map, a, (cudaStream_t) stream);
         case B200_Q4_0: return tc_launch<B200_Q4_0>(map, a, (cudaStream_t) stream);
         case B200_Q8_0: return tc_launch<B200_Q8_0>(map, a, (cudaStream_t) stream);
+        case B200_MXFP4: return tc_launch<B200_MXFP4>(map, a, (cudaStream_t) stream);
     }
     return B200_ERR_UNSUPPORTED;
 }

@@ -11,7 +11,7 @@ from conftest import ptr
 
 pytestmark = pytest.mark.gpu
 
-Q4_0, Q8_0, Q4_K, Q6_K = 2, 8, 12, 14
+Q4_0, Q8_0, Q4_K, Q6_K, MXFP4 = 2, 8, 12, 14, 39
 
 
 def _dequant(orc, gs, raw, t, K, M):
@@ -24,7 +24,7 @@ def _dequant(orc, gs, raw, t, K, M):
 
 
 @pytest.mark.parametrize("act_fmt", [0])
-@pytest.mark.parametrize("t", [Q4_K, Q6_K, Q4_0, Q8_0])
+@pytest.mark.parametrize("t", [Q4_K, Q6_K, Q4_0, Q8_0, MXFP4])
 @pytest.mark.parametrize("M,K,N", [(256, 512, 300), (128, 256, 9), (384, 1024, 512), (200, 768, 64), (256, 2048, 40), (4096, 4096, 512)])
 def test_mul_mat_q_vs_float64(orc, t, M, K, N, act_fmt):
     import torch
@@ -33,6 +33,8 @@ def test_mul_mat_q_vs_float64(orc, t, M, K, N, act_fmt):
         pytest.skip("rows of this type/K are not 16-byte multiples: not a tensor-map shape (the plugin keeps the GEMV-window path)")
     if M * K > 4e6 and t != Q4_K:
         pytest.skip("large case once")
+    if t == MXFP4:
+        act_fmt = 1          # bf16 operands: e2m1 x 2^(e-127) does not fit f16 (csrc/kernels/mmq_tc.cu)
     rng = np.random.default_rng(M * 7 + K + N + t)
     raw = gs.make_tensor_bytes(rng, t, (K, M), 0.02)
     x = rng.standard_normal((N, K)).astype(np.float32)
