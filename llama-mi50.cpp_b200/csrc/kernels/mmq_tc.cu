@@ -391,10 +391,18 @@ mmq_tc_kernel(const __grid_constant__ CUtensorMap tmA, const uint8_t * __restric
             const int col = half * (BN / 2) + c * 32;
             tc_ld32(tmem + ((uint32_t) (q * 32) << 16) + (uint32_t) col, v);
             if (m < M) {
+                // the addend may alias dst (in-place residual add): all its loads are issued before the first store, otherwise
+                // every load would have to wait for the store in front of it (measured: 5 % of pp512)
+                float r[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
                     const int n = n0 + col + j;
-                    if (n < N) dst[(int64_t) n * ldd + m] = __uint_as_float(v[j]) + (add ? add[(int64_t) n * lda + m] : 0.0f);
+                    r[j] = add && n < N ? add[(int64_t) n * lda + m] : 0.0f;
+                }
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const int n = n0 + col + j;
+                    if (n < N) dst[(int64_t) n * ldd + m] = __uint_as_float(v[j]) + r[j];
                 }
             }
         }
