@@ -34,6 +34,11 @@ int ggml_backend_score(void);
  */
 struct ggml_backend_buffer_type * ggml_backend_b200_split_buffer_type(int main_device, const float * tensor_split);
 
+/* The row partition of that buffer type as plain arithmetic (no device needed): rows [*row_lo, *row_hi) of `device` for a
+ * tensor of `nrows` rows over `n_devices` equal devices (reference get_row_split, ggml-cuda.cu:791-804: cumulative
+ * fractions, boundaries rounded down to 128 rows, the last device takes the remainder).  0 on success, -1 on bad arguments. */
+int ggml_backend_b200_split_rows(const float * tensor_split, int n_devices, long long nrows, int device, long long * row_lo, long long * row_hi);
+
 /* Extension used by bench.py / tools: counters and device-side timing of graph_compute.
  * Device time is measured with CUDA events recorded on the backend stream around every graph
  * launch when the environment variable GGML_B200_TIMING=1 is set. */

@@ -31,13 +31,31 @@ struct split_buf_ctx {
 
 const char * split_buft_name(ggml_backend_buffer_type_t t) { return ((split_buft_ctx *) t->context)->name.c_str(); }
 
-void row_range(const split_buft_ctx * c, int64_t nrows, int id, int64_t & lo, int64_t & hi) {
-    const int n = b200_n_devices();
-    lo = id == 0 ? 0 : (int64_t) (nrows * c->split[id]);
+// rows [lo, hi) of device `id` out of n devices with cumulative start fractions `split` (reference get_row_split,
+// ggml-cuda.cu:791-804: boundaries rounded down to the row rounding, the last device takes the remainder)
+void row_range_n(const float * split, int n, int64_t nrows, int id, int64_t & lo, int64_t & hi) {
+    lo = id == 0 ? 0 : (int64_t) (nrows * split[id]);
     lo -= lo % kRowRounding;
     if (id == n - 1) hi = nrows;
-    else { hi = (int64_t) (nrows * c->split[id + 1]); hi -= hi % kRowRounding; }
+    else { hi = (int64_t) (nrows * split[id + 1]); hi -= hi % kRowRounding; }
     if (hi < lo) hi = lo;
+}
+void row_range(const split_buft_ctx * c, int64_t nrows, int id, int64_t & lo, int64_t & hi) {
+    row_range_n(c->split.data(), b200_n_devices(), nrows, id, lo, hi);
+}
+// user-facing tensor_split (relative sizes, all zero = default) -> cumulative start fractions (reference ggml-cuda.cu:1078-1090)
+void cumulative_split(const float * tensor_split, int n, const double * default_weight, float * out) {
+    bool all_zero = true;
+    for (int i = 0; tensor_split && i < n; ++i) all_zero = all_zero && tensor_split[i] == 0.0f;
+    if (all_zero) {
+        double total = 0, acc = 0;
+        for (int i = 0; i < n; ++i) total += default_weight[i];
+        for (int i = 0; i < n; ++i) { out[i] = (float) (acc / total); acc += default_weight[i]; }
+    } else {
+        float sum = 0.0f;
+        for (int i = 0; i < n; ++i) { out[i] = sum; sum += tensor_split[i]; }
+        for (int i = 0; i < n; ++i) out[i] /= sum;
+    }
 }
 
 size_t slice_bytes(const ggml_tensor * t, int64_t rows) {
@@ -185,22 +203,29 @@ ggml_backend_buffer_type_t ggml_backend_b200_split_buffer_type(int main_device, 
     const int n = b200_n_devices();
     if (n < 1 || main_device < 0 || main_device >= n) return nullptr;
     std::array<float, B200_MAX_DEVICES> split{};
-    bool all_zero = true;
-    for (int i = 0; tensor_split && i < n; ++i) all_zero = all_zero && tensor_split[i] == 0.0f;
-    if (all_zero) {
-        // default: proportional to device memory (reference default_tensor_split, ggml-cuda.cu:231-232, 304-306)
-        double total = 0, acc = 0;
-        for (int i = 0; i < n; ++i) total += (double) b200_device(i).total_mem;
-        for (int i = 0; i < n; ++i) { split[i] = (float) (acc / total); acc += (double) b200_device(i).total_mem; }
-    } else {
-        float sum = 0.0f;
-        for (int i = 0; i < n; ++i) { split[i] = sum; sum += tensor_split[i]; }
-        for (int i = 0; i < n; ++i) split[i] /= sum;
-    }
+    double mem[B200_MAX_DEVICES];      // default: proportional to device memory (reference default_tensor_split, ggml-cuda.cu:231-232, 304-306)
+    for (int i = 0; i < n; ++i) mem[i] = (double) b200_device(i).total_mem;
+    cumulative_split(tensor_split, n, mem, split.data());
     auto key = std::make_pair(main_device, split);
     auto it = types.find(key);
     if (it != types.end()) return &it->second;
     if (n > 1) b200_enable_peer_access();
     ggml_backend_buffer_type t{ kSplitBuftIface, b200_dev(main_device), new split_buft_ctx{main_device, split, b200_device(main_device).name + "_Split"} };
     return &types.emplace(key, t).first->second;
+}
+
+// The partition arithmetic alone (no device needed): rows [*row_lo, *row_hi) of `device` for a tensor of `nrows` rows
+// split over `n_devices` equal devices with the user's `tensor_split` (NULL / all zero: equal shares).  Returns 0, or -1
+// on bad arguments.  Used by the CPU tests and by hosts that want to place data before creating buffers.
+extern "C" __attribute__((visibility("default")))
+int ggml_backend_b200_split_rows(const float * tensor_split, int n_devices, long long nrows, int device, long long * row_lo, long long * row_hi) {
+    if (n_devices < 1 || n_devices > B200_MAX_DEVICES || device < 0 || device >= n_devices || nrows < 0 || !row_lo || !row_hi) return -1;
+    float split[B200_MAX_DEVICES];
+    double w[B200_MAX_DEVICES];
+    for (int i = 0; i < n_devices; ++i) w[i] = 1.0;
+    cumulative_split(tensor_split, n_devices, w, split);
+    int64_t lo, hi;
+    row_range_n(split, n_devices, nrows, device, lo, hi);
+    *row_lo = lo; *row_hi = hi;
+    return 0;
 }
