@@ -9,6 +9,7 @@
 // elements: one 128-bit load for f16, 8 B + scale for q8_0) and 32/LPR "row slots" run in parallel,
 // each with a private online-softmax state; states are merged once per block in shared memory.
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -22,6 +23,112 @@ struct fattn_params {
     float scale, softcap, max_bias, m0, m1; uint32_t n_head_log2;
     float * part; int * counters;
 };
+
+// ---------------------------------------------------------------- shared tail of the decode kernels
+// in: sm = NSTATE online-softmax states per column, [state][column][acc[D], m, l] (m = -inf: nothing seen).  Merges them,
+// writes the output (one split) or the partial of this split, and lets the last block of the group combine all splits.
+template <int D, int NCOLS, int NSTATE>
+__device__ __forceinline__ void fattn_tail(const fattn_params & p, float * sm, int split, int grp, int seq, int hkv, int chunk, int lane, int warp) {
+    constexpr int ST = D + 2;
+    __shared__ int s_last;
+    const int64_t grp_lin = (int64_t) seq * gridDim.y + grp;
+    float * part = p.part + (grp_lin * p.n_split + split) * NCOLS * ST;
+    for (int e = threadIdx.x; e < NCOLS * D; e += 128) {
+        const int c = e / D, d = e % D;
+        float M = -INFINITY;
+        for (int s = 0; s < NSTATE; ++s) M = fmaxf(M, sm[((int64_t) s * NCOLS + c) * ST + D]);
+        float A = 0.0f, L = 0.0f;
+        for (int s = 0; s < NSTATE; ++s) {
+            const float * o = sm + ((int64_t) s * NCOLS + c) * ST;
+            const float w = o[D] == -INFINITY ? 0.0f : expf(o[D] - M);
+            A += w * o[d]; L += w * o[D + 1];
+        }
+        if (p.n_split == 1) {
+            const int ci = chunk * NCOLS + c;
+            if (ci < p.ncols_total) {
+                const int j = ci / p.gqa, h = hkv * p.gqa + ci % p.gqa;
+                if (p.sinks) {
+                    const float sk = p.sinks[h], Mn = fmaxf(M, sk);
+                    const float w = M == -INFINITY ? 0.0f : expf(M - Mn);
+                    A *= w; L = L * w + expf(sk - Mn);
+                }
+                ((float *) (p.dst + (int64_t) h * p.d_nb1 + (int64_t) j * p.d_nb2 + (int64_t) seq * p.d_nb3))[d] = A / L;
+            }
+        } else {
+            part[c * ST + d] = A;
+            if (d == 0) { part[c * ST + D] = M; part[c * ST + D + 1] = L; }
+        }
+    }
+    if (p.n_split == 1) return;
+
+    // ---- split-KV: the last block of this group to arrive combines all partials
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const int prev = atomicAdd(p.counters + grp_lin, 1);
+        s_last = prev == p.n_split - 1;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    // The partials of the n_split blocks are independent loads: a first pass (threads over splits) turns the per-split
+    // maxima into weights in shared memory, a second pass (threads over output elements) sums with 8 loads in flight.
+    // (The first version walked the splits one dependent L2 round trip at a time: ~40 us of an 87 us launch at 64 splits.)
+    const float * all = p.part + grp_lin * p.n_split * NCOLS * ST;
+    float * s_w = sm;                                   // [NCOLS][n_split] weights; reuses the state area (all reads of it are done)
+    __shared__ float s_red[NCOLS][4], s_M[NCOLS], s_L[NCOLS];
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) {
+        float M = -INFINITY;
+        for (int sp = threadIdx.x; sp < p.n_split; sp += 128) M = fmaxf(M, all[((int64_t) sp * NCOLS + c) * ST + D]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
+        if (lane == 0) s_red[c][warp] = M;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < NCOLS; ++c) {
+        float M = fmaxf(fmaxf(s_red[c][0], s_red[c][1]), fmaxf(s_red[c][2], s_red[c][3]));
+        const int ci = chunk * NCOLS + c;
+        const int h = hkv * p.gqa + (ci < p.ncols_total ? ci % p.gqa : 0);
+        float Lsink = 0.0f;
+        if (p.sinks && ci < p.ncols_total) { const float sk = p.sinks[h]; const float Mn = fmaxf(M, sk); Lsink = expf(sk - Mn); M = Mn; }
+        float L = 0.0f;
+        for (int sp = threadIdx.x; sp < p.n_split; sp += 128) {
+            const float * o = all + ((int64_t) sp * NCOLS + c) * ST;
+            const float w = o[D] == -INFINITY ? 0.0f : expf(o[D] - M);
+            s_w[c * p.n_split + sp] = w;
+            L += w * o[D + 1];
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) L += __shfl_xor_sync(0xffffffffu, L, o);
+        __syncthreads();                                // s_red of this column has been read by everyone
+        if (lane == 0) s_red[c][warp] = L;
+        __syncthreads();
+        if (threadIdx.x == 0) { s_M[c] = M; s_L[c] = s_red[c][0] + s_red[c][1] + s_red[c][2] + s_red[c][3] + Lsink; }
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < NCOLS * D; e += 128) {
+        const int c = e / D, d = e % D;
+        const int ci = chunk * NCOLS + c;
+        if (ci >= p.ncols_total) continue;
+        const int j = ci / p.gqa, h = hkv * p.gqa + ci % p.gqa;
+        const float * col = all + (int64_t) c * ST + d;
+        const float * w = s_w + c * p.n_split;
+        float A = 0.0f;
+        int sp = 0;
+        for (; sp + 8 <= p.n_split; sp += 8) {
+            float v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = col[(int64_t) (sp + u) * NCOLS * ST];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) A += w[sp + u] * v[u];
+        }
+        for (; sp < p.n_split; ++sp) A += w[sp] * col[(int64_t) sp * NCOLS * ST];
+        ((float *) (p.dst + (int64_t) h * p.d_nb1 + (int64_t) j * p.d_nb2 + (int64_t) seq * p.d_nb3))[d] = A / s_L[c];
+    }
+}
 
 // raw K/V bytes of one lane's 8 elements, kept unconverted while the loads are in flight
 template <int KVT> struct kvraw;
@@ -64,7 +171,6 @@ __global__ void __launch_bounds__(128) fattn_vec_kernel(const fattn_params p) {
     constexpr int LPR = D / 8, RPI = 32 / LPR, NW = 4, NSTATE = NW * RPI, ST = D + 2;
     constexpr int U = NCOLS >= 3 ? 2 : 4;
     extern __shared__ float sm[];   // [NSTATE][NCOLS][ST]: acc[D], m, l
-    __shared__ int s_last;
     pdl_launch_dependents();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane % LPR, rsel = lane / LPR;
     const int split = blockIdx.x, grp = blockIdx.y, seq = blockIdx.z;
@@ -212,103 +318,7 @@ __global__ void __launch_bounds__(128) fattn_vec_kernel(const fattn_params p) {
         if (sub == 0) { o[D] = m[c]; o[D + 1] = l[c]; }
     }
     __syncthreads();
-    const int64_t grp_lin = (int64_t) seq * gridDim.y + grp;
-    float * part = p.part + (grp_lin * p.n_split + split) * NCOLS * ST;
-    for (int e = threadIdx.x; e < NCOLS * D; e += 128) {
-        const int c = e / D, d = e % D;
-        float M = -INFINITY;
-        for (int s = 0; s < NSTATE; ++s) M = fmaxf(M, sm[((int64_t) s * NCOLS + c) * ST + D]);
-        float A = 0.0f, L = 0.0f;
-        for (int s = 0; s < NSTATE; ++s) {
-            const float * o = sm + ((int64_t) s * NCOLS + c) * ST;
-            const float w = o[D] == -INFINITY ? 0.0f : expf(o[D] - M);
-            A += w * o[d]; L += w * o[D + 1];
-        }
-        if (p.n_split == 1) {
-            const int ci = chunk * NCOLS + c;
-            if (ci < p.ncols_total) {
-                const int j = ci / p.gqa, h = hkv * p.gqa + ci % p.gqa;
-                if (p.sinks) {
-                    const float sk = p.sinks[h], Mn = fmaxf(M, sk);
-                    const float w = M == -INFINITY ? 0.0f : expf(M - Mn);
-                    A *= w; L = L * w + expf(sk - Mn);
-                }
-                ((float *) (p.dst + (int64_t) h * p.d_nb1 + (int64_t) j * p.d_nb2 + (int64_t) seq * p.d_nb3))[d] = A / L;
-            }
-        } else {
-            part[c * ST + d] = A;
-            if (d == 0) { part[c * ST + D] = M; part[c * ST + D + 1] = L; }
-        }
-    }
-    if (p.n_split == 1) return;
-
-    // ---- split-KV: the last block of this group to arrive combines all partials
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        const int prev = atomicAdd(p.counters + grp_lin, 1);
-        s_last = prev == p.n_split - 1;
-    }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-    // The partials of the n_split blocks are independent loads: a first pass (threads over splits) turns the per-split
-    // maxima into weights in shared memory, a second pass (threads over output elements) sums with 8 loads in flight.
-    // (The first version walked the splits one dependent L2 round trip at a time: ~40 us of an 87 us launch at 64 splits.)
-    const float * all = p.part + grp_lin * p.n_split * NCOLS * ST;
-    float * s_w = sm;                                   // [NCOLS][n_split] weights; reuses the state area (all reads of it are done)
-    __shared__ float s_red[NCOLS][4], s_M[NCOLS], s_L[NCOLS];
-    __syncthreads();
-#pragma unroll
-    for (int c = 0; c < NCOLS; ++c) {
-        float M = -INFINITY;
-        for (int sp = threadIdx.x; sp < p.n_split; sp += 128) M = fmaxf(M, all[((int64_t) sp * NCOLS + c) * ST + D]);
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
-        if (lane == 0) s_red[c][warp] = M;
-    }
-    __syncthreads();
-#pragma unroll
-    for (int c = 0; c < NCOLS; ++c) {
-        float M = fmaxf(fmaxf(s_red[c][0], s_red[c][1]), fmaxf(s_red[c][2], s_red[c][3]));
-        const int ci = chunk * NCOLS + c;
-        const int h = hkv * p.gqa + (ci < p.ncols_total ? ci % p.gqa : 0);
-        float Lsink = 0.0f;
-        if (p.sinks && ci < p.ncols_total) { const float sk = p.sinks[h]; const float Mn = fmaxf(M, sk); Lsink = expf(sk - Mn); M = Mn; }
-        float L = 0.0f;
-        for (int sp = threadIdx.x; sp < p.n_split; sp += 128) {
-            const float * o = all + ((int64_t) sp * NCOLS + c) * ST;
-            const float w = o[D] == -INFINITY ? 0.0f : expf(o[D] - M);
-            s_w[c * p.n_split + sp] = w;
-            L += w * o[D + 1];
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) L += __shfl_xor_sync(0xffffffffu, L, o);
-        __syncthreads();                                // s_red of this column has been read by everyone
-        if (lane == 0) s_red[c][warp] = L;
-        __syncthreads();
-        if (threadIdx.x == 0) { s_M[c] = M; s_L[c] = s_red[c][0] + s_red[c][1] + s_red[c][2] + s_red[c][3] + Lsink; }
-    }
-    __syncthreads();
-    for (int e = threadIdx.x; e < NCOLS * D; e += 128) {
-        const int c = e / D, d = e % D;
-        const int ci = chunk * NCOLS + c;
-        if (ci >= p.ncols_total) continue;
-        const int j = ci / p.gqa, h = hkv * p.gqa + ci % p.gqa;
-        const float * col = all + (int64_t) c * ST + d;
-        const float * w = s_w + c * p.n_split;
-        float A = 0.0f;
-        int sp = 0;
-        for (; sp + 8 <= p.n_split; sp += 8) {
-            float v[8];
-#pragma unroll
-            for (int u = 0; u < 8; ++u) v[u] = col[(int64_t) (sp + u) * NCOLS * ST];
-#pragma unroll
-            for (int u = 0; u < 8; ++u) A += w[sp + u] * v[u];
-        }
-        for (; sp < p.n_split; ++sp) A += w[sp] * col[(int64_t) sp * NCOLS * ST];
-        ((float *) (p.dst + (int64_t) h * p.d_nb1 + (int64_t) j * p.d_nb2 + (int64_t) seq * p.d_nb3))[d] = A / s_L[c];
-    }
+    fattn_tail<D, NCOLS, NSTATE>(p, sm, split, grp, seq, hkv, chunk, lane, warp);
 }
 
 // ---------------------------------------------------------------- prefill attention on the tensor cores
@@ -503,6 +513,169 @@ __global__ void __launch_bounds__(128) fattn_mma_kernel(const fattn_params p) {
     }
 }
 
+// ---------------------------------------------------------------- decode attention on the tensor cores (contexts >= 1024 positions)
+// Long-context decode with GQA is instruction-bound on the CUDA cores.  Here the <= 8 query columns of a
+// chunk (the heads of a GQA group) are the rows of the A operand (rows 8..15 of m16n8k16 stay zero), every warp owns KV
+// tiles of 32 positions in its private shared memory (cp.async for f16, block expansion for q8_0 — the loaders of the
+// prefill kernel), S = Q.K^T and O += P.V are mma.sync, and each warp ends as one online-softmax state of the shared
+// tail (fattn_tail: in-block merge, split-KV partials, last-block combine).  Measured at 32 k positions against the vector
+// kernel (profiles/r01c_fattn_decode.txt): Llama-3-70B f16 (gqa 8) 189 -> 99 us, gpt-oss q8_0 130 -> 67 us, Qwen2.5-32B q8_0
+// (C3) 127 -> 107 us, Llama-3-8B f16 89 -> 72 us.  Q and P are rounded to f16 (NMSE ~1e-7 against the f32 oracle).
+template <int D, int KVT, int NCOLS>
+__global__ void __launch_bounds__(128) fattn_dec_mma_kernel(const fattn_params p) {
+    constexpr int BN = 32, ROW = D * 2 + 16, KS = D / 16, NT = BN / 8, DT = D / 8, CPR = D / 8, ST = D + 2, NW = 4;
+    extern __shared__ __align__(16) uint8_t dsm[];
+    pdl_launch_dependents();
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
+    const int split = blockIdx.x, grp = blockIdx.y, seq = blockIdx.z;
+    const int hkv = grp / p.n_chunks, chunk = grp % p.n_chunks;
+    uint8_t * sK = dsm + warp * (2 * BN * ROW), * sV = sK + BN * ROW;
+    float * sm = (float *) (dsm + NW * 2 * BN * ROW);
+    const uint32_t sK_a = (uint32_t) __cvta_generic_to_shared(sK), sV_a = (uint32_t) __cvta_generic_to_shared(sV);
+
+    // row g of the A operand = column g of the chunk (rows of inactive columns carry q = 0 and are never written out)
+    const bool cvalid = g < NCOLS && chunk * NCOLS + g < p.ncols_total;
+    const int ci = cvalid ? chunk * NCOLS + g : chunk * NCOLS;
+    const int cj = ci / p.gqa, ch = hkv * p.gqa + ci % p.gqa;
+    pdl_wait();
+    uint32_t qf[KS][4];
+    {
+        const float * qp = (const float *) (p.q + (int64_t) cj * p.q_nb1 + (int64_t) ch * p.q_nb2 + (int64_t) seq * p.q_nb3);
+#pragma unroll
+        for (int kk = 0; kk < KS; ++kk) {
+            const int d = kk * 16 + t * 2;
+            const float2 a0 = *(const float2 *) (qp + d), a2 = *(const float2 *) (qp + d + 8);
+            qf[kk][0] = cvalid ? fa_pack(a0.x * p.scale, a0.y * p.scale) : 0u; qf[kk][1] = 0u;
+            qf[kk][2] = cvalid ? fa_pack(a2.x * p.scale, a2.y * p.scale) : 0u; qf[kk][3] = 0u;
+        }
+    }
+    const char * mr = p.mask ? p.mask + (int64_t) cj * p.m_nb1 + (int64_t) (ch % p.m_ne2) * p.m_nb2 + (int64_t) (seq % p.m_ne3) * p.m_nb3 : nullptr;
+    const int kv0 = split * p.kv_per_split, kv1 = min(p.n_kv, kv0 + p.kv_per_split);
+    const char * kb = p.k + (int64_t) hkv * p.k_nb2 + (int64_t) seq * p.k_nb3;
+    const char * vb = p.v + (int64_t) hkv * p.v_nb2 + (int64_t) seq * p.v_nb3;
+
+    constexpr float M_NONE = -1.0e30f;
+    float ma = M_NONE, la = 0.0f;
+    float o[DT][4];
+#pragma unroll
+    for (int i = 0; i < DT; ++i) { o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.0f; }
+
+    for (int base = kv0 + warp * BN; base < kv1; base += NW * BN) {
+        __syncwarp();                                            // the warp has consumed its previous tile
+        if (KVT == B200_Q8_0) {
+            constexpr int BPR = D / 32;
+            for (int i = lane; i < 2 * BN * BPR; i += 32) {
+                const bool isv = i >= BN * BPR;
+                const int ii = isv ? i - BN * BPR : i, r = ii / BPR, j = ii % BPR, kr = base + r;
+                uint4 * dstp = (uint4 *) ((isv ? sV : sK) + r * ROW + j * 64);
+                if (kr < kv1) {
+                    const uintptr_t a = (uintptr_t) ((isv ? vb + (int64_t) kr * p.v_nb1 : kb + (int64_t) kr * p.k_nb1) + 34 * j);
+                    const uint32_t sh = (uint32_t) (a & 3) * 8;
+                    const uint32_t * q = (const uint32_t *) (a & ~(uintptr_t) 3);
+                    uint32_t w[10], x[9];
+#pragma unroll
+                    for (int u = 0; u < 9; ++u) w[u] = q[u];
+                    w[9] = 0u;
+#pragma unroll
+                    for (int u = 0; u < 9; ++u) x[u] = __funnelshift_r(w[u], w[u + 1], sh);
+                    const uint16_t dbits = (uint16_t) (x[0] & 0xFFFFu);
+                    const __half2 d2 = __half2half2(*(const __half *) &dbits), off = __float2half2_rn(1152.0f);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        uint32_t ov[4];
+#pragma unroll
+                        for (int v = 0; v < 2; ++v) {
+                            const uint32_t y = __funnelshift_r(x[2 * u + v], x[2 * u + v + 1], 16) ^ 0x80808080u;
+                            const uint32_t lo = __byte_perm(y, 0x64646464u, 0x4140), hi = __byte_perm(y, 0x64646464u, 0x4342);
+                            const __half2 hl = __hmul2(__hsub2(*(const __half2 *) &lo, off), d2), hh = __hmul2(__hsub2(*(const __half2 *) &hi, off), d2);
+                            ov[2 * v] = *(const uint32_t *) &hl; ov[2 * v + 1] = *(const uint32_t *) &hh;
+                        }
+                        dstp[u] = make_uint4(ov[0], ov[1], ov[2], ov[3]);
+                    }
+                } else {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) dstp[u] = make_uint4(0u, 0u, 0u, 0u);
+                }
+            }
+        } else {
+            for (int i = lane; i < BN * CPR; i += 32) {
+                const int r = i / CPR, c = i % CPR, kr = base + r;
+                const uint32_t dk = sK_a + r * ROW + c * 16, dv = sV_a + r * ROW + c * 16;
+                if (kr < kv1) {
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dk), "l"(kb + (int64_t) kr * p.k_nb1 + c * 16) : "memory");
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dv), "l"(vb + (int64_t) kr * p.v_nb1 + c * 16) : "memory");
+                } else {
+                    *(uint4 *) (sK + r * ROW + c * 16) = make_uint4(0u, 0u, 0u, 0u);
+                    *(uint4 *) (sV + r * ROW + c * 16) = make_uint4(0u, 0u, 0u, 0u);
+                }
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        __syncwarp();
+
+        float sc[NT][4];
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) { sc[nt][0] = sc[nt][1] = sc[nt][2] = sc[nt][3] = 0.0f; }
+#pragma unroll
+        for (int kk = 0; kk < KS; kk += 2) {
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+                uint32_t b[4];
+                fa_ldsm4(sK_a + (nt * 8 + (lane & 7)) * ROW + (kk * 16 + 8 * (lane >> 3)) * 2, b);
+                fa_mma(sc[nt], qf[kk], b[0], b[1]);
+                fa_mma(sc[nt], qf[kk + 1], b[2], b[3]);
+            }
+        }
+        float mx = ma;
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            const int k = base + nt * 8 + t * 2;
+            float2 f = make_float2(0.0f, 0.0f);
+            if (mr) f = __half22float2(*(const __half2 *) (mr + (int64_t) min(k, p.n_kv - 2) * 2));
+            sc[nt][0] = k     < kv1 ? sc[nt][0] + f.x : -INFINITY;
+            sc[nt][1] = k + 1 < kv1 ? sc[nt][1] + f.y : -INFINITY;
+            mx = fmaxf(mx, fmaxf(sc[nt][0], sc[nt][1]));
+        }
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1)); mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+        const float ca = __expf(ma - mx);
+        ma = mx;
+        float sa = 0.0f;
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            sc[nt][0] = __expf(sc[nt][0] - mx); sc[nt][1] = __expf(sc[nt][1] - mx);
+            sa += sc[nt][0] + sc[nt][1];
+        }
+        la = la * ca + sa;
+#pragma unroll
+        for (int i = 0; i < DT; ++i) { o[i][0] *= ca; o[i][1] *= ca; }
+#pragma unroll
+        for (int j = 0; j < BN / 16; ++j) {
+            uint32_t pa[4];
+            pa[0] = fa_pack(sc[2 * j][0], sc[2 * j][1]); pa[1] = 0u;
+            pa[2] = fa_pack(sc[2 * j + 1][0], sc[2 * j + 1][1]); pa[3] = 0u;
+#pragma unroll
+            for (int dn = 0; dn < DT; dn += 2) {
+                uint32_t b[4];
+                const int mi = lane >> 3;
+                fa_ldsm4_t(sV_a + (16 * j + 8 * (mi & 1) + (lane & 7)) * ROW + ((dn + (mi >> 1)) * 8) * 2, b);
+                fa_mma(o[dn], pa, b[0], b[1]);
+                fa_mma(o[dn + 1], pa, b[2], b[3]);
+            }
+        }
+    }
+    la += __shfl_xor_sync(0xffffffffu, la, 1); la += __shfl_xor_sync(0xffffffffu, la, 2);
+    // ---- every warp is one state of the shared tail
+    if (g < NCOLS) {
+        float * os = sm + ((int64_t) warp * NCOLS + g) * ST;
+#pragma unroll
+        for (int i = 0; i < DT; ++i) { os[i * 8 + t * 2] = o[i][0]; os[i * 8 + t * 2 + 1] = o[i][1]; }
+        if (t == 0) { os[D] = ma <= 0.5f * M_NONE ? -INFINITY : ma; os[D + 1] = la; }
+    }
+    __syncthreads();
+    fattn_tail<D, NCOLS, NW>(p, sm, split, grp, seq, hkv, chunk, lane, warp);
+}
+
 struct fattn_plan { int ncols, n_chunks, n_split, kv_per_split, ncols_total; int64_t n_groups; size_t part_bytes, counter_bytes; };
 
 static bool fattn_make_plan(const b200_fattn_args * a, fattn_plan & pl) {
@@ -560,6 +733,49 @@ static bool fattn_use_mma(const b200_fattn_args * a) {
     for (int i = 1; i < 4; ++i) if (q.nb[i] % 8 || d.nb[i] % 8) return false;
     if (a->mask && (((uintptr_t) a->mask->data) % 4 || a->mask->nb[1] % 4 || a->mask->nb[2] % 4 || a->mask->nb[3] % 4)) return false;
     return true;
+}
+
+// long-context decode (>= 1024 positions) of up to 8 columns on the tensor cores; B200_FATTN_DECODE_MMA=0 keeps the vector kernel
+static bool fattn_use_dec_mma(const b200_fattn_args * a) {
+    static const bool on = [] { const char * e = getenv("B200_FATTN_DECODE_MMA"); return !(e && atoi(e) == 0); }();   // =0: vector kernel only
+    if (!on) return false;
+    const b200_tensor & q = a->q; const b200_tensor & k = a->k; const b200_tensor & v = a->v;
+    const int64_t D = q.ne[0], n_kv = k.ne[1];
+    if ((D != 64 && D != 128) || a->logit_softcap != 0.0f || a->max_bias != 0.0f || n_kv < 1024 || n_kv % 2) return false;
+    if (k.type == B200_Q8_0) {
+        if (((uintptr_t) k.data | (uintptr_t) v.data) % 4) return false;
+        for (int i = 1; i < 4; ++i) if (k.nb[i] % 4 || v.nb[i] % 4) return false;
+    } else if (k.type != B200_F16) return false;
+    if (((uintptr_t) q.data) % 8) return false;
+    for (int i = 1; i < 4; ++i) if (q.nb[i] % 8) return false;
+    if (a->mask && (((uintptr_t) a->mask->data) % 4 || a->mask->nb[1] % 4 || a->mask->nb[2] % 4 || a->mask->nb[3] % 4)) return false;
+    return true;
+}
+template <int D, int KVT, int NCOLS>
+static int fattn_launch_dec_mma_n(const fattn_params & p, dim3 grid, cudaStream_t st) {
+    const size_t smem = (size_t) 4 * 2 * 32 * (D * 2 + 16) + std::max((size_t) 4 * NCOLS * (D + 2) * 4, (size_t) NCOLS * p.n_split * 4);
+    static bool attr_set[64] = {};
+    int dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(fattn_dec_mma_kernel<D, KVT, NCOLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        attr_set[dev] = true;
+    }
+    fattn_dec_mma_kernel<D, KVT, NCOLS><<<grid, 128, smem, st>>>(p);
+    return B200_OK;
+}
+template <int D, int KVT>
+static int fattn_launch_dec_mma(const fattn_params & p, int ncols, dim3 grid, cudaStream_t st) {
+    switch (ncols) {
+        case 1: return fattn_launch_dec_mma_n<D, KVT, 1>(p, grid, st);
+        case 2: return fattn_launch_dec_mma_n<D, KVT, 2>(p, grid, st);
+        case 3: return fattn_launch_dec_mma_n<D, KVT, 3>(p, grid, st);
+        case 4: return fattn_launch_dec_mma_n<D, KVT, 4>(p, grid, st);
+        case 5: return fattn_launch_dec_mma_n<D, KVT, 5>(p, grid, st);
+        case 6: return fattn_launch_dec_mma_n<D, KVT, 6>(p, grid, st);
+        case 7: return fattn_launch_dec_mma_n<D, KVT, 7>(p, grid, st);
+        default: return fattn_launch_dec_mma_n<D, KVT, 8>(p, grid, st);
+    }
 }
 
 template <int D, int KVT>
@@ -625,6 +841,14 @@ extern "C" int b200_flash_attn_ext(const b200_fattn_args * a, void * stream) {
     if (pl.n_split > 1)   // arrival counters of the split-KV combine: zeroed per launch (a memset node under graph capture)
         B200_CUDA_TRY(cudaMemsetAsync(p.counters, 0, pl.counter_bytes, st));
     const int D = (int) q.ne[0];
+    if (fattn_use_dec_mma(a)) {
+        int rc;
+        if (k.type == B200_F16) rc = D == 64 ? fattn_launch_dec_mma<64, B200_F16>(p, pl.ncols, grid, st) : fattn_launch_dec_mma<128, B200_F16>(p, pl.ncols, grid, st);
+        else                    rc = D == 64 ? fattn_launch_dec_mma<64, B200_Q8_0>(p, pl.ncols, grid, st) : fattn_launch_dec_mma<128, B200_Q8_0>(p, pl.ncols, grid, st);
+        if (rc != B200_OK) return rc;
+        count_launch();
+        return check_launch("flash_attn_ext (decode mma)");
+    }
     if (k.type == B200_F16) {
         if (D == 64) fattn_launch_nc<64, B200_F16>(p, pl.ncols, grid, st);
         else if (D == 128) fattn_launch_nc<128, B200_F16>(p, pl.ncols, grid, st);
