@@ -21,7 +21,7 @@ configs[1]).
             sample (tg16) of the same GGUF on this box's host cores.
 
 --impl reference times the reference's own CPU implementation (oracle/_ref/llama-bench, CPU backend,
-all host threads) on the same GGUF; each step is a bounded sample (tg32) of the workload.
+all host threads) on the same GGUF and the same step (one tg128 run, about 6 s on 16 host cores for the 8B model).
 """
 from __future__ import annotations
 
@@ -105,7 +105,7 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def run_llama_bench(gguf, n_gen, n_prompt, reps, plugin: bool, threads=None, extra_env=None, timeout=1500):
+def run_llama_bench(gguf, n_gen, n_prompt, reps, plugin: bool, threads=None, extra_env=None, timeout=1500, n_devices=None, extra_args=()):
     """Run the reference's llama-bench; returns the parsed JSON list (or raises)."""
     env = dict(os.environ)
     env.pop("GGML_BACKEND_PATH", None)
@@ -113,14 +113,27 @@ def run_llama_bench(gguf, n_gen, n_prompt, reps, plugin: bool, threads=None, ext
         from llama_mi50_b200 import BACKEND_SO
         env["GGML_BACKEND_PATH"] = BACKEND_SO
     env.update(extra_env or {})
+    if plugin and n_devices is not None:
+        # llama-bench offloads to EVERY device the plugin registers (layer split): on a multi-GPU box an N-GPU measurement
+        # must see exactly N devices
+        vis = [x for x in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if x.strip()]
+        env["CUDA_VISIBLE_DEVICES"] = ",".join(vis[:n_devices]) if vis else ",".join(str(i) for i in range(n_devices))
     cmd = [LLAMA_BENCH, "-m", gguf, "-p", str(n_prompt), "-n", str(n_gen), "-r", str(reps), "-fa", "1", "-o", "json",
            "-ngl", "99" if plugin else "0"]
     if threads:
         cmd += ["-t", str(threads)]
+    cmd += list(extra_args)
     r = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=timeout)
     if r.returncode != 0:
         raise RuntimeError(f"llama-bench failed rc={r.returncode}: {r.stderr[-2000:]}")
     return json.loads(r.stdout)
+
+
+def workload_config(key, world):
+    """`config` of the JSON line: the workload, identical for the b200 arm and the reference arm."""
+    return {"workload": key, "n_prompt": 0, "n_gen": N_GEN, "n_kv": 256, "kv_type": "f16", "flash_attn": 1,
+            "parallelism": f"row-split tp{world}" if world > 1 else "single device",
+            "l2": "inputs larger than L2 (every weight byte is read once per token; the model is >> 126 MB)"}
 
 
 def cpu_baseline(gguf, n_gen=16):
@@ -143,7 +156,7 @@ def main_reference(a):
     key = WORKLOADS[a.workload]
     gguf = ensure_gguf(key)
     cores = host_cores()
-    n_gen = 32
+    n_gen = N_GEN          # the b200 arm's step: one llama-bench tg128 run (about 6 s per step on 16 host cores for the 8B model)
     t0 = time.time()
     res = run_llama_bench(gguf, n_gen, 0, a.steps + a.warmup, plugin=False, threads=cores)
     tg = [x for x in res if x["n_gen"] == n_gen][0]
@@ -153,7 +166,7 @@ def main_reference(a):
     line = {"impl": "reference", "metric": "llama-bench tg128 tok/s", "value": round(val, 3), "unit": "tok/s", "n_gpus": a.gpus,
             "steps": len(ns), "warmup": a.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "int8 x int4/6 (ggml CPU vec_dot, Q8_K activations)", "data": "synthetic",
-            "config": {"workload": key, "n_gen": N_GEN, "step": f"bounded sample: tg{n_gen} per step", "flash_attn": 1},
+            "config": workload_config(key, a.gpus),
             "cpu_baseline": {"value": round(val, 3), "unit": "tok/s", "cores": cores, "kind": "reference",
                              "sample": f"llama-bench tg{n_gen} x {len(ns)} reps, ggml CPU backend, -t {cores}, {tg.get('cpu_info', '?')}"},
             "e2e": {"value": round(val, 3), "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -307,10 +320,8 @@ def main_b200(a):
     line = {"metric": "llama-bench tg128 tok/s", "value": round(value, 2), "unit": "tok/s", "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": round(ms_per_step, 3), "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "int8 x int4/6 dp4a, f32 accumulate", "data": "synthetic",
-            "config": {"workload": key, "n_gen": N_GEN, "n_kv": n_ctx, "kv_type": "f16", "flash_attn": 1,
-                       "parallelism": (f"row-split tp{world}, " + ("decode chain over NVLink peer memory (no collective)" if mode == "chain" else "NCCL all-gather per matmul"))
-                                      if world > 1 else "single GPU", "issue": a.mode,
-                       "l2": "inputs larger than L2 (weights %.2f GB per token vs 126 MB L2)" % (wbytes / 1e9)},
+            "config": workload_config(key, world), "issue": a.mode,
+            "exchange": ("decode chain over NVLink peer memory (no collective)" if mode == "chain" else "NCCL all-gather per matmul") if world > 1 else None,
             "roofline": roofline, "clocks": clocks, "gpu_launches": gpu_launches,
             "e2e": {"value": round(e2e_cabi, 2), "unit": "tok/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "via": "c-abi session (pinned-host token H2D + logits D2H + sync per token)"}}
@@ -322,7 +333,7 @@ def main_b200(a):
         try:
             gguf = ensure_gguf(key)
             if os.path.exists(LLAMA_BENCH):
-                res = run_llama_bench(gguf, N_GEN, 512, a.steps + min(a.warmup, 2), plugin=True, extra_env={"GGML_B200_TIMING": "0"})
+                res = run_llama_bench(gguf, N_GEN, 512, a.steps + min(a.warmup, 2), plugin=True, extra_env={"GGML_B200_TIMING": "0"}, n_devices=1)
                 tg = [x for x in res if x["n_gen"] == N_GEN][0]
                 pp = [x for x in res if x["n_prompt"] == 512][0]
                 w = min(a.warmup, 2)

@@ -227,9 +227,17 @@ struct matcher {
         // ---- shapes
         const int64_t D = kc->ne[0], n_kv = kc->ne[1], H_kv = kc->ne[2], H = ggml_nelements(q) / D;
         if (q->ne[0] != D || ggml_nelements(q) != mm[0]->ne[0] || mm[1]->ne[0] != D * H_kv || mm[2]->ne[0] != D * H_kv || H % H_kv != 0) return 0;
+        // the attention phase gives one query head to one CTA and walks all n_kv positions: beyond ~1k positions the
+        // split-KV kernels (b200_flash_attn_ext: vector / tensor-core decode) are faster even with the chain cut in two
+        static const int64_t attn_max_kv = [] { const char * e = getenv("GGML_B200_CHAIN_ATTN_MAX_KV"); return e ? (int64_t) atoll(e) : (int64_t) 1024; }();
+        if (n_kv > attn_max_kv) return 0;
         if (kc->ne[3] != 1 || vc->ne[0] != D || vc->ne[1] != n_kv || vc->ne[2] != H_kv || vc->ne[3] != 1) return 0;
         if (kc->data != k_leaf->data || vc->data != v_leaf->data || kc->nb[1] != k_leaf->nb[1] || vc->nb[1] != v_leaf->nb[1]) return 0;
         if (k_leaf->ne[0] != D * H_kv || v_leaf->ne[0] != D * H_kv) return 0;
+        // the attention phase writes cache row `slot` at leaf->data + slot * leaf->nb[1]: the SET_ROWS it replaces must address
+        // the cache the same way (no offset or merged view in between)
+        if (sr_k->data != k_leaf->data || sr_k->nb[1] != k_leaf->nb[1] || sr_k->ne[0] != D * H_kv) return 0;
+        if (sr_v->data != v_leaf->data || sr_v->nb[1] != v_leaf->nb[1] || sr_v->ne[0] != D * H_kv) return 0;
         for (const ggml_tensor * sr : {sr_k, sr_v}) {
             const ggml_tensor * ids = sr->src[1];
             if (ids->type != GGML_TYPE_I64 || ggml_nelements(ids) != 1 || !is_f32_vec(sr->src[0], D * H_kv) || sr->type != GGML_TYPE_F16) return 0;
@@ -363,7 +371,8 @@ struct matcher {
         if (defer_norm) {
             // nothing the phase writes may alias the deferred norm's output, and nobody but the phase may read it before
             for (int s2 = 0; s2 < a.n_seg; ++s2)
-                if (overlap(a.seg[s2].dst.data, (size_t) a.seg[s2].dst.ne[0] * 4, mul->data, ggml_nbytes(mul))) return 0;
+                if (overlap(a.seg[s2].dst.data, (size_t) a.seg[s2].dst.ne[0] * 4, mul->data, ggml_nbytes(mul)) ||
+                    overlap(a.seg[s2].dst.data, (size_t) a.seg[s2].dst.ne[0] * 4, g->nodes[i]->data, ggml_nbytes(g->nodes[i]))) return 0;
             if (ggml_node_get_use_count(g, i + 1) != n_mm) return 0;
         }
         b200_plan_item it{}; it.kind = B200_ITEM_PHASE; it.phase = ph; it.first_node = i;

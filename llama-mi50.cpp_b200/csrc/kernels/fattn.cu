@@ -11,6 +11,8 @@
 #include <algorithm>
 #include <cstdlib>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -724,6 +726,9 @@ static bool fattn_use_mma(const b200_fattn_args * a) {
     const b200_tensor & q = a->q; const b200_tensor & k = a->k; const b200_tensor & v = a->v; const b200_tensor & d = a->dst;
     const int64_t D = q.ne[0], n_q = q.ne[1], n_kv = k.ne[1];
     if (n_q < 16 || (D != 64 && D != 128) || a->sinks || a->logit_softcap != 0.0f || a->max_bias != 0.0f) return false;
+    // this kernel has no split-KV: a CTA walks all n_kv positions of its 64 query rows.  A small batch (16-63 tokens of
+    // speculative / parallel decode) at long context would leave most SMs idle: it stays on the split-KV decode path
+    if (n_kv > 2048 && ((n_q + 63) / 64) * q.ne[2] * q.ne[3] < 74) return false;
     if (k.type == B200_Q8_0) {          // blocks are read as aligned words around their 2-byte aligned start
         if (((uintptr_t) k.data | (uintptr_t) v.data) % 4) return false;
         for (int i = 1; i < 4; ++i) if (k.nb[i] % 4 || v.nb[i] % 4) return false;
@@ -754,13 +759,13 @@ static bool fattn_use_dec_mma(const b200_fattn_args * a) {
 template <int D, int KVT, int NCOLS>
 static int fattn_launch_dec_mma_n(const fattn_params & p, dim3 grid, cudaStream_t st) {
     const size_t smem = (size_t) 4 * 2 * 32 * (D * 2 + 16) + std::max((size_t) 4 * NCOLS * (D + 2) * 4, (size_t) NCOLS * p.n_split * 4);
-    static bool attr_set[64] = {};
+    static std::once_flag attr_once[64];                       // per device; launches may come from several host threads
     int dev = 0;
     B200_CUDA_TRY(cudaGetDevice(&dev));
-    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(fattn_dec_mma_kernel<D, KVT, NCOLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-        attr_set[dev] = true;
-    }
+    if (dev < 0 || dev >= 64) return B200_ERR_ARG;
+    cudaError_t attr_rc = cudaSuccess;
+    std::call_once(attr_once[dev], [&] { attr_rc = cudaFuncSetAttribute(fattn_dec_mma_kernel<D, KVT, NCOLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); });
+    B200_CUDA_TRY(attr_rc);
     fattn_dec_mma_kernel<D, KVT, NCOLS><<<grid, 128, smem, st>>>(p);
     return B200_OK;
 }

@@ -3,6 +3,7 @@
 #pragma once
 #include <algorithm>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "quantize.cuh"
@@ -848,8 +849,16 @@ __device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int * p) {
 template <bool PEER>
 __device__ __forceinline__ void gs_wait_counter(const unsigned int * bar, unsigned int target) {
     if (!PEER) {
-        unsigned int spins = 0;
-        while (ld_acquire_gpu(bar) < target) { if (++spins > (1u << 24)) __trap(); }
+        // bounded by WALL time, not by iterations: under compute-sanitizer, ncu replay or GPU time-slicing a healthy wait can
+        // outlast any iteration count.  20 s without progress is a deadlock (a trap ends the context instead of hanging the GPU)
+        unsigned int spins = 0; unsigned long long t0 = 0;
+        while (ld_acquire_gpu(bar) < target) {
+            if ((++spins & 0xFFFu) == 0) {
+                const unsigned long long now = gs_now();
+                if (!t0) t0 = now; else if (now - t0 > 20000000000ull) __trap();
+                __nanosleep(64);
+            }
+        }
     } else {
         unsigned int spins = 0; unsigned long long t0 = 0;
         while ((int) (ld_acquire_sys(bar) - target) < 0) {
@@ -1003,14 +1012,13 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
 template <int T0, int T1, int MODE>
 int gs_launch(const gs_params & p, size_t smem, int grid, cudaStream_t st) {
     constexpr bool CHAIN = MODE >= 1;
-    static bool attr_set[64] = {};
+    static std::once_flag attr_once[64];                       // per device; launches may come from several host threads
     int dev = 0;
     B200_CUDA_TRY(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64) return B200_ERR_ARG;
-    if (!attr_set[dev]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(gemv_stream_kernel<T0, T1, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, GS_SMEM_MAX));
-        attr_set[dev] = true;
-    }
+    cudaError_t attr_rc = cudaSuccess;
+    std::call_once(attr_once[dev], [&] { attr_rc = cudaFuncSetAttribute(gemv_stream_kernel<T0, T1, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, GS_SMEM_MAX); });
+    B200_CUDA_TRY(attr_rc);
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned) grid); cfg.blockDim = dim3(GS_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
     cudaLaunchAttribute at[1];

@@ -6,7 +6,7 @@
 //
 // This file holds the GENERIC kernel: any strides, batch/broadcast, ids, fused bias/gate/GLU,
 // byte-granular loads, one warp per output row.  The streaming fast path for contiguous decode
-// weights lives in mmvq_stream.cu and is selected by the launcher below when it applies.
+// weights is a separate entry point (b200_gemv_fused / the decode chain, gemv_stream.cu).
 #include "vecdot.cuh"
 
 namespace b200 {
@@ -142,8 +142,6 @@ static int launch_type(const mmvq_params & p, int ncols, bool ids, bool fused, d
     }
 }
 
-int mmvq_stream_try(const b200_mmvq_args * a, void * stream);   // mmvq_stream.cu; B200_ERR_UNSUPPORTED if n/a
-
 }  // namespace b200
 
 using namespace b200;
@@ -189,9 +187,6 @@ extern "C" int b200_mul_mat_vec_q(const b200_mmvq_args * a, void * stream) {
     if (!b200_mmvq_supported(a)) { set_error("b200_mul_mat_vec_q: unsupported arguments"); return B200_ERR_UNSUPPORTED; }
     const b200_tensor & w = a->w; const b200_tensor & d = a->dst;
     if (nelements(d) == 0) return B200_OK;
-
-    const int rs = mmvq_stream_try(a, stream);
-    if (rs != B200_ERR_UNSUPPORTED) return rs;
 
     mmvq_params p{};
     p.w = (const uint8_t *) w.data; p.gate_w = a->gate_w ? (const uint8_t *) a->gate_w->data : nullptr;

@@ -3,11 +3,15 @@
 // backend and once with every layer offloaded to the plugin; the logits of every step are compared (NMSE).
 // usage: plugin-parity model.gguf backend_dir plugin.so [n_prompt n_decode tol]
 // B200_PARITY_SPLIT_ROW=1: the plugin run uses --split-mode row (weights in the backend's split buffer type).
+// B200_PARITY_KV=q8_0 (or f16): type of the K and V caches in BOTH runs (-ctk / -ctv); B200_PARITY_NCTX=n: context size
+// (default 1024).  Prompts longer than the batch size are decoded in chunks; the logits of the last chunk are compared.
 #include "llama.h"
 #include "ggml.h"
 #include "ggml-backend.h"
 
+#include <algorithm>
 #include <cmath>
+#include <cstring>
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -20,12 +24,19 @@ static std::vector<std::vector<float>> run(const char * path, int ngl, int n_pro
     if (!m) { fprintf(stderr, "model load failed\n"); exit(3); }
     const int n_vocab = llama_vocab_n_tokens(llama_model_get_vocab(m));
     llama_context_params cp = llama_context_default_params();
-    cp.n_ctx = 1024; cp.n_batch = 512; cp.flash_attn_type = LLAMA_FLASH_ATTN_TYPE_ENABLED; cp.n_threads = 8; cp.n_threads_batch = 8;
+    cp.n_ctx = getenv("B200_PARITY_NCTX") ? atoi(getenv("B200_PARITY_NCTX")) : 1024;
+    cp.n_batch = 512; cp.flash_attn_type = LLAMA_FLASH_ATTN_TYPE_ENABLED; cp.n_threads = 8; cp.n_threads_batch = 8;
+    if (const char * kv = getenv("B200_PARITY_KV")) {
+        const ggml_type t = !strcmp(kv, "q8_0") ? GGML_TYPE_Q8_0 : !strcmp(kv, "q4_0") ? GGML_TYPE_Q4_0 : GGML_TYPE_F16;
+        cp.type_k = t; cp.type_v = t;
+    }
     llama_context * c = llama_init_from_model(m, cp);
+    if (!c) { fprintf(stderr, "context creation failed\n"); exit(3); }
     std::vector<std::vector<float>> out;
     std::vector<llama_token> prompt;
     for (int i = 0; i < n_prompt; ++i) prompt.push_back((llama_token) ((i * 37 + 11) % n_vocab));
-    if (llama_decode(c, llama_batch_get_one(prompt.data(), n_prompt)) != 0) { fprintf(stderr, "prompt decode failed\n"); exit(4); }
+    for (int i0 = 0; i0 < n_prompt; i0 += (int) cp.n_batch)
+        if (llama_decode(c, llama_batch_get_one(prompt.data() + i0, std::min<int>(cp.n_batch, n_prompt - i0))) != 0) { fprintf(stderr, "prompt decode failed\n"); exit(4); }
     { const float * l = llama_get_logits_ith(c, -1); out.emplace_back(l, l + n_vocab); }
     for (int i = 0; i < n_decode; ++i) {
         llama_token t = (llama_token) ((i * 101 + 7) % n_vocab);     // fixed stream: both runs see identical inputs

@@ -25,7 +25,8 @@ def _dequant(orc, gs, raw, t, K, M):
 
 @pytest.mark.parametrize("act_fmt", [0])
 @pytest.mark.parametrize("t", [Q4_K, Q6_K, Q4_0, Q8_0, MXFP4])
-@pytest.mark.parametrize("M,K,N", [(256, 512, 300), (128, 256, 9), (384, 1024, 512), (200, 768, 64), (256, 2048, 40), (4096, 4096, 512)])
+@pytest.mark.parametrize("M,K,N", [(256, 512, 300), (128, 256, 9), (384, 1024, 512), (200, 768, 64), (256, 2048, 40), (4096, 4096, 512),
+                                   (256, 4096, 40), (128, 14336, 64)])      # the attn_v / ffn_down shapes of Llama-3-8B (Q6_K in Q4_K_M)
 def test_mul_mat_q_vs_float64(orc, t, M, K, N, act_fmt):
     import torch
     from llama_mi50_b200 import capi, gguf_synth as gs

@@ -115,7 +115,7 @@ def _kv_bytes(orc, capi, x, kv_type):
 @pytest.mark.parametrize("D,H,H_kv,n_q,n_kv", [(128, 32, 8, 1, 256), (64, 32, 4, 1, 300), (128, 40, 8, 1, 4096),
                                                  (128, 8, 8, 2, 1000), (64, 16, 4, 35, 512), (256, 4, 1, 1, 700), (128, 64, 8, 1, 32768),
                                                  (128, 8, 2, 130, 600)])
-@pytest.mark.parametrize("extras", ["plain", "mask", "mask+sinks+softcap", "alibi"])
+@pytest.mark.parametrize("extras", ["plain", "mask", "mask+sinks+softcap", "mask+sinks", "alibi"])      # mask+sinks: the gpt-oss form
 def test_flash_attn_decode(orc, kv_type, D, H, H_kv, n_q, n_kv, extras):
     torch, capi, _ = _mods()
     if n_kv == 32768 and extras not in ("mask",):
@@ -141,7 +141,7 @@ def test_flash_attn_decode(orc, kv_type, D, H, H_kv, n_q, n_kv, extras):
         mask = m.astype(np.float16)
     if "sinks" in extras:
         sinks = rng.standard_normal(H).astype(np.float32)
-        softcap = 10.0
+        softcap = 10.0 if "softcap" in extras else 0.0
     got = capi.flash_attn(torch.from_numpy(q).cuda(), torch.from_numpy(kb).cuda(), torch.from_numpy(vb).cuda(), t, n_kv, H_kv,
                           mask=None if mask is None else torch.from_numpy(mask).cuda(),
                           sinks=None if sinks is None else torch.from_numpy(sinks).cuda(),
@@ -154,5 +154,5 @@ def test_flash_attn_decode(orc, kv_type, D, H, H_kv, n_q, n_kv, extras):
     # reference gate: NMSE <= 5e-4 (tests/test-backend-ops.cpp:6082-6084); the f32 vector kernel is far tighter.  Many query
     # positions over an f16 cache run on the tensor cores (Q and P rounded to f16, f32 accumulation): 2e-6
     dec_mma = bool(int(os.environ.get("B200_FATTN_DECODE_MMA", "1"))) and n_kv >= 1024 and D in (64, 128)   # tensor-core decode kernel (long contexts)
-    mma = (n_q >= 16 or dec_mma) and extras in ("plain", "mask") and n_kv % 2 == 0
+    mma = ((n_q >= 16 and extras in ("plain", "mask")) or (dec_mma and extras in ("plain", "mask", "mask+sinks"))) and n_kv % 2 == 0
     assert orc.orc_nmse(ptr(want), ptr(np.ascontiguousarray(got)), C.c_size_t(want.size)) < (2e-6 if mma else 1e-8)

@@ -45,3 +45,70 @@ def test_plugin_row_split_matches_cpu_backend(key, tmp_path):
     out = subprocess.run([exe, path, REF_DIR, PLUGIN, "20", "8", "2e-3"], capture_output=True, text=True, timeout=600, env=env)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     assert "plugin-parity: PASS" in out.stdout
+
+
+def _parity(path, n_prompt, n_decode, tol, env_extra=None, timeout=900):
+    exe = os.path.join(REF_DIR, "plugin-parity")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/plugin-parity not built")
+    env = dict(os.environ, **(env_extra or {}))
+    out = subprocess.run([exe, path, REF_DIR, PLUGIN, str(n_prompt), str(n_decode), str(tol)], capture_output=True, text=True, timeout=timeout, env=env)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
+    assert "plugin-parity: PASS" in out.stdout
+    return out.stdout
+
+
+def test_plugin_llama3_8b_matches_cpu_backend(tmp_path):
+    """The model the bench times (BASELINE.json configs[1], Llama-3-8B-shape Q4_K_M: the 161-phase decode chain and the
+    tcgen05 prefill GEMM at their real sizes): a 64-token prompt and 3 decode steps against the CPU backend.  Tolerance
+    5e-3: 32 layers of q8_1 (here) vs Q8_K (CPU) activation rounding compound; every matmul alone is gated at 5e-4 by
+    test-backend-ops (tests/test_gpu_tbo.py)."""
+    from llama_mi50_b200 import gguf_synth as gs
+    model_dir = os.environ.get("B200_MODEL_DIR", "/tmp/b200_models")
+    os.makedirs(model_dir, exist_ok=True)
+    path = os.path.join(model_dir, "llama3-8b-q4_k_m.gguf")      # shared with bench.py
+    if not os.path.exists(path):
+        gs.write_gguf(path + ".tmp", gs.SHAPES["llama3-8b-q4_k_m"])
+        os.replace(path + ".tmp", path)
+    out = _parity(path, 64, 3, 5e-3, timeout=1500)
+    print(out[-600:])
+
+
+@pytest.mark.parametrize("chain", [True, False])
+@pytest.mark.parametrize("key", ["tiny-q8_0", "tiny-q4_k_m"])
+def test_plugin_q8_0_kv_cache(key, chain, tmp_path):
+    """-ctk q8_0 -ctv q8_0 (BASELINE.json configs[2]): SET_ROWS quantises K/V rows to q8_0 blocks, attention reads them."""
+    from llama_mi50_b200 import gguf_synth as gs
+    path = str(tmp_path / f"{key}.gguf")
+    gs.write_gguf(path, gs.SHAPES[key])
+    env = {"B200_PARITY_KV": "q8_0"}
+    if not chain:
+        env["GGML_B200_DISABLE_CHAIN"] = "1"
+    _parity(path, 20, 12, 2e-3, env)
+
+
+@pytest.mark.parametrize("chain", [True, False])
+def test_plugin_decodes_across_kv_padding_boundaries(chain, tmp_path):
+    """n_kv is padded to 256: decoding from position 250 to 550 changes the graph twice (256 -> 512 -> 768), which drops
+    the captured CUDA graph, destroys the chains (their phases bake in n_kv and addresses) and rebuilds the plan
+    (exec.cpp b200_graph_compute, key mismatch path).  Every step's logits are compared with the CPU backend."""
+    from llama_mi50_b200 import gguf_synth as gs
+    path = str(tmp_path / "tiny-q4_k_m.gguf")
+    gs.write_gguf(path, gs.SHAPES["tiny-q4_k_m"])
+    env = {} if chain else {"GGML_B200_DISABLE_CHAIN": "1"}
+    out = _parity(path, 250, 300, 2e-3, env)
+    assert out.count(" ok") >= 301
+
+
+@pytest.mark.parametrize("chain", [True, False])
+@pytest.mark.parametrize("kv", ["f16", "q8_0"])
+def test_plugin_long_context(kv, chain, tmp_path):
+    """Context beyond 1024 positions through the plugin: the chain hands attention over to the split-KV kernels
+    (fattn_dec_mma_kernel from 1024 positions on), and the prompt (1000 tokens) runs the prefill attention in two batches."""
+    from llama_mi50_b200 import gguf_synth as gs
+    path = str(tmp_path / "tiny-q4_k_m.gguf")
+    gs.write_gguf(path, gs.SHAPES["tiny-q4_k_m"])
+    env = {"B200_PARITY_NCTX": "2048", "B200_PARITY_KV": kv}
+    if not chain:
+        env["GGML_B200_DISABLE_CHAIN"] = "1"
+    _parity(path, 1000, 60, 2e-3, env)
