@@ -287,6 +287,20 @@ B200_API int b200_rope(const b200_tensor * x, const b200_tensor * pos, const b20
 B200_API int b200_soft_max(const b200_tensor * x, const b200_tensor * mask, const b200_tensor * sinks,
                            const b200_tensor * dst, float scale, float max_bias, void * stream);
 
+/* ---- MoE routing glue (reference ggml-cuda/argsort.cu, top-k.cu, add-id.cu:28, sumrows.cu, clamp.cu) and the float-weight
+ * matmul of the router matrix (ggml-cuda.cu:2183-2266 / mmvf.cu).  Graph: reference src/llama-graph.cpp build_moe_ffn. */
+/* ARGSORT: dst i32 [ne0, rows] = indices that sort each f32 row (order 0 ascending, 1 descending); ne0 <= 32768 */
+B200_API int b200_argsort(const b200_tensor * x, const b200_tensor * dst, int order, void * stream);
+/* TOP_K: dst i32 [k, rows] = indices of the k largest values of each row (descending) */
+B200_API int b200_top_k(const b200_tensor * x, const b200_tensor * dst, void * stream);
+/* ADD_ID: dst[:, e, t] = a[:, e, t] + b[:, ids[e, t]]; a f32 [n, n_used, n_tok], b f32 [n, n_expert], ids i32 [n_used, n_tok] (strided) */
+B200_API int b200_add_id(const b200_tensor * a, const b200_tensor * b, const b200_tensor * ids, const b200_tensor * dst, void * stream);
+/* SUM_ROWS: dst[0, i1, i2, i3] = sum over ne0; CLAMP: dst = min(max(x, lo), hi) (contiguous) */
+B200_API int b200_sum_rows(const b200_tensor * x, const b200_tensor * dst, void * stream);
+B200_API int b200_clamp(const b200_tensor * x, const b200_tensor * dst, float lo, float hi, void * stream);
+/* MUL_MAT with f32 / f16 / bf16 weights [K, M] (2-D) and f32 activations [K, N]: dst f32 [M, N] */
+B200_API int b200_mul_mat_f(const b200_tensor * w, const b200_tensor * x, const b200_tensor * dst, void * stream);
+
 /* ---- K7: FLASH_ATTN_EXT decode (fattn-vec.cuh:19-507, fattn-common.cuh:728-779, launch :781-1036)
  * q f32 [D, n_q, H, n_seq]; k,v f16 or q8_0 [D, n_kv, H_kv, n_seq] (row stride = cache stride);
  * mask f16 [n_kv, n_q_pad, 1|.., 1|n_seq] or NULL; sinks f32 [H] or NULL; dst f32 [D, H, n_q, n_seq].

@@ -318,8 +318,22 @@ int run_node(exec_state & st, const ggml_tensor * n) {
             float sc, mb; memcpy(&sc, n->op_params, 4); memcpy(&mb, (const float *) n->op_params + 1, 4);
             RUN(b200_soft_max(&a, s1 ? &m : nullptr, n->src[2] ? &k : nullptr, &d, sc, mb, s));
         }
+        case GGML_OP_ARGSORT: { b200_tensor a = b200_desc(s0), d = b200_desc(n); RUN(b200_argsort(&a, &d, n->op_params[0], s)); }
+        case GGML_OP_TOP_K:   { b200_tensor a = b200_desc(s0), d = b200_desc(n); RUN(b200_top_k(&a, &d, s)); }
+        case GGML_OP_ADD_ID:  { b200_tensor a = b200_desc(s0), b = b200_desc(s1), i = b200_desc(n->src[2]), d = b200_desc(n); RUN(b200_add_id(&a, &b, &i, &d, s)); }
+        case GGML_OP_SUM_ROWS: { b200_tensor a = b200_desc(s0), d = b200_desc(n); RUN(b200_sum_rows(&a, &d, s)); }
+        case GGML_OP_CLAMP: {
+            b200_tensor a = b200_desc(s0), d = b200_desc(n); float lo, hi; memcpy(&lo, n->op_params, 4); memcpy(&hi, (const float *) n->op_params + 1, 4);
+            RUN(b200_clamp(&a, &d, lo, hi, s));
+        }
         case GGML_OP_FLASH_ATTN_EXT: return run_flash_attn(st, n);
-        case GGML_OP_MUL_MAT: case GGML_OP_MUL_MAT_ID: return run_mul_mat(st, n, nullptr, nullptr, nullptr, B200_GLU_NONE, 0.0f, 0.0f);
+        case GGML_OP_MUL_MAT:
+            if (s0->type == GGML_TYPE_F32 || s0->type == GGML_TYPE_F16 || s0->type == GGML_TYPE_BF16) {     // the MoE router matrix
+                if (is_split_tensor(s0)) return B200_ERR_UNSUPPORTED;
+                b200_tensor a = b200_desc(s0), b = b200_desc(s1), d = b200_desc(n); RUN(b200_mul_mat_f(&a, &b, &d, s));
+            }
+            return run_mul_mat(st, n, nullptr, nullptr, nullptr, B200_GLU_NONE, 0.0f, 0.0f);
+        case GGML_OP_MUL_MAT_ID: return run_mul_mat(st, n, nullptr, nullptr, nullptr, B200_GLU_NONE, 0.0f, 0.0f);
         default: return B200_ERR_UNSUPPORTED;
     }
 }

@@ -228,11 +228,12 @@ struct b200_chain {
     size_t smem = 0;
     int grid = 0, t0 = -1, t1 = -1, device = 0;
     gs_phase * d_phases = nullptr;
-    unsigned int * d_bar = nullptr;
+    unsigned int * d_ctl = nullptr;    // [0] launches completed (the epoch of the tags), [1] CTAs that have left the current launch
+    unsigned long long * d_shadow = nullptr;   // tagged words of every output a later phase reads (private to this chain)
+    int2 * d_ranges = nullptr;         // rows of every (phase, CTA, segment)
     int n_gemv = 0, n_attn = 0;
     unsigned long long * d_dbg = nullptr;
     bool peer = false;                 // row split over peer memory
-    unsigned int * d_epoch = nullptr;
 };
 
 static bool gs_build_attn(const b200_attn_phase * a, gs_phase & ph, int & attn_floats) {
@@ -266,97 +267,66 @@ static bool gs_build_attn(const b200_attn_phase * a, gs_phase & ph, int & attn_f
     return true;
 }
 
-// ---- row split: who produced what.  Looks backwards from phase i for the matmul whose output lies inside the f32 range
-// [ptr, ptr + n): returns its phase index and the elements [lo, hi) THIS rank computed there (the rest of the range comes
-// from the other ranks); -1: not produced by a row-split matmul of this chain (graph input, attention output: local);
-// -2: an overlap this kernel cannot express.
-static int gs_find_producer(const b200_phase * phases, int i, const void * ptr, int64_t n, int & lo, int & hi) {
+// ---- who produced what.  Every value a phase reads from an earlier phase of the chain travels as a tagged word in a shadow
+// array (gemv_stream.cuh, gs_seg).  An OUTPUT of phase j is a run of f32: a GEMV segment's dst or an attention phase's dst.
+struct gs_output { const char * p0; const char * p1; int phase; int seg; unsigned long long * ll; bool consumed; };
+
+// the most recent output before phase i that overlaps the f32 range [ptr, ptr + n); null: plain memory (written before the launch)
+static gs_output * gs_find_output(std::vector<gs_output> & outs, int i, const void * ptr, int64_t n) {
     const char * p0 = (const char *) ptr, * p1 = p0 + 4 * n;
-    for (int j = i - 1; j >= 0; --j) {
-        if (phases[j].kind == B200_PHASE_ATTN) {
-            const b200_tensor & d = phases[j].attn.dst;
-            const char * d0 = (const char *) d.data, * d1 = d0 + 4 * nelements(d);
-            if (d0 < p1 && d1 > p0) return -1;
-            continue;
-        }
-        if (phases[j].kind != B200_PHASE_GEMV) continue;
-        const b200_gemv_fused_args & g = phases[j].gemv;
-        int hits = 0;
-        for (int k = 0; k < g.n_seg && k < B200_GEMV_MAX_SEG; ++k) {
-            if (g.glu_op != B200_GLU_NONE && k == 0) continue;                 // the gate segment has no dst of its own
-            const char * d0 = (const char *) g.seg[k].dst.data;
-            const int64_t M = g.seg[k].w.ne[1];
-            if (!d0) continue;
-            if (d0 >= p0 && d0 < p1 && d0 + 4 * M <= p1) { lo = (int) ((d0 - p0) / 4); hi = lo + (int) M; ++hits; }
-            else if (M > 0 && d0 < p1 && d0 + 4 * M > p0) return -2;
-        }
-        if (hits > 1) return -2;
-        if (hits == 1) return j;
+    gs_output * best = nullptr;
+    for (gs_output & o : outs) {
+        // an EMPTY output (row split: a rank that owns no rows of a matrix still names where its slice would start, an address
+        // inside the full dst) counts as produced: the other ranks' rows of that phase fill the range
+        const bool hit = o.p0 == o.p1 ? (o.p0 >= p0 && o.p0 < p1) : (o.p0 < p1 && o.p1 > p0);
+        if (o.phase < i && hit && (!best || o.phase > best->phase)) best = &o;
     }
-    return -1;
+    return best;
 }
 
 static b200_chain * gs_chain_create(const b200_phase * phases_in, int n_phases, int flags, const b200_peer_group * pg) {
     if (!phases_in || n_phases < 1 || n_phases > GS_MAX_PHASES) { set_error("b200_chain_create: bad phase count"); return nullptr; }
     std::vector<b200_phase> phv(phases_in, phases_in + n_phases);        // private copy: zero-row segments are removed below
-    struct peer_info { int x_lo = 0, x_hi = 0, x_tag = 0, q[3] = {0, 0, 0}, k[3] = {0, 0, 0}, v[3] = {0, 0, 0}; bool remote_x = false; };
-    std::vector<peer_info> pi((size_t) n_phases);
-    std::vector<char> consumed((size_t) n_phases, 0);
+    uintptr_t a0 = 0, a1 = 0, act1 = 0;
     if (pg) {
         if (pg->n_ranks < 1 || pg->n_ranks > B200_MAX_RANKS || pg->rank < 0 || pg->rank >= pg->n_ranks || pg->delta[pg->rank] != 0 ||
             pg->total_ctas < 1 || !pg->arena || !pg->sync) { set_error("b200_chain_create_peer: bad peer group"); return nullptr; }
-        const uintptr_t a0 = (uintptr_t) pg->arena, a1 = a0 + pg->arena_bytes, s0 = (uintptr_t) pg->sync;
+        a0 = (uintptr_t) pg->arena; a1 = a0 + pg->arena_bytes; const uintptr_t s0 = (uintptr_t) pg->sync;
         if (pg->act_bytes == 0 || pg->act_bytes % 16 || pg->ll_offset % 16 || pg->ll_offset < pg->act_bytes || pg->ll_offset + 2 * pg->act_bytes > pg->arena_bytes) {
             set_error("b200_chain_create_peer: bad arena layout (act_bytes / ll_offset)"); return nullptr;
         }
-        const uintptr_t act1 = a0 + pg->act_bytes;
+        act1 = a0 + pg->act_bytes;
         if (s0 < a0 || s0 + sizeof(unsigned int) * (size_t) n_phases > a1 || s0 % 4 ||
             (s0 < a0 + pg->ll_offset + 2 * pg->act_bytes && s0 + sizeof(unsigned int) * (size_t) n_phases > a0 + pg->ll_offset)) {
             set_error("b200_chain_create_peer: sync counters outside the arena (or inside the tagged shadow)"); return nullptr;
         }
         for (int i = 0; i < n_phases; ++i) {
-            const b200_phase & P = phv[i];
-            int lo, hi;
-            if (P.kind == B200_PHASE_GEMV) {
-                const b200_gemv_fused_args & g = P.gemv;
-                if (g.n_seg < 1 || g.n_seg > B200_GEMV_MAX_SEG) { set_error("b200_chain_create_peer: phase %d: bad segment count", i); return nullptr; }
-                for (int k = 0; k < g.n_seg; ++k) {
-                    if (!(g.glu_op != B200_GLU_NONE && k == 0)) {
-                        const uintptr_t d0 = (uintptr_t) g.seg[k].dst.data, d1 = d0 + 4 * (size_t) g.seg[k].w.ne[1];
-                        if (d0 < a0 || d1 > act1) { set_error("b200_chain_create_peer: phase %d segment %d: dst outside the symmetric arena", i, k); return nullptr; }
-                    }
-                    if (g.seg[k].bias) {       // epilogue operands are read as plain memory: they must be rows this rank wrote itself
-                        const int r = gs_find_producer(phv.data(), i, g.seg[k].bias->data, g.seg[k].w.ne[1], lo, hi);
-                        if (r == -2 || (r >= 0 && (lo != 0 || hi != (int) g.seg[k].w.ne[1]))) {
-                            set_error("b200_chain_create_peer: phase %d segment %d: bias rows were not computed by this rank", i, k); return nullptr;
-                        }
-                    }
-                }
-                const int64_t K = g.x.ne[0];
-                const int r = gs_find_producer(phv.data(), i, g.x.data, K, lo, hi);
-                if (r == -2) { set_error("b200_chain_create_peer: phase %d: activation overlaps earlier outputs irregularly", i); return nullptr; }
-                pi[i].x_lo = 0; pi[i].x_hi = (int) K;
-                if (r >= 0) {
-                    if (lo % 4 || hi % 4) { set_error("b200_chain_create_peer: phase %d: row slice not a multiple of 4", i); return nullptr; }
-                    pi[i].x_lo = lo; pi[i].x_hi = hi; pi[i].x_tag = r; consumed[r] = 1;
-                    if ((uintptr_t) g.x.data < a0 || (uintptr_t) g.x.data + 4 * (size_t) K > act1) { set_error("b200_chain_create_peer: phase %d: x outside the arena", i); return nullptr; }
-                }
-            } else if (P.kind == B200_PHASE_ATTN) {
-                const b200_attn_phase & a = P.attn;
-                const b200_tensor * t[3] = {&a.q, &a.k_new, &a.v_new};
-                int * out[3] = {pi[i].q, pi[i].k, pi[i].v};
-                for (int u = 0; u < 3; ++u) {
-                    const int64_t n = nelements(*t[u]);
-                    const int r = gs_find_producer(phv.data(), i, t[u]->data, n, lo, hi);
-                    if (r == -2) { set_error("b200_chain_create_peer: phase %d: q/k/v overlap earlier outputs irregularly", i); return nullptr; }
-                    out[u][0] = 0; out[u][1] = (int) n; out[u][2] = 0;
-                    if (r >= 0) {
-                        out[u][0] = lo; out[u][1] = hi; out[u][2] = r; consumed[r] = 1;
-                        if ((uintptr_t) t[u]->data < a0 || (uintptr_t) t[u]->data + 4 * (size_t) n > act1) { set_error("b200_chain_create_peer: phase %d: q/k/v outside the arena", i); return nullptr; }
-                    }
-                }
+            if (phv[i].kind != B200_PHASE_GEMV) continue;
+            const b200_gemv_fused_args & g = phv[i].gemv;
+            if (g.n_seg < 1 || g.n_seg > B200_GEMV_MAX_SEG) { set_error("b200_chain_create_peer: phase %d: bad segment count", i); return nullptr; }
+            for (int k = 0; k < g.n_seg; ++k) {
+                if (g.glu_op != B200_GLU_NONE && k == 0) continue;
+                const uintptr_t d0 = (uintptr_t) g.seg[k].dst.data, d1 = d0 + 4 * (size_t) g.seg[k].w.ne[1];
+                if (d0 < a0 || d1 > act1) { set_error("b200_chain_create_peer: phase %d segment %d: dst outside the symmetric arena", i, k); return nullptr; }
             }
         }
+    }
+    // ---- outputs (before empty slices are dropped: they still say which phase fills a range)
+    std::vector<gs_output> outs;
+    for (int i = 0; i < n_phases; ++i) {
+        if (phv[i].kind == B200_PHASE_GEMV) {
+            const b200_gemv_fused_args & g = phv[i].gemv;
+            for (int k = 0; k < g.n_seg && k < B200_GEMV_MAX_SEG; ++k) {
+                if (g.glu_op != B200_GLU_NONE && k == 0) continue;                 // the gate segment has no dst of its own
+                const char * d0 = (const char *) g.seg[k].dst.data;
+                if (d0) outs.push_back({d0, d0 + 4 * (size_t) std::max<int64_t>(g.seg[k].w.ne[1], 0), i, 0, nullptr, false});
+            }
+        } else if (phv[i].kind == B200_PHASE_ATTN) {
+            const b200_tensor & d = phv[i].attn.dst;
+            outs.push_back({(const char *) d.data, (const char *) d.data + 4 * (size_t) nelements(d), i, -1, nullptr, false});
+        }
+    }
+    if (pg) {
         // a rank may own no rows of a small matrix (split boundaries round down): the segment only described the slice
         for (int i = 0; i < n_phases; ++i) {
             if (phv[i].kind != B200_PHASE_GEMV) continue;
@@ -379,25 +349,68 @@ static b200_chain * gs_chain_create(const b200_phase * phases_in, int n_phases, 
         else if (phases[i].kind == B200_PHASE_NOP)  { memset(&ph[i], 0, sizeof(gs_phase)); ph[i].kind = 2; ok = true; }
         else ok = false;
         if (!ok) { set_error("b200_chain_create: phase %d is not supported", i); delete ch; return nullptr; }
-        ph[i].x_lo = 0; ph[i].x_hi = ph[i].K; ph[i].self_tag = (uint32_t) i;
-        gs_attn & g = ph[i].attn;
-        if (ph[i].kind == 1) { g.q_lo = g.k_lo = g.v_lo = 0; g.q_hi = g.D * g.H; g.k_hi = g.v_hi = g.D * g.H_kv; }
+        ph[i].self_tag = (uint32_t) i;
     }
+    // ---- outputs and their shadows.  Row split: the shadow of an arena address is arena-mapped (every rank's copy sits at the
+    // same offset, so a peer's copy is one delta away) and a consumer may read rows other ranks produced in the same phase of
+    // THEIR chain; everything else gets a private slot in this chain's own shadow pool.
+    size_t pool_words = 0;
+    auto in_arena = [&](const void * p, int64_t n) { return pg && (uintptr_t) p >= a0 && (uintptr_t) p + 4 * (size_t) n <= act1; };
+    auto arena_ll = [&](const void * p) { return (unsigned long long *) ((char *) pg->arena + pg->ll_offset + 2 * ((uintptr_t) p - a0)); };
+    for (gs_output & o : outs) {
+        const int64_t n = (o.p1 - o.p0) / 4;
+        if (in_arena(o.p0, n)) o.ll = arena_ll(o.p0);
+        else { o.ll = (unsigned long long *) (uintptr_t) (8 * pool_words + 8); pool_words += (size_t) ((n + 1) & ~(int64_t) 1); }     // offset + 8 for now (0 = none); 16 B aligned slots
+    }
+    // ---- inputs: x, epilogue operands, q / k / v
+    struct use { const void * ptr; int64_t n; const unsigned long long ** ll; uint32_t * tag; };
+    bool bad = false;
+    auto resolve = [&](int i, const void * ptr, int64_t n, const unsigned long long *& ll, uint32_t & tag, const char * what) {
+        ll = nullptr; tag = 0;
+        if (!ptr) return;
+        gs_output * o = gs_find_output(outs, i, ptr, n);
+        if (!o) return;                                            // plain memory written before the launch
+        const char * p0 = (const char *) ptr;
+        if (in_arena(ptr, n)) {
+            // row split: [ptr, ptr + n) may be the concatenation of every rank's slice of phase o->phase; all of it carries that tag
+            if (!in_arena(o->p0, (o->p1 - o->p0) / 4)) { set_error("b200_chain_create_peer: phase %d: %s mixes arena and private memory", i, what); bad = true; return; }
+            ll = arena_ll(ptr); tag = (uint32_t) o->phase; o->consumed = true;
+            // other outputs of the same phase that overlap the range are consumed too (q, k, v of one projection phase)
+            for (gs_output & q : outs) if (q.phase == o->phase && q.p0 < p0 + 4 * n && q.p1 > p0) q.consumed = true;
+            return;
+        }
+        if (p0 < o->p0 || p0 + 4 * n > o->p1) { set_error("b200_chain_create: phase %d: %s is only partly produced by phase %d", i, what, o->phase); bad = true; return; }
+        ll = (const unsigned long long *) ((uintptr_t) o->ll + 2 * (size_t) (p0 - o->p0));      // still pool-relative (+8)
+        tag = (uint32_t) o->phase; o->consumed = true;
+    };
+    for (int i = 0; i < n_phases && !bad; ++i) {
+        if (ph[i].kind == 0) {
+            resolve(i, ph[i].x, ph[i].K, ph[i].x_ll, ph[i].x_tag, "x");
+            // the prologue reads the shadow of x two words (16 bytes) at a time
+            const uintptr_t xa = (uintptr_t) ph[i].x_ll - (in_arena(ph[i].x, ph[i].K) ? 0 : 8);
+            if (ph[i].x_ll && xa % 16) { set_error("b200_chain_create: phase %d: x is not 8-byte aligned inside its producer's dst", i); bad = true; }
+            for (int s = 0; s < ph[i].n_ws && !bad; ++s) {
+                gs_seg & g = ph[i].seg[s];
+                resolve(i, g.bias, g.M, g.bias_ll, g.bias_tag, "bias");
+            }
+        } else if (ph[i].kind == 1) {
+            gs_attn & g = ph[i].attn;
+            resolve(i, g.q, (int64_t) g.D * g.H, g.q_ll, g.q_tag, "q");
+            resolve(i, g.k_new, (int64_t) g.D * g.H_kv, g.k_ll, g.k_tag, "k");
+            resolve(i, g.v_new, (int64_t) g.D * g.H_kv, g.v_ll, g.v_tag, "v");
+        }
+    }
+    if (bad) { delete ch; return nullptr; }
     int n_final = 0, final_phase[4] = {0, 0, 0, 0};
     if (pg) {
         for (int i = 0; i < n_phases; ++i) {
-            if (phases_in[i].kind == B200_PHASE_GEMV) {
-                ph[i].x_lo = pi[i].x_lo; ph[i].x_hi = pi[i].x_hi; ph[i].x_tag = (uint32_t) pi[i].x_tag;
-                ph[i].peer_mode = consumed[i] ? 1 : 2;
-                if (!consumed[i]) {
-                    if (n_final == 4) { set_error("b200_chain_create_peer: more than 4 phases whose outputs leave the chain"); delete ch; return nullptr; }
-                    final_phase[n_final++] = i;
-                }
-            } else if (ph[i].kind == 1) {
-                gs_attn & g = ph[i].attn;
-                g.q_lo = pi[i].q[0]; g.q_hi = pi[i].q[1]; g.q_tag = (uint32_t) pi[i].q[2];
-                g.k_lo = pi[i].k[0]; g.k_hi = pi[i].k[1]; g.k_tag = (uint32_t) pi[i].k[2];
-                g.v_lo = pi[i].v[0]; g.v_hi = pi[i].v[1]; g.v_tag = (uint32_t) pi[i].v[2];
+            if (ph[i].kind != 0) continue;
+            bool any = false;
+            for (gs_output & o : outs) if (o.phase == i && o.consumed) any = true;
+            ph[i].peer_mode = any ? 1 : 2;
+            if (!any) {
+                if (n_final == 4) { set_error("b200_chain_create_peer: more than 4 phases whose outputs leave the chain"); delete ch; return nullptr; }
+                final_phase[n_final++] = i;
             }
         }
     }
@@ -407,24 +420,66 @@ static b200_chain * gs_chain_create(const b200_phase * phases_in, int n_phases, 
         if (ph[i].kind == 0 && !gs_finish_phase(ph[i], cfg.stage_payload)) { set_error("b200_chain_create: phase %d: row does not fit a stage", i); delete ch; return nullptr; }
     cudaGetDevice(&ch->device);
     ch->peer = pg != nullptr;
+    const size_t pool_bytes = 8 * pool_words + 64;
     if (cudaMalloc((void **) &ch->d_phases, sizeof(gs_phase) * (size_t) n_phases) != cudaSuccess ||
-        cudaMalloc((void **) &ch->d_bar, sizeof(unsigned int) * (size_t) n_phases) != cudaSuccess ||
-        (pg && (cudaMalloc((void **) &ch->d_epoch, sizeof(unsigned int)) != cudaSuccess || cudaMemset(ch->d_epoch, 0, sizeof(unsigned int)) != cudaSuccess)) ||
-        cudaMemcpy(ch->d_phases, ph.data(), sizeof(gs_phase) * (size_t) n_phases, cudaMemcpyHostToDevice) != cudaSuccess) {
+        cudaMalloc((void **) &ch->d_ctl, 2 * sizeof(unsigned int)) != cudaSuccess || cudaMemset(ch->d_ctl, 0, 2 * sizeof(unsigned int)) != cudaSuccess ||
+        cudaMalloc((void **) &ch->d_shadow, pool_bytes) != cudaSuccess || cudaMemset(ch->d_shadow, 0, pool_bytes) != cudaSuccess) {
         set_error("b200_chain_create: device allocation failed"); cudaGetLastError();
-        if (ch->d_phases) cudaFree(ch->d_phases); if (ch->d_bar) cudaFree(ch->d_bar); if (ch->d_epoch) cudaFree(ch->d_epoch);
+        if (ch->d_phases) cudaFree(ch->d_phases); if (ch->d_ctl) cudaFree(ch->d_ctl); if (ch->d_shadow) cudaFree(ch->d_shadow);
         delete ch; return nullptr;
+    }
+    // pool-relative shadow addresses -> device addresses; outputs nobody reads get no shadow
+    auto fix = [&](const unsigned long long *& ll, const void * ptr, int64_t n) {
+        if (ll && !in_arena(ptr, n)) ll = (const unsigned long long *) ((char *) ch->d_shadow + ((uintptr_t) ll - 8));
+    };
+    for (gs_output & o : outs) {
+        unsigned long long * ll = nullptr;
+        if (o.consumed) ll = in_arena(o.p0, (o.p1 - o.p0) / 4) ? o.ll : (unsigned long long *) ((char *) ch->d_shadow + ((uintptr_t) o.ll - 8));
+        if (o.seg < 0) { ph[o.phase].attn.dst_ll = ll; continue; }
+        if (ph[o.phase].kind != 0) continue;                       // dropped: this rank owns no rows of it
+        for (int s2 = 0; s2 < ph[o.phase].n_ws; ++s2)
+            if ((const char *) ph[o.phase].seg[s2].dst == o.p0 && o.p1 > o.p0) ph[o.phase].seg[s2].dst_ll = ll;
+    }
+    for (int i = 0; i < n_phases; ++i) {
+        if (ph[i].kind == 0) {
+            fix(ph[i].x_ll, ph[i].x, ph[i].K);
+            for (int s = 0; s < ph[i].n_ws; ++s) fix(ph[i].seg[s].bias_ll, ph[i].seg[s].bias, ph[i].seg[s].M);
+        } else if (ph[i].kind == 1) {
+            gs_attn & g = ph[i].attn;
+            fix(g.q_ll, g.q, (int64_t) g.D * g.H); fix(g.k_ll, g.k_new, (int64_t) g.D * g.H_kv); fix(g.v_ll, g.v_new, (int64_t) g.D * g.H_kv);
+        }
+    }
+    // rows of every segment for every CTA: bytes of a phase are split evenly, a CTA takes the rows that START in its share
+    const int grid = gs_sm_count();
+    std::vector<int2> ranges((size_t) n_phases * grid * B200_GEMV_MAX_SEG, make_int2(0, 0));
+    for (int i = 0; i < n_phases; ++i) {
+        if (ph[i].kind != 0) continue;
+        for (int c = 0; c < grid; ++c) {
+            const int64_t lo = ph[i].total_bytes * (int64_t) c / grid, hi = ph[i].total_bytes * (int64_t) (c + 1) / grid;
+            for (int s2 = 0; s2 < ph[i].n_ws; ++s2) {
+                const gs_seg & g = ph[i].seg[s2];
+                const int64_t rbw = (int64_t) g.rb * g.nsub, tot = rbw * g.M;
+                const int64_t a = std::min(std::max(lo - g.byte_prefix, (int64_t) 0), tot), b = std::min(std::max(hi - g.byte_prefix, (int64_t) 0), tot);
+                ranges[((size_t) i * grid + c) * B200_GEMV_MAX_SEG + s2] = make_int2((int) ((a + rbw - 1) / rbw), (int) ((b + rbw - 1) / rbw));
+            }
+        }
+    }
+    if (cudaMalloc((void **) &ch->d_ranges, sizeof(int2) * ranges.size()) != cudaSuccess ||
+        cudaMemcpy(ch->d_ranges, ranges.data(), sizeof(int2) * ranges.size(), cudaMemcpyHostToDevice) != cudaSuccess ||
+        cudaMemcpy(ch->d_phases, ph.data(), sizeof(gs_phase) * (size_t) n_phases, cudaMemcpyHostToDevice) != cudaSuccess) {
+        set_error("b200_chain_create: descriptor upload failed"); cudaGetLastError();
+        cudaFree(ch->d_phases); cudaFree(ch->d_ctl); cudaFree(ch->d_shadow); if (ch->d_ranges) cudaFree(ch->d_ranges); delete ch; return nullptr;
     }
     memset(&ch->p, 0, sizeof(ch->p));
     if (pg) {
-        ch->p.epoch = ch->d_epoch; ch->p.total_ctas = pg->total_ctas; ch->p.sync = pg->sync;
-        ch->p.arena = (const char *) pg->arena; ch->p.ll_base = (char *) pg->arena + pg->ll_offset;
+        ch->p.total_ctas = pg->total_ctas; ch->p.sync = pg->sync;
         ch->p.n_final = n_final;
         for (int k = 0; k < 4; ++k) ch->p.final_phase[k] = final_phase[k];
         for (int r = 0; r < pg->n_ranks; ++r)
             if (r != pg->rank) ch->p.peer_delta[ch->p.n_peers++] = pg->delta[r];
     }
-    ch->p.phases = ch->d_phases; ch->p.bar = ch->d_bar; ch->p.n_phases = n_phases;
+    ch->p.epoch = ch->d_ctl; ch->p.exit_count = ch->d_ctl + 1;
+    ch->p.phases = ch->d_phases; ch->p.n_phases = n_phases; ch->p.ranges = ch->d_ranges;
     ch->p.act_qs_bytes = cfg.act_qs; ch->p.stage_stride = cfg.stage_payload + GS_STAGE_SLACK; ch->p.n_stages = cfg.n_stages;
     ch->p.attn_floats = cfg.attn_floats; ch->p.flags = flags;
     if (flags & 4) {
@@ -432,7 +487,7 @@ static b200_chain * gs_chain_create(const b200_phase * phases_in, int n_phases, 
             cudaMemset(ch->d_dbg, 0, sizeof(unsigned long long) * 16 * (size_t) n_phases);
         ch->p.dbg = ch->d_dbg;
     }
-    ch->smem = cfg.smem; ch->grid = gs_sm_count(); ch->t0 = types[0]; ch->t1 = types[1];
+    ch->smem = cfg.smem; ch->grid = grid; ch->t0 = types[0]; ch->t1 = types[1];
     return ch;
 }
 
@@ -472,7 +527,6 @@ extern "C" int b200_peer_close(void * ptr) { B200_CUDA_TRY(cudaIpcCloseMemHandle
 extern "C" int b200_chain_launch(b200_chain * ch, void * stream) {
     if (!ch) return B200_ERR_ARG;
     cudaStream_t st = (cudaStream_t) stream;
-    B200_CUDA_TRY(cudaMemsetAsync(ch->d_bar, 0, sizeof(unsigned int) * (size_t) ch->p.n_phases, st));
     if (ch->peer) {
         // the arrivals of the other ranks for THIS launch cannot come before they have consumed rows this launch produces,
         // and those of the previous launch were all counted before it ended: resetting here does not race with them
@@ -491,6 +545,6 @@ extern "C" int b200_chain_debug_read(b200_chain * ch, unsigned long long * out, 
 
 extern "C" void b200_chain_destroy(b200_chain * ch) {
     if (!ch) return;
-    cudaFree(ch->d_phases); cudaFree(ch->d_bar); if (ch->d_dbg) cudaFree(ch->d_dbg); if (ch->d_epoch) cudaFree(ch->d_epoch);
+    cudaFree(ch->d_phases); cudaFree(ch->d_ctl); cudaFree(ch->d_shadow); cudaFree(ch->d_ranges); if (ch->d_dbg) cudaFree(ch->d_dbg);
     delete ch;
 }

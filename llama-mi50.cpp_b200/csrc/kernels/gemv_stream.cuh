@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cstring>
 #include <mutex>
+#include <type_traits>
 #include <vector>
 
 #include "quantize.cuh"
@@ -31,14 +32,20 @@ constexpr int GS_SMEM_MAX    = 220 * 1024;             // dynamic; ~3 KB of stat
 constexpr int GS_RB          = 2;                      // rows per warp pass (two independent dp4a chains)
 constexpr int GS_MAX_PHASES  = 1024;
 
+// Inside a chain every value a later phase reads travels as a TAGGED WORD {f32 bits, tag of (launch, producing phase)} in a
+// shadow array (`*_ll`): the reader spins on the tag, so a phase starts as soon as ITS inputs exist — no grid barrier, no
+// fence (a device-scope release on B200 waits for everything the SM has in flight, including the bulk copies of the next
+// phase's weights).  Null `*_ll`: plain memory written before the launch (graph inputs, weights' biases).
 struct gs_seg {
     const uint8_t * w[2];     // [1] = paired "up" matrix of a GLU work segment (else null)
     const float *   bias;
     float *         dst;
+    unsigned long long * dst_ll;         // tagged shadow of dst (null: nothing in the chain reads it)
+    const unsigned long long * bias_ll;  // tagged shadow of bias when an earlier phase of the chain produced it
     int64_t         byte_prefix;   // bytes of the work segments before this one
     int32_t M, rb, type, nsub;     // rows, row bytes, ggml type, 1 (or 2 for a GLU pair)
     int32_t R, KS, spr, ipr;       // rows per chunk, warps along K, steps per row, items per row
-    int32_t spw, _pad;             // K-steps per warp (1, 2 or 4): the per-step activation registers are hoisted
+    int32_t spw; uint32_t bias_tag;   // K-steps per warp (1, 2 or 4): the per-step activation registers are hoisted; phase that produced bias
 };
 // attention phase of the decode chain: one query position, f16 KV cache, RoPE + KV-cache write fused in
 struct gs_attn {
@@ -48,10 +55,10 @@ struct gs_attn {
     int64_t k_nb1, k_nb2, v_nb1, v_nb2;
     int32_t D, H, H_kv, n_kv, rope_mode, n_dims;
     float scale, theta_scale, freq_scale;
-    // row split: elements [lo, hi) of q / k_new / v_new were computed by this rank (plain memory, after the local
-    // barrier); the rest arrives from the other ranks as tagged words.  *_tag: index of the producing phase
-    int32_t q_lo, q_hi, k_lo, k_hi, v_lo, v_hi;
-    uint32_t q_tag, k_tag, v_tag;
+    // tagged shadows of q / k_new / v_new (null: plain) and the index of the phase that produced them; shadow of dst
+    const unsigned long long * q_ll; const unsigned long long * k_ll; const unsigned long long * v_ll;
+    unsigned long long * dst_ll;
+    uint32_t q_tag, k_tag, v_tag, _pad;
 };
 struct alignas(16) gs_phase {
     int32_t kind;                  // 0 = GEMV, 1 = attention
@@ -61,17 +68,19 @@ struct alignas(16) gs_phase {
     const float * x; const float * norm_w; float eps; int32_t K;
     blk_q8_1 * xq_out;
     int64_t total_bytes;
-    // row split: x[x_lo, x_hi) is local, the rest are tagged words written by the other ranks in phase x_tag.
-    // peer_mode: how this phase's outputs reach the other ranks: 0 not at all, 1 tagged words (read by a later phase),
-    // 2 plain stores + system-scope arrival (read after the launch: the logits)
-    int32_t x_lo, x_hi; uint32_t x_tag; int32_t peer_mode;
+    // x_ll: tagged shadow of x written in phase x_tag (null: x is plain memory written before the launch).
+    // peer_mode (row split): how this phase's outputs reach the other ranks: 0 not at all, 1 tagged words (read by a later
+    // phase), 2 plain stores + system-scope arrival (read after the launch: the logits)
+    const unsigned long long * x_ll; uint32_t x_tag; int32_t peer_mode;
     uint32_t self_tag; int32_t _pad2[3];      // index of this phase (added to the launch tag for its own tagged stores)
     gs_attn attn;
 };
 struct gs_params {
     gs_phase inl;                  // the phase of a single-phase launch (b200_gemv_fused)
     const gs_phase * phases;       // device array for a chain (null: use inl)
-    unsigned int * bar;            // one arrival counter per phase (zeroed before the launch)
+    unsigned int * exit_count;     // chain: CTAs that have finished the launch (the last one counts the launch in `epoch`)
+    const int2 * ranges;           // chain: rows [x, y) of segment s of phase i for CTA c at [(i * grid + c) * B200_GEMV_MAX_SEG + s]
+                                   // (computed on the host: 64-bit divisions in every thread of every phase were 5 % of the launch)
     int32_t n_phases;
     int32_t act_qs_bytes;          // activation region sized for the largest K of the chain
     int32_t stage_stride;          // bytes between ring stages (payload + GS_STAGE_SLACK, multiple of 128)
@@ -83,10 +92,8 @@ struct gs_params {
     int32_t n_peers;               // other ranks
     int32_t total_ctas;            // CTAs of all ranks: arrivals per phase and launch
     int64_t peer_delta[B200_MAX_RANKS - 1];   // byte offset from a local arena address to the same location on peer r
-    unsigned int * epoch;          // launches completed so far on this rank: tags of different launches differ
+    unsigned int * epoch;          // chain: launches completed so far: tags of different launches differ
     unsigned int * sync;           // arena: arrival counters of the peer_mode 2 phases (all ranks' CTAs)
-    const char * arena;            // local arena base and its shadow of tagged words: the word of the f32 at arena + o
-    char * ll_base;                //   is at ll_base + 2 * o
     int32_t n_final; int32_t final_phase[4];   // peer_mode 2 phases the launch waits for before it ends
 };
 
@@ -124,18 +131,25 @@ __device__ __forceinline__ void named_bar_sync(int id, int n) { asm volatile("ba
 // ---- tagged words (row split over peer memory): a value and the tag of the (launch, phase) that produced it travel in
 // ONE 64-bit store, so a reader that sees the tag has the value: one NVLink traversal, no fence round trip, no counter
 // (the idea of NCCL's LL protocol).  Spins are bounded: a rank that never delivers becomes a trap, not a hung GPU.
+// SYS: system scope (the word crosses NVLink to / from another GPU); else device scope (L2 of this GPU)
+template <bool SYS>
 __device__ __forceinline__ void ll_store(void * p, float v, unsigned int tag) {
     const unsigned long long w = (unsigned long long) __float_as_uint(v) | ((unsigned long long) tag << 32);
-    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
+    if (SYS) asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
+    else     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
 }
+template <bool SYS>
 __device__ __forceinline__ unsigned long long ll_load1(const void * p) {
     unsigned long long w;
-    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+    if (SYS) asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+    else     asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
     return w;
 }
+template <bool SYS>
 __device__ __forceinline__ ulonglong2 ll_load2(const void * p) {      // two elements, 16 B aligned
     ulonglong2 r;
-    asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(r.x), "=l"(r.y) : "l"(p) : "memory");
+    if (SYS) asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(r.x), "=l"(r.y) : "l"(p) : "memory");
+    else     asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(r.x), "=l"(r.y) : "l"(p) : "memory");
     return r;
 }
 __device__ __forceinline__ bool ll_ok(unsigned long long w, unsigned int tag) { return (unsigned int) (w >> 32) == tag; }
@@ -146,15 +160,25 @@ __device__ __forceinline__ void ll_spin_check(unsigned int & spins, unsigned lon
         if (!t0) t0 = now; else if (now - t0 > 20000000000ull) __trap();          // 20 s
     }
 }
-__device__ __forceinline__ float ll_read(const void * p, unsigned int tag) {
-    unsigned long long w = ll_load1(p);
+template <bool SYS>
+__device__ __forceinline__ float ll_settle1(unsigned long long w, const void * p, unsigned int tag) {
     unsigned int spins = 0; unsigned long long t0 = 0;
-    while (!ll_ok(w, tag)) { ll_spin_check(spins, t0); w = ll_load1(p); }
+    while (!ll_ok(w, tag)) { ll_spin_check(spins, t0); w = ll_load1<SYS>(p); }
     return __uint_as_float((unsigned int) w);
 }
+template <bool SYS>
+__device__ __forceinline__ float ll_read(const void * p, unsigned int tag) { return ll_settle1<SYS>(ll_load1<SYS>(p), p, tag); }
+template <bool SYS>
 __device__ __forceinline__ void ll_settle2(ulonglong2 & a, const void * p, unsigned int tag) {
     unsigned int spins = 0; unsigned long long t0 = 0;
-    while (!ll_ok(a.x, tag) || !ll_ok(a.y, tag)) { ll_spin_check(spins, t0); a = ll_load2(p); }
+    while (!ll_ok(a.x, tag) || !ll_ok(a.y, tag)) { ll_spin_check(spins, t0); a = ll_load2<SYS>(p); }
+}
+// one lane waits (with back-off) until the word at p carries `tag`: the gate in front of a many-thread read, so that CTAs
+// waiting for a phase to finish do not flood L2 with retries
+template <bool SYS>
+__device__ __forceinline__ void ll_gate(const void * p, unsigned int tag) {
+    unsigned int spins = 0; unsigned long long t0 = 0;
+    while (!ll_ok(ll_load1<SYS>(p), tag)) { ll_spin_check(spins, t0); __nanosleep(100); }
 }
 
 // N consecutive little-endian u32 words starting at an arbitrarily aligned shared-memory byte address
@@ -387,6 +411,12 @@ __device__ __forceinline__ float gs_glu(int op, float g, float x, float alpha, f
     }
 }
 
+__device__ __forceinline__ unsigned long long gs_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 // ring position carried by the producer and the consumers across the segments and phases of a launch
 struct gs_pos {
     int st = 0, full_par = 0;      // ring stage, parity of its "full" phase
@@ -406,125 +436,160 @@ struct gs_ctx {                    // per-thread view of the launch-wide shared 
     int stage_stride, flags;
 };
 
+__device__ __forceinline__ unsigned int sh_tag_of(const gs_ctx & c) { return c.sh->tag; }
+
 __device__ __forceinline__ void gs_row_range(const gs_seg & sg, int64_t lo, int64_t hi, int & r0, int & r1) {
     const int64_t rbw = (int64_t) sg.rb * sg.nsub, tot = rbw * sg.M;
     const int64_t a = min(max(lo - sg.byte_prefix, (int64_t) 0), tot), b = min(max(hi - sg.byte_prefix, (int64_t) 0), tot);
     r0 = (int) ((a + rbw - 1) / rbw); r1 = (int) ((b + rbw - 1) / rbw);
 }
 
+// rows of every segment of a staged phase for this CTA -> rng[0..n_ws): from the host's table (chain) or computed by one lane each
+__device__ __forceinline__ void gs_stage_ranges(int2 * rng, const gs_phase * buf, const int2 * table, int ip, int cta, int n_cta, int t) {
+    if (t >= B200_GEMV_MAX_SEG) return;
+    if (table) { rng[t] = table[((int64_t) ip * n_cta + cta) * B200_GEMV_MAX_SEG + t]; return; }
+    int r0 = 0, r1 = 0;
+    if (buf->kind == 0 && t < buf->n_ws) {
+        const int64_t lo = buf->total_bytes * (int64_t) cta / n_cta, hi = buf->total_bytes * (int64_t) (cta + 1) / n_cta;
+        gs_row_range(buf->seg[t], lo, hi, r0, r1);
+    }
+    rng[t] = make_int2(r0, r1);
+}
+
 // warp-uniform walk over the weight chunks of ONE CTA through every GEMV phase of a launch, in consumption order
-struct gs_walk { int ip = -1, s = 0, row = 0, r1 = 0; int64_t lo = 0, hi = 0; };
-// moves w to its next chunk (rows [row, min(row + R, r1)) of segment s of phase ip); the descriptor of a phase is staged
-// into *buf by the whole warp when the walk enters it.  The caller steps `row` by the segment's R.  false: no chunk left
-__device__ __forceinline__ bool gs_walk_next(gs_walk & w, gs_phase * buf, const gs_phase * phases, int n_phases, int cta, int n_cta, int lane) {
+struct gs_walk { int ip = -1, s = 0, row = 0, r1 = 0; };
+// moves w to its next chunk (rows [row, min(row + R, r1)) of segment s of phase ip); the descriptor of a phase and this CTA's
+// row ranges are staged into *buf / rng by the whole warp when the walk enters it.  The caller steps `row` by the segment's R.
+// false: no chunk left
+__device__ __forceinline__ bool gs_walk_next(gs_walk & w, gs_phase * buf, int2 * rng, const gs_phase * phases, const int2 * table, int n_phases, int cta, int n_cta, int lane) {
     for (;;) {
         if (w.row < w.r1) return true;
-        if (w.ip >= 0 && buf->kind == 0 && ++w.s < buf->n_ws) { gs_row_range(buf->seg[w.s], w.lo, w.hi, w.row, w.r1); continue; }
+        if (w.ip >= 0 && buf->kind == 0 && ++w.s < buf->n_ws) { w.row = rng[w.s].x; w.r1 = rng[w.s].y; continue; }
         if (++w.ip >= n_phases) return false;
         __syncwarp();
         for (int i = lane; i < (int) (sizeof(gs_phase) / 16); i += 32) ((uint4 *) buf)[i] = ((const uint4 *) (phases + w.ip))[i];
         __syncwarp();
+        gs_stage_ranges(rng, buf, table, w.ip, cta, n_cta, lane);
+        __syncwarp();
         w.s = -1; w.row = w.r1 = 0;
-        w.lo = buf->total_bytes * (int64_t) cta / n_cta; w.hi = buf->total_bytes * (int64_t) (cta + 1) / n_cta;
     }
 }
+
+__device__ __forceinline__ int wt_first_row(const gs_walk & w, const gs_phase &) { return w.row; }      // (debug hook: every chunk qualifies; the stamp keeps the first)
 
 // consumer warps: all chunks of one work segment.  A pass of a warp covers GS_RB rows (for a GLU pair: the gate row and the
 // up row of ONE output row); the KS warps of a row group each own a K slice, reduce their lanes by shuffles and meet at a
 // named barrier of their own; warp ks == 0 sums the KS values in fixed order, applies the epilogue and stores.
 // one output value: the local store and, under row split, the same store into every peer's copy of the buffer
-template <bool PEER>
-__device__ __forceinline__ void gs_put(const gs_params & p, const gs_phase & ph, const gs_shared & sh, float * d, float v) {
+template <bool CHAIN, bool PEER>
+__device__ __forceinline__ void gs_put(const gs_params & p, const gs_phase & ph, const gs_shared & sh, float * d, unsigned long long * ll, float v) {
     *d = v;
-    if (PEER) {
-        if (ph.peer_mode == 1) {
-            char * l = p.ll_base + 2 * ((const char *) d - p.arena);
-            const unsigned int tag = sh.tag + ph.self_tag;
+    if (CHAIN && ll) {                                   // the value a later phase waits for
+        const unsigned int tag = sh.tag + ph.self_tag;
+        ll_store<PEER>(ll, v, tag);
+        if (PEER && ph.peer_mode == 1) {
 #pragma unroll
             for (int r = 0; r < B200_MAX_RANKS - 1; ++r)
-                if (r < p.n_peers) ll_store(l + p.peer_delta[r], v, tag);
-        } else if (ph.peer_mode == 2) {
-#pragma unroll
-            for (int r = 0; r < B200_MAX_RANKS - 1; ++r)
-                if (r < p.n_peers) *(float *) ((char *) d + p.peer_delta[r]) = v;
+                if (r < p.n_peers) ll_store<true>((char *) ll + p.peer_delta[r], v, tag);
         }
+    }
+    if (PEER && ph.peer_mode == 2) {
+#pragma unroll
+        for (int r = 0; r < B200_MAX_RANKS - 1; ++r)
+            if (r < p.n_peers) *(float *) ((char *) d + p.peer_delta[r]) = v;
     }
 }
 
+// Rows of a chunk are dealt round-robin to the RG row groups (a row group = the KS warps that share a row), starting one
+// group further every chunk, so short chunks (4-6 rows of a K = 14336 matrix) keep every warp busy.  A pass of a warp covers
+// up to GS_RB = 2 rows of its group (for a GLU pair: the gate row and the up row of ONE output row).  The two row sums are
+// reduced TOGETHER: after the first exchange lane parity selects the row, so 5 shuffles serve both rows and the totals land
+// in lanes 0 and 1, which then run the epilogue of "their" row.
 template <int TYPE, int SPW, bool COHERENT, bool PEER>
 __device__ __forceinline__ void consume_segment(const gs_params & p, const gs_ctx & c, const gs_phase & ph, const gs_seg & sg, int r0, int r1, gs_pos & pos, int warp, int lane) {
+    static_assert(GS_RB == 2, "the paired reduction below is written for two rows per pass");
     const int KS = sg.KS, ksl = 31 - __clz(KS), ks = warp & (KS - 1), rg = warp >> ksl, RG = GS_NW >> ksl;
     item<TYPE> itm[SPW];
 #pragma unroll
     for (int s = 0; s < SPW; ++s) itm[s].init((ks + s * KS) * 32 + lane, sg.ipr, c.aq, c.ads);
     const int rb = sg.rb, R = sg.R;
     const bool pair = sg.nsub == 2;
-    const int rpp = pair ? 1 : (R >= GS_RB ? GS_RB : 1);   // output rows per warp pass
-    const int RGP = RG * rpp;                              // output rows per CTA pass
-    int off = 0;                                           // (row - r0) mod RGP: row groups rotate through the chunks, so a
-                                                           // chunk shorter than a CTA pass does not leave the same warps idle
-    const float * __restrict__ bias = sg.bias;
-    float * __restrict__ dst = sg.dst;
-    const int glu_op = ph.glu_op; const float glu_alpha = ph.glu_alpha, glu_limit = ph.glu_limit;
+    int off = 0;                                           // row group that gets the first row of the current chunk
     uint32_t ga0 = (uint32_t) ((uintptr_t) (sg.w[0] + (int64_t) r0 * rb) & 15);
     uint32_t ga1 = pair ? (uint32_t) ((uintptr_t) (sg.w[1] + (int64_t) r0 * rb) & 15) : 0u;
     const uint32_t gstep = (uint32_t) R * (uint32_t) rb;
     gs_shared & sh = *c.sh;
+    const volatile gs_seg & vs = sg;                       // epilogue fields are re-read where they are used (two lanes per pass):
+                                                           // hoisted into registers they cost more in the dot-product loops
+    const bool epi = ks == 0 && lane < GS_RB;
     int par = 0;
     for (int row = r0; row < r1; row += R) {
         const int nr = min(R, r1 - row);
         const uint8_t * sub0 = c.ring + pos.st * c.stage_stride + ga0;
         const uint8_t * sub1 = sub0 - ga0 + ((ga0 + (uint32_t) nr * rb + 15u) & ~15u) + ga1;
+        if ((c.flags & 4) && warp == 0 && lane == 0 && p.dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) {
+            // debug: time warp 0 spends waiting for weight bytes, and the chunks it saw ([3] ns, [4] chunks)
+            const unsigned long long t0 = gs_now();
+            mbar_wait(&sh.full[pos.st], pos.full_par);
+            unsigned long long * dd = p.dbg + (ph.self_tag * 2 + (blockIdx.x ? 1 : 0)) * 8;
+            dd[3] += gs_now() - t0; dd[4] += 1;
+        } else
         mbar_wait(&sh.full[pos.st], pos.full_par);
-        int jb0 = rg * rpp - off; if (jb0 < 0) jb0 += RGP;
-        off += R; while (off >= RGP) off -= RGP;
-        for (int jb = jb0; jb < nr; jb += RGP) {
+        // passes of this chunk ((gate, up) of one output row, or two consecutive plain rows) are dealt round-robin to the row
+        // groups, starting one group further every chunk
+        const int npass = pair ? nr : (nr + 1) >> 1;
+        int first = rg - off; if (first < 0) first += RG;
+        off += npass; while (off >= RG) off -= RG;
+        for (int q = first; q < npass; q += RG) {
+            // rows of this pass; an odd last row is computed alone (the kernel is issue-bound: a duplicate row computed and
+            // dropped costs what a real one does)
+            const int jb = pair ? q : 2 * q;
+            const int j1 = pair ? jb : (jb + 1 < nr ? jb + 1 : jb);
+            const bool two = pair || j1 != jb;             // warp-uniform
             const uint8_t * rowp[GS_RB];
-            if (pair) { rowp[0] = sub0 + jb * rb; rowp[1] = sub1 + jb * rb; }
-            else {
-#pragma unroll
-                for (int j = 0; j < GS_RB; ++j) rowp[j] = sub0 + min(jb + j, nr - 1) * rb;     // clamp: a duplicate row is computed and dropped
+            rowp[0] = sub0 + jb * rb; rowp[1] = (pair ? sub1 : sub0) + j1 * rb;
+            const int my = lane == 0 ? jb : j1;            // the row whose epilogue this lane runs
+            const bool live = epi && (lane == 0 || (!pair && j1 != jb));
+            float bv = 0.0f; unsigned long long bw = 0ull;      // epilogue operand, requested before the dot products
+            if (live && vs.bias) {
+                if (COHERENT && vs.bias_ll) bw = ll_load1<PEER>((const unsigned long long *) vs.bias_ll + row + my);
+                else bv = COHERENT ? __ldcg((const float *) vs.bias + row + my) : ((const float *) vs.bias)[row + my];
             }
-            float bv[GS_RB];                               // epilogue operand, requested before the dot products
-#pragma unroll
-            for (int j = 0; j < GS_RB; ++j) {
-                bv[j] = 0.0f;
-                if (bias && ks == 0 && lane == 0 && j < rpp && jb + j < nr) bv[j] = COHERENT ? __ldcg(bias + row + jb + j) : bias[row + jb + j];
-            }
-            float acc[GS_RB];
-#pragma unroll
-            for (int j = 0; j < GS_RB; ++j) acc[j] = 0.0f;
+            float acc[GS_RB] = {0.0f, 0.0f};
             if (!(c.flags & 1)) {
+                if (two) {
 #pragma unroll
-                for (int s = 0; s < SPW; ++s)
-                    if (itm[s].ok) itm[s].template dot<GS_RB>(rowp, acc);
-            }
+                    for (int s = 0; s < SPW; ++s)
+                        if (itm[s].ok) itm[s].template dot<GS_RB>(rowp, acc);
+                } else {
 #pragma unroll
-            for (int j = 0; j < GS_RB; ++j) acc[j] = warp_sum(acc[j]);
-            if (KS > 1) {
-                if (lane == 0) {
-#pragma unroll
-                    for (int j = 0; j < GS_RB; ++j) sh.slots[par][warp][j] = acc[j];
+                    for (int s = 0; s < SPW; ++s)
+                        if (itm[s].ok) itm[s].template dot<1>(rowp, acc);
                 }
-                named_bar_sync(4 + rg, KS * 32);
-                if (ks == 0 && lane == 0) {
+            }
+            // paired reduction: even lanes end with the total of row 0, odd lanes with the total of row 1
+            float v = (lane & 1) ? acc[1] : acc[0];
+            v += __shfl_xor_sync(0xffffffffu, (lane & 1) ? acc[0] : acc[1], 1);
 #pragma unroll
-                    for (int j = 0; j < GS_RB; ++j) {
-                        float t = 0.0f;
-                        for (int k = 0; k < KS; ++k) t += sh.slots[par][warp + k][j];
-                        acc[j] = t;
-                    }
+            for (int o = 2; o < 32; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (KS > 1) {
+                if (lane < GS_RB) sh.slots[par][warp][lane] = v;
+                named_bar_sync(4 + rg, KS * 32);
+                if (epi) {
+                    float t = 0.0f;
+                    for (int k = 0; k < KS; ++k) t += sh.slots[par][warp + k][lane];
+                    v = t;
                 }
                 par ^= 1;
             }
-            if (ks == 0 && lane == 0) {
-                if (pair) {
-                    gs_put<PEER>(p, ph, sh, dst + row + jb, gs_glu(glu_op, acc[0], acc[1], glu_alpha, glu_limit) + bv[0]);
-                } else {
-#pragma unroll
-                    for (int j = 0; j < GS_RB; ++j)
-                        if (j < rpp && jb + j < nr) gs_put<PEER>(p, ph, sh, dst + row + jb + j, acc[j] + bv[j]);
-                }
+            if (pair) {                                    // lane 0: gate total, lane 1: up total
+                const float up = __shfl_sync(0xffffffffu, v, 1);
+                if (live) v = gs_glu(ph.glu_op, v, up, ph.glu_alpha, ph.glu_limit);
+            }
+            if (live) {
+                if (COHERENT && vs.bias && vs.bias_ll) bv = ll_settle1<PEER>(bw, (const unsigned long long *) vs.bias_ll + row + my, sh.tag + vs.bias_tag);
+                unsigned long long * dll = COHERENT ? (unsigned long long *) vs.dst_ll : nullptr;
+                gs_put<COHERENT, PEER>(p, ph, sh, (float *) vs.dst + row + my, dll ? dll + row + my : nullptr, v + bv);
             }
         }
         __syncwarp();
@@ -542,11 +607,6 @@ __device__ __forceinline__ void consume_dispatch(const gs_params & p, const gs_c
         consume_segment<TYPE, (item<TYPE>::max_spw >= 4 ? 4 : 1), COHERENT, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
 }
 
-__device__ __forceinline__ unsigned long long gs_now() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
 #define GS_STAMP(ip, k) do { if (p.dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) \
     p.dbg[((ip) * 2 + (blockIdx.x ? 1 : 0)) * 8 + (k)] = gs_now(); } while (0)
 #define GS_STAMP_MAX(ip, k) do { if (p.dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) \
@@ -559,136 +619,129 @@ template <bool COHERENT>
 __device__ __forceinline__ float4 gs_ld4(const float * p) {
     return COHERENT ? __ldcg((const float4 *) p) : *(const float4 *) p;
 }
-// four consecutive elements of a row-split activation that another rank computed: spin on their tags
-__device__ __forceinline__ float4 ll_read4(const char * l, unsigned int tag) {
-    ulonglong2 a = ll_load2(l), b = ll_load2(l + 16);
-    ll_settle2(a, l, tag); ll_settle2(b, l + 16, tag);
-    return make_float4(__uint_as_float((unsigned int) a.x), __uint_as_float((unsigned int) a.y),
-                       __uint_as_float((unsigned int) b.x), __uint_as_float((unsigned int) b.y));
+// eight consecutive elements of an activation an earlier phase produced
+template <bool SYS>
+__device__ __forceinline__ void ll_read8(const unsigned long long * l, unsigned int tag, float * out) {
+    ulonglong2 a[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) a[i] = ll_load2<SYS>(l + 2 * i);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        ll_settle2<SYS>(a[i], l + 2 * i, tag);
+        out[2 * i] = __uint_as_float((unsigned int) a[i].x); out[2 * i + 1] = __uint_as_float((unsigned int) a[i].y);
+    }
 }
+// Prologue of a GEMV phase: x -> [rms norm * w] -> q8_1 in shared memory, arithmetic of quantize_row_q8_1_ref
+// (ggml-quants.c:225-258).  Four lanes own a 32-element block, eight consecutive elements per lane: K = 4096 is ONE pass of
+// the 512 prologue threads (every CTA repeats this work for every phase: it was a fifth of the launch's instructions).
 template <bool COHERENT, bool PEER>
 __device__ __forceinline__ void gs_prologue(const gs_params & p, const gs_ctx & c, const gs_phase & ph, int warp, int lane) {
     const int K = ph.K, nblk = K >> 5;
-    // row split: elements outside [x_lo, x_hi) come from the other ranks as tagged words
-    const bool has_remote = PEER && (ph.x_lo > 0 || ph.x_hi < K);
-    const char * xl = PEER ? p.ll_base + 2 * ((const char *) ph.x - p.arena) : nullptr;
-    const unsigned int xtag = PEER ? c.sh->tag + ph.x_tag : 0u;
-    auto remote = [&](int e) { return has_remote && (e < ph.x_lo || e >= ph.x_hi); };
+    // inside a chain x is normally the output of an earlier phase: tagged words, each thread spins on the ones it needs
+    const unsigned long long * xl = COHERENT ? ph.x_ll : nullptr;
+    const unsigned int xtag = COHERENT ? c.sh->tag + ph.x_tag : 0u;
     const float * __restrict__ x = ph.x;
     const float * __restrict__ nw = ph.norm_w;
     blk_q8_1 * xq_out = blockIdx.x == 0 ? ph.xq_out : nullptr;
-    const int pw = warp;                                        // prologue warps = the consumer warps
     gs_shared & sh = *c.sh;
-    const int sub = lane & 7, bw = lane >> 3;                   // 8 lanes per 32-element block, 4 blocks per warp pass
-    constexpr int BPP = GS_NW * 4;                              // blocks per pass of the prologue warps
-    constexpr int NV = 8;                                       // passes whose x values stay in registers
+    const int sub = lane & 3, bw = lane >> 2;                   // 4 lanes per 32-element block, 8 blocks per warp pass
+    constexpr int BPP = GS_NW * 8;                              // blocks per pass of the prologue warps
 
-    auto quant_store = [&](int blk, bool act, float4 t, float4 w, float scale) {
-        float v[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-        if (act) {
-            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-            if (nw) {                                           // same op order as rms_norm then mul: (x*scale)*w
-                v[0] = __fmul_rn(__fmul_rn(v[0], scale), w.x); v[1] = __fmul_rn(__fmul_rn(v[1], scale), w.y);
-                v[2] = __fmul_rn(__fmul_rn(v[2], scale), w.z); v[3] = __fmul_rn(__fmul_rn(v[3], scale), w.w);
-            }
+    auto load8 = [&](int e, float * v) {
+        if (xl) { ll_read8<PEER>(xl + e, xtag, v); return; }
+        const float4 a = gs_ld4<COHERENT>(x + e), b = gs_ld4<COHERENT>(x + e + 4);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    };
+    auto quant_store = [&](int blk, bool act, float * v, float scale) {
+        if (act && nw) {                                        // same op order as rms_norm then mul: (x*scale)*w
+            const float4 w0 = *(const float4 *) (nw + blk * 32 + sub * 8), w1 = *(const float4 *) (nw + blk * 32 + sub * 8 + 4);
+            v[0] = __fmul_rn(__fmul_rn(v[0], scale), w0.x); v[1] = __fmul_rn(__fmul_rn(v[1], scale), w0.y);
+            v[2] = __fmul_rn(__fmul_rn(v[2], scale), w0.z); v[3] = __fmul_rn(__fmul_rn(v[3], scale), w0.w);
+            v[4] = __fmul_rn(__fmul_rn(v[4], scale), w1.x); v[5] = __fmul_rn(__fmul_rn(v[5], scale), w1.y);
+            v[6] = __fmul_rn(__fmul_rn(v[6], scale), w1.z); v[7] = __fmul_rn(__fmul_rn(v[7], scale), w1.w);
         }
         float d; int sum;
-        const int q = quantize_block32_quad<8>(v, d, sum);
+        const int2 q = quantize_block32_oct(v, d, sum);
         if (act) {
-            *(int *) (c.aq + act_off(blk) + sub * 4) = q;
+            *(int2 *) (c.aq + act_off(blk) + sub * 8) = q;
             if (sub == 0) {
                 const float dh = __half2float(__float2half_rn(d));          // the value a q8_1 block stores
                 c.ads[blk] = make_float2(dh, dh * (float) sum);
             }
             if (xq_out) {
                 int * out = (int *) (xq_out + blk);
-                out[1 + sub] = q;
+                out[1 + 2 * sub] = q.x; out[2 + 2 * sub] = q.y;
                 if (sub == 0) *(__half2 *) out = q8_1_scales(d, sum);
             }
         }
     };
 
-    if (nblk <= BPP * NV) {
-        // ---- all loads first (one L2 round trip), values stay in registers for both passes
-        float4 xv[NV], wv[NV];
+    if (xl) {
+        // gate: one lane per warp waits (with back-off) for the first word this warp needs; the other 31 lanes and the
+        // CTAs that finished early add no traffic while a phase is still running
+        if (lane == 0 && warp * 8 < nblk) ll_gate<PEER>(xl + (warp * 8) * 32, xtag);
+        __syncwarp();
+    }
+    auto reg_path = [&](auto nv_tag) {
+        constexpr int NV = decltype(nv_tag)::value;             // passes (of BPP blocks) this row length needs: no predicated-off work
+        float xv[NV][8];
 #pragma unroll
         for (int it = 0; it < NV; ++it) {
-            const int blk = pw * 4 + bw + it * BPP;
-            xv[it] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); wv[it] = xv[it];
-            if (blk < nblk) {
-                if (!remote(blk * 32 + sub * 4)) xv[it] = gs_ld4<COHERENT>(x + blk * 32 + sub * 4);
-                if (nw) wv[it] = *(const float4 *) (nw + blk * 32 + sub * 4);
-            }
+            const int blk = warp * 8 + bw + it * BPP;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) xv[it][i] = 0.0f;
+            if (blk < nblk) load8(blk * 32 + sub * 8, xv[it]);
         }
-        if (has_remote) {
-#pragma unroll
-            for (int it0 = 0; it0 < NV; it0 += 2) {                        // two passes (four 16 B loads) in flight per thread
-                ulonglong2 a[2], b[2];
-#pragma unroll
-                for (int u = 0; u < 2; ++u) {
-                    const int e = (pw * 4 + bw + (it0 + u) * BPP) * 32 + sub * 4;
-                    a[u] = make_ulonglong2(0, 0); b[u] = a[u];
-                    if (e < K && remote(e)) { a[u] = ll_load2(xl + 8 * (int64_t) e); b[u] = ll_load2(xl + 8 * (int64_t) e + 16); }
-                }
-#pragma unroll
-                for (int u = 0; u < 2; ++u) {
-                    const int e = (pw * 4 + bw + (it0 + u) * BPP) * 32 + sub * 4;
-                    if (e < K && remote(e)) {
-                        ll_settle2(a[u], xl + 8 * (int64_t) e, xtag); ll_settle2(b[u], xl + 8 * (int64_t) e + 16, xtag);
-                        xv[it0 + u] = make_float4(__uint_as_float((unsigned int) a[u].x), __uint_as_float((unsigned int) a[u].y),
-                                                  __uint_as_float((unsigned int) b[u].x), __uint_as_float((unsigned int) b[u].y));
-                    }
-                }
-            }
-        }
+        if (COHERENT && warp == 0 && lane == 0) GS_STAMP(ph.self_tag, 5);
         float scale = 1.0f;
         if (nw) {
             float ss = 0.0f;
 #pragma unroll
-            for (int it = 0; it < NV; ++it) ss += xv[it].x * xv[it].x + xv[it].y * xv[it].y + xv[it].z * xv[it].z + xv[it].w * xv[it].w;
+            for (int it = 0; it < NV; ++it)
+#pragma unroll
+                for (int i = 0; i < 8; ++i) ss += xv[it][i] * xv[it][i];
             ss = warp_sum(ss);
-            if (lane == 0) sh.part[pw] = ss;
+            if (lane == 0) sh.part[warp] = ss;
             named_bar_sync(1, GS_PRO_THREADS);
             float tot = 0.0f;
 #pragma unroll
             for (int i = 0; i < GS_NW; ++i) tot += sh.part[i];
             scale = rsqrtf(tot / (float) K + ph.eps);
-            if (COHERENT && warp == 0 && lane == 0) GS_STAMP(ph.self_tag, 5);
         }
 #pragma unroll
         for (int it = 0; it < NV; ++it) {
-            const int b0 = pw * 4 + it * BPP;                   // warp-uniform
-            if (b0 < nblk) quant_store(b0 + bw, b0 + bw < nblk, xv[it], wv[it], scale);
+            const int b0 = warp * 8 + it * BPP;                 // warp-uniform
+            if (b0 < nblk) quant_store(b0 + bw, b0 + bw < nblk, xv[it], scale);
         }
         if (COHERENT && warp == 0 && lane == 0) GS_STAMP(ph.self_tag, 6);
-    } else {
+    };
+    if (nblk <= BPP)          reg_path(std::integral_constant<int, 1>{});
+    else if (nblk <= BPP * 2) reg_path(std::integral_constant<int, 2>{});
+    else if (nblk <= BPP * 4) reg_path(std::integral_constant<int, 4>{});
+    else {
         // ---- long rows: two passes over x
-        const int ptid = pw * 32 + lane;
         float scale = 1.0f;
         if (nw) {
             float ss = 0.0f;
-            for (int i = ptid * 4; i < K; i += GS_PRO_THREADS * 4) {
-                const float4 v = remote(i) ? ll_read4(xl + 8 * (int64_t) i, xtag) : gs_ld4<COHERENT>(x + i);
-                ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+            for (int b0 = warp * 8; b0 < nblk; b0 += BPP) {
+                float v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                if (b0 + bw < nblk) load8((b0 + bw) * 32 + sub * 8, v);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) ss += v[i] * v[i];
             }
             ss = warp_sum(ss);
-            if (lane == 0) sh.part[pw] = ss;
+            if (lane == 0) sh.part[warp] = ss;
             named_bar_sync(1, GS_PRO_THREADS);
             float tot = 0.0f;
 #pragma unroll
             for (int i = 0; i < GS_NW; ++i) tot += sh.part[i];
             scale = rsqrtf(tot / (float) K + ph.eps);
         }
-        for (int b0 = pw * 4; b0 < nblk; b0 += BPP) {
-            const int blk = b0 + bw;
-            const bool act = blk < nblk;
-            float4 t = make_float4(0.0f, 0.0f, 0.0f, 0.0f), w = t;
-            if (act) {
-                const int e = blk * 32 + sub * 4;
-                t = remote(e) ? ll_read4(xl + 8 * (int64_t) e, xtag) : gs_ld4<COHERENT>(x + e);
-                if (nw) w = *(const float4 *) (nw + e);
-            }
-            quant_store(blk, act, t, w, scale);
+        for (int b0 = warp * 8; b0 < nblk; b0 += BPP) {
+            float v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            const bool act = b0 + bw < nblk;
+            if (act) load8((b0 + bw) * 32 + sub * 8, v);
+            quant_store(b0 + bw, act, v, scale);
         }
     }
     named_bar_sync(1, GS_PRO_THREADS);
@@ -699,14 +752,13 @@ __device__ __forceinline__ void gs_prologue(const gs_params & p, const gs_ctx & 
 // FLASH_ATTN_EXT nodes (rope.cu:563, set-rows.cu:318, fattn-vec.cuh:19-507).  The current token's K/V rows are taken
 // from the raw projections (RoPE applied, rounded to f16 exactly as the cache stores them) and written to the cache by
 // the first query head of each KV group; all other positions are read from the cache.
-// one element of q / k_new / v_new: plain when this rank computed it, else the tagged word another rank stored
+// one element of q / k_new / v_new: a tagged word when a phase of this chain produced it
 template <bool PEER>
-__device__ __forceinline__ float gs_attn_ld(const gs_params & p, const float * base, int64_t i, int lo, int hi, unsigned int tag) {
-    if (!PEER || (i >= lo && i < hi)) return __ldcg(base + i);
-    return ll_read(p.ll_base + 2 * ((const char *) (base + i) - p.arena), tag);
+__device__ __forceinline__ float gs_attn_ld(const float * base, const unsigned long long * ll, int64_t i, unsigned int tag) {
+    return ll ? ll_read<PEER>(ll + i, tag) : __ldcg(base + i);
 }
 template <int D, bool PEER>
-__device__ __forceinline__ void gs_attn_item(const gs_params & p, unsigned int ltag, const gs_attn & a, int h, float * sm, int warp, int lane) {
+__device__ __forceinline__ void gs_attn_item(unsigned int ltag, unsigned int self_tag, const gs_attn & a, int h, float * sm, int warp, int lane) {
     constexpr int LPP = D / 32, PPB = 32 / LPP, DPL = D / 32;     // lanes per position, positions per batch, dims per lane (V)
     const int tid = warp * 32 + lane;
     const int gqa = a.H / a.H_kv, g = h / gqa;
@@ -720,26 +772,26 @@ __device__ __forceinline__ void gs_attn_item(const gs_params & p, unsigned int l
             const int i = isk ? tid - D / 2 : tid;
             const float * src = isk ? a.k_new : a.q;
             const int64_t so = isk ? (int64_t) g * D : (int64_t) h * D;
-            const int slo = isk ? a.k_lo : a.q_lo, shi = isk ? a.k_hi : a.q_hi;
+            const unsigned long long * sll = isk ? a.k_ll : a.q_ll;
             const unsigned int stag = ltag + (isk ? a.k_tag : a.q_tag);
             float * dst = isk ? s_k : s_q;
             if (i < half_d) {
                 const int i0 = a.rope_mode == 2 ? i : 2 * i, i1 = a.rope_mode == 2 ? i + half_d : 2 * i + 1;
                 const float theta = (float) pos * powf(a.theta_scale, (float) i) * a.freq_scale;
                 float sn, cs; sincosf(theta, &sn, &cs);
-                const float x0 = gs_attn_ld<PEER>(p, src, so + i0, slo, shi, stag), x1 = gs_attn_ld<PEER>(p, src, so + i1, slo, shi, stag);
+                const float x0 = gs_attn_ld<PEER>(src, sll, so + i0, stag), x1 = gs_attn_ld<PEER>(src, sll, so + i1, stag);
                 float y0 = x0 * cs - x1 * sn, y1 = x0 * sn + x1 * cs;
                 if (isk) { y0 = __half2float(__float2half_rn(y0)); y1 = __half2float(__float2half_rn(y1)); }
                 else     { y0 *= a.scale; y1 *= a.scale; }
                 dst[i0] = y0; dst[i1] = y1;
             }
             for (int d = a.n_dims + i; d < D; d += D / 2) {       // dims beyond n_dims pass through
-                const float y = gs_attn_ld<PEER>(p, src, so + d, slo, shi, stag);
+                const float y = gs_attn_ld<PEER>(src, sll, so + d, stag);
                 dst[d] = isk ? __half2float(__float2half_rn(y)) : y * a.scale;
             }
         } else if (tid < 2 * D) {
             const int d = tid - D;
-            s_v[d] = __half2float(__float2half_rn(gs_attn_ld<PEER>(p, a.v_new, (int64_t) g * D + d, a.v_lo, a.v_hi, ltag + a.v_tag)));
+            s_v[d] = __half2float(__float2half_rn(gs_attn_ld<PEER>(a.v_new, a.v_ll, (int64_t) g * D + d, ltag + a.v_tag)));
         }
     }
     named_bar_sync(3, GS_CON_THREADS);
@@ -829,7 +881,9 @@ __device__ __forceinline__ void gs_attn_item(const gs_params & p, unsigned int l
             const float wgt = mw == -INFINITY ? 0.0f : __expf(mw - M);
             A += wgt * s_part[w * (D + 2) + tid]; L += wgt * s_part[w * (D + 2) + D + 1];
         }
-        a.dst[(int64_t) h * D + tid] = A / L;
+        const float o = A / L;
+        a.dst[(int64_t) h * D + tid] = o;
+        if (a.dst_ll) ll_store<PEER>(a.dst_ll + (int64_t) h * D + tid, o, ltag + self_tag);      // every rank computes every head: local only
     }
     named_bar_sync(3, GS_CON_THREADS);                            // scratch is reused by the next item
 }
@@ -881,6 +935,7 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
     // trip per field per chunk (measured: 1.3 us per chunk in the finalizer)
     __shared__ gs_phase s_ph[2];       // consumers + finalizer (double-buffered: the finalizer may trail by a phase)
     __shared__ gs_phase s_pp;          // producer (runs ahead)
+    __shared__ int2 s_rng[2][B200_GEMV_MAX_SEG], s_prng[B200_GEMV_MAX_SEG];      // this CTA's row ranges of the staged phases
     gs_ctx c;
     c.ring = smem;                                                            // n_stages x stage_stride
     c.aq   = smem + p.n_stages * p.stage_stride;                              // activation int8, padded layout
@@ -892,7 +947,9 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
     if (tid == 0) {
         for (int s = 0; s < p.n_stages; ++s) { mbar_init(&sh.full[s], 1); mbar_init(&sh.empty[s], GS_NW); }
         // row split: tags of this launch = (launches so far + 1) * 1024 + phase index (never 0, the value of fresh memory)
-        sh.tag = PEER ? (__ldcg(p.epoch) + 1u) << 10 : 0u;
+        sh.tag = CHAIN ? (__ldcg(p.epoch) + 1u) << 10 : 0u;
+        if ((p.flags & 4) && p.dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1))     // debug accumulators of this launch
+            for (int i = 0; i < p.n_phases; ++i) { unsigned long long * dd = p.dbg + (i * 2 + (blockIdx.x ? 1 : 0)) * 8; dd[3] = dd[4] = dd[7] = 0; }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -914,11 +971,15 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
         // or per-line prefetch.global.L2 — ran 1-4 % slower; the consume phases are not short of HBM bytes in flight.)
         const uint64_t pol = policy_evict_first();
         gs_walk wt;
-        while (gs_walk_next(wt, &s_pp, phases, n_phases, blockIdx.x, gridDim.x, lane)) {
+        while (gs_walk_next(wt, &s_pp, s_prng, phases, CHAIN ? p.ranges : nullptr, n_phases, blockIdx.x, gridDim.x, lane)) {
             if (lane == 0) {
                 const gs_seg & sg = s_pp.seg[wt.s];
                 const int nr = min(sg.R, wt.r1 - wt.row);
                 mbar_wait(&sh.empty[pos.st], pos.full_par ^ 1);
+                if ((p.flags & 4) && p.dbg && wt.row == wt_first_row(wt, s_pp) && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) {
+                    unsigned long long * dd = p.dbg + (wt.ip * 2 + (blockIdx.x ? 1 : 0)) * 8;
+                    if (!dd[7]) dd[7] = gs_now();                  // debug: when the FIRST chunk of this phase was requested
+                }
                 uint8_t * dstp = c.ring + pos.st * p.stage_stride;
                 const uintptr_t g0 = (uintptr_t) (sg.w[0] + (int64_t) wt.row * sg.rb);
                 const uint32_t o0 = (uint32_t) (g0 & 15), b0 = (o0 + (uint32_t) nr * sg.rb + 15u) & ~15u;
@@ -941,70 +1002,61 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
     }
 
     // ================= consumers (warps 0..GS_NW-1)
+    // There is no grid barrier between the phases of a chain: whatever a phase reads from an earlier one arrives as tagged
+    // words (see gs_seg), so a CTA moves on as soon as ITS inputs exist, publishes nothing and fences nothing.  No CTA can be
+    // more than one phase ahead of the slowest one: a GEMV prologue needs every row of the phase before it.
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(GS_REG_CONSUMER));
     for (int ip = 0; ip < n_phases; ++ip) {
         const gs_phase & ph = s_ph[ip & 1];
-        // static data: staged (and the norm weights requested into L2) before the dependency wait
+        // the descriptor is double-buffered: slower warps of this CTA may still be reading the previous one
         for (int i = tid; i < PH_VEC; i += GS_CON_THREADS) ((uint4 *) &s_ph[ip & 1])[i] = ((const uint4 *) (phases + ip))[i];
-        // ---- dependency: everything this phase reads was produced by the previous phase (or earlier kernels)
-        if (ip == 0) {
-            pdl_wait();
-        } else if (tid == 0) {
-            gs_wait_counter<false>(p.bar + ip - 1, gridDim.x);       // this GPU's CTAs; rows of other ranks carry their own tags
-        }
-        named_bar_sync(1, GS_CON_THREADS);
+        if (CHAIN) gs_stage_ranges(s_rng[ip & 1], &ph, p.ranges, ip, blockIdx.x, gridDim.x, tid);
+        if (ip == 0) pdl_wait();                                   // plain inputs were written by earlier kernels
+        named_bar_sync(1, GS_CON_THREADS);                         // descriptor staged; every warp has left phase ip - 1
+        if (!CHAIN) { gs_stage_ranges(s_rng[0], &ph, nullptr, 0, blockIdx.x, gridDim.x, tid); named_bar_sync(1, GS_CON_THREADS); }
         if (CHAIN && tid == 0) GS_STAMP(ip, 0);
         if (ph.kind == 0) {
             gs_prologue<CHAIN, PEER>(p, c, ph, warp, lane);
             if (CHAIN && tid == 0) GS_STAMP(ip, 1);
-            const int64_t lo = ph.total_bytes * (int64_t) blockIdx.x / gridDim.x, hi = ph.total_bytes * (int64_t) (blockIdx.x + 1) / gridDim.x;
             for (int s = 0; s < ph.n_ws; ++s) {
                 const gs_seg & sg = ph.seg[s];
-                int r0, r1; gs_row_range(sg, lo, hi, r0, r1);
+                const int r0 = s_rng[ip & 1][s].x, r1 = s_rng[ip & 1][s].y;
                 if (r0 >= r1) continue;
                 if (sg.type == T0) consume_dispatch<T0, CHAIN, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
                 else               consume_dispatch<T1, CHAIN, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
             }
         } else if (CHAIN && ph.kind == 1) {
             for (int h = blockIdx.x; h < ph.attn.H; h += gridDim.x) {
-                if (ph.attn.D == 128) gs_attn_item<128, PEER>(p, sh.tag, ph.attn, h, c.attn, warp, lane);
-                else                  gs_attn_item<64, PEER>(p, sh.tag, ph.attn, h, c.attn, warp, lane);
+                if (ph.attn.D == 128) gs_attn_item<128, PEER>(sh.tag, ph.self_tag, ph.attn, h, c.attn, warp, lane);
+                else                  gs_attn_item<64, PEER>(sh.tag, ph.self_tag, ph.attn, h, c.attn, warp, lane);
             }
         }
-        if (CHAIN) {
-            if (tid == 0) GS_STAMP(ip, 2);
-            // ---- publish: this CTA's stores of the phase are visible device-wide, then count it in
-            // Default: thread 0 alone releases, after the CTA barrier (the barrier orders every consumer thread's stores before
-            // it and the release is cumulative — the pattern of a cooperative-groups grid sync).  flags bit 3: the older
-            // variant, __threadfence in every thread before the barrier (measured equal within 0.5 %).
-            const bool fence_all = (c.flags & 8) != 0;
-            if (fence_all) __threadfence();
+        if (CHAIN && tid == 0) GS_STAMP(ip, 2);
+        if (PEER && ph.peer_mode == 2) {
+            // outputs read after the launch (the logits) went to the other ranks as plain stores: CTA barrier, one
+            // system-scope fence, then the arrival is counted on every rank
             named_bar_sync(1, GS_CON_THREADS);
             if (tid == 0) {
-                GS_STAMP(ip, 4);
-                // release at device scope on the arrival itself (MEMBAR.ALL.GPU + RED; __threadfence would add an L1
-                // invalidate nobody needs: data of this launch is only ever read with ld.cg / ld.acquire)
-                if (fence_all) atomicAdd(p.bar + ip, 1u);
-                else asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p.bar + ip), "r"(1u) : "memory");
-                if (PEER && ph.peer_mode == 2) {
-                    // outputs read after the launch (the logits) went to the other ranks as plain stores: one system-scope
-                    // fence, then the arrival is counted on every rank
-                    __threadfence_system();
-                    atomicAdd_system(p.sync + ip, 1u);
+                __threadfence_system();
+                atomicAdd_system(p.sync + ip, 1u);
 #pragma unroll
-                    for (int r = 0; r < B200_MAX_RANKS - 1; ++r)
-                        if (r < p.n_peers) atomicAdd_system((unsigned int *) ((char *) (p.sync + ip) + p.peer_delta[r]), 1u);
-                }
-                GS_STAMP(ip, 3);
+                for (int r = 0; r < B200_MAX_RANKS - 1; ++r)
+                    if (r < p.n_peers) atomicAdd_system((unsigned int *) ((char *) (p.sync + ip) + p.peer_delta[r]), 1u);
             }
         }
     }
-    if (PEER && blockIdx.x == 0 && tid == 0) {
-        // the launch ends only when every rank has delivered its plain-stored rows (the logits) into this rank's buffers;
-        // then the launch is counted.  No CTA of this launch reads the epoch after its first instructions, and no CTA of
-        // the next launch starts before this one has exited (same stream).
-        for (int k = 0; k < p.n_final; ++k) gs_wait_counter<true>(p.sync + p.final_phase[k], (unsigned int) p.total_ctas);
-        *p.epoch = __ldcg(p.epoch) + 1u;
+    if (CHAIN && tid == 0) {
+        if (PEER) {
+            // the launch ends only when every rank has delivered its plain-stored rows (the logits) into this rank's buffers
+            if (blockIdx.x == 0)
+                for (int k = 0; k < p.n_final; ++k) gs_wait_counter<true>(p.sync + p.final_phase[k], (unsigned int) p.total_ctas);
+        }
+        // the last CTA to leave counts the launch: every CTA read the epoch in its first instructions, and the next launch
+        // starts only after this one has exited (same stream)
+        if (atomicAdd(p.exit_count, 1u) == gridDim.x - 1) {
+            const unsigned int e = sh.tag >> 10;                   // = epoch + 1; tags are (epoch + 1) << 10 | phase: keep them non-zero in 32 bits
+            *p.exit_count = 0u; *p.epoch = e >= 0x3FFFFEu ? 0u : e;
+        }
     }
 }
 

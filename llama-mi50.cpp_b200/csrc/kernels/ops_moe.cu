@@ -1,0 +1,209 @@
+// ops_moe.cu — row G glue of the MoE decode graph (gpt-oss, BASELINE.json configs[4]): expert routing and the small float
+// matmul in front of it.  Replaces reference ggml-cuda/argsort.cu (bitonic sort), top-k.cu, add-id.cu (:28), sumrows.cu,
+// clamp.cu and the float-weight path of ggml_cuda_mul_mat (ggml-cuda.cu:2183-2266; mmvf.cu for few columns) for the router
+// matrix `ffn_gate_inp` (f32 [n_embd, n_expert]).  Graph of reference src/llama-graph.cpp build_moe_ffn:
+//   logits = gate_inp . x (+ bias) ; selected = view(argsort_desc(logits), n_used) ; weights = softmax(get_rows(logits, selected))
+//   up/gate/down = mul_mat_id(..., selected) (+ add_id(bias, selected)) ; out = sum_e weights[e] * down[e]
+#include <cuda_bf16.h>
+
+#include <mutex>
+
+#include "common.cuh"
+
+namespace b200 {
+
+#define VALIDATE_ONLY(stream) ((stream) == B200_STREAM_VALIDATE)
+
+// ------------------------------------------------------------------ ARGSORT / TOP_K
+// One CTA per row: indices in shared memory, bitonic network over the row padded to a power of two (padding sorts last).
+// order: 0 ascending, 1 descending (ggml_sort_order).  Only the first n_out indices of the sorted row are written.
+template <int ORDER>
+__global__ void __launch_bounds__(1024) argsort_kernel(const float * x, int32_t * dst, int n, int n_pad, int64_t x_row, int64_t d_row, int n_out) {
+    extern __shared__ int32_t s_idx[];
+    pdl_launch_dependents();
+    const float * row = x + (int64_t) blockIdx.x * x_row;
+    for (int i = threadIdx.x; i < n_pad; i += blockDim.x) s_idx[i] = i;
+    pdl_wait();
+    __syncthreads();
+    // a < b in the target order; indices >= n (padding) are larger than everything
+    auto before = [&](int a, int b) {
+        if (a >= n) return false;
+        if (b >= n) return true;
+        const float va = row[a], vb = row[b];
+        return ORDER == 0 ? va < vb : va > vb;
+    };
+    for (int k = 2; k <= n_pad; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = threadIdx.x; i < n_pad; i += blockDim.x) {
+                const int l = i ^ j;
+                if (l > i) {
+                    const int a = s_idx[i], b = s_idx[l];
+                    const bool up = (i & k) == 0;           // this pair sorts in the target order
+                    if (up ? before(b, a) : before(a, b)) { s_idx[i] = b; s_idx[l] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    }
+    int32_t * out = dst + (int64_t) blockIdx.x * d_row;
+    for (int i = threadIdx.x; i < n_out; i += blockDim.x) out[i] = s_idx[i];
+}
+
+static int argsort_common(const b200_tensor * x, const b200_tensor * d, int order, int n_out, void * stream, const char * what) {
+    if (!x || !d || x->type != B200_F32 || d->type != B200_I32 || x->nb[0] != 4 || d->nb[0] != 4) return B200_ERR_UNSUPPORTED;
+    if (!is_contiguous(*x) || !is_contiguous(*d) || x->ne[0] < 1 || x->ne[0] > 32768) return B200_ERR_UNSUPPORTED;
+    if (d->ne[0] != n_out || d->ne[1] != x->ne[1] || d->ne[2] != x->ne[2] || d->ne[3] != x->ne[3] || n_out > x->ne[0] || n_out < 1) return B200_ERR_UNSUPPORTED;
+    if (order != 0 && order != 1) return B200_ERR_UNSUPPORTED;
+    const int64_t rows = nrows(*x);
+    if (rows > 0x7fffffff) return B200_ERR_UNSUPPORTED;
+    if (VALIDATE_ONLY(stream)) return B200_OK;
+    if (rows == 0) return B200_OK;
+    int n_pad = 1; while (n_pad < x->ne[0]) n_pad <<= 1;
+    const size_t smem = (size_t) n_pad * 4;
+    static std::once_flag once[64]; int dev = 0; B200_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return B200_ERR_ARG;
+    cudaError_t rc = cudaSuccess;
+    std::call_once(once[dev], [&] {
+        rc = cudaFuncSetAttribute(argsort_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
+        if (rc == cudaSuccess) rc = cudaFuncSetAttribute(argsort_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
+    });
+    B200_CUDA_TRY(rc);
+    const int threads = n_pad >= 1024 ? 1024 : (n_pad < 32 ? 32 : n_pad);
+    if (order == 0) argsort_kernel<0><<<(unsigned) rows, threads, smem, (cudaStream_t) stream>>>((const float *) x->data, (int32_t *) d->data, (int) x->ne[0], n_pad, x->ne[0], n_out, n_out);
+    else            argsort_kernel<1><<<(unsigned) rows, threads, smem, (cudaStream_t) stream>>>((const float *) x->data, (int32_t *) d->data, (int) x->ne[0], n_pad, x->ne[0], n_out, n_out);
+    count_launch();
+    return check_launch(what);
+}
+
+// ------------------------------------------------------------------ ADD_ID: dst[:, e, t] = a[:, e, t] + b[:, ids[e, t]]
+__global__ void __launch_bounds__(256) add_id_kernel(const char * a, const char * b, const char * ids, char * d, int64_t ne0, int64_t ne1,
+                                                     int64_t a_nb1, int64_t a_nb2, int64_t b_nb1, int64_t i_nb0, int64_t i_nb1, int64_t d_nb1, int64_t d_nb2) {
+    pdl_launch_dependents();
+    const int64_t e = blockIdx.x % ne1, t = blockIdx.x / ne1;
+    pdl_wait();
+    const int32_t id = *(const int32_t *) (ids + e * i_nb0 + t * i_nb1);
+    const float * pa = (const float *) (a + e * a_nb1 + t * a_nb2);
+    const float * pb = (const float *) (b + (int64_t) id * b_nb1);
+    float * pd = (float *) (d + e * d_nb1 + t * d_nb2);
+    for (int64_t i = threadIdx.x; i < ne0; i += blockDim.x) pd[i] = pa[i] + pb[i];
+}
+
+// ------------------------------------------------------------------ SUM_ROWS / CLAMP
+__global__ void __launch_bounds__(256) sum_rows_kernel(const char * x, char * d, int64_t ne0, int64_t ne1, int64_t ne2,
+                                                       int64_t x_nb1, int64_t x_nb2, int64_t x_nb3, int64_t d_nb1, int64_t d_nb2, int64_t d_nb3) {
+    pdl_launch_dependents();
+    const int64_t r = blockIdx.x, i1 = r % ne1, i2 = (r / ne1) % ne2, i3 = r / (ne1 * ne2);
+    pdl_wait();
+    const float * row = (const float *) (x + i1 * x_nb1 + i2 * x_nb2 + i3 * x_nb3);
+    float s = 0.0f;
+    for (int64_t i = threadIdx.x; i < ne0; i += blockDim.x) s += row[i];
+    s = warp_sum(s);
+    __shared__ float part[8];
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.0f;
+        for (int w = 0; w < (int) (blockDim.x >> 5); ++w) t += part[w];
+        *(float *) (d + i1 * d_nb1 + i2 * d_nb2 + i3 * d_nb3) = t;
+    }
+}
+__global__ void __launch_bounds__(256) clamp_kernel(const float * x, float * d, float lo, float hi, int64_t n) {
+    pdl_launch_dependents();
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    pdl_wait();
+    if (i < n) { const float v = x[i]; d[i] = v < lo ? lo : (v > hi ? hi : v); }
+}
+
+// ------------------------------------------------------------------ float-weight matmul: dst[m, n] = sum_k W[k, m] * x[k, n]
+// one CTA per weight row and window of up to 8 columns (the router matrix is 1.5 MB: it lives in L2 across the windows)
+template <typename T> __device__ __forceinline__ float w_as_f32(const T & v);
+template <> __device__ __forceinline__ float w_as_f32<float>(const float & v) { return v; }
+template <> __device__ __forceinline__ float w_as_f32<__half>(const __half & v) { return __half2float(v); }
+template <> __device__ __forceinline__ float w_as_f32<__nv_bfloat16>(const __nv_bfloat16 & v) { return __bfloat162float(v); }
+template <typename T>
+__global__ void __launch_bounds__(128) mul_mat_f_kernel(const char * w, const float * x, float * d, int64_t K, int64_t N, int64_t w_nb1, int64_t x_ld, int64_t d_ld) {
+    pdl_launch_dependents();
+    const int64_t m = blockIdx.x, n0 = (int64_t) blockIdx.y * 8;
+    const int nc = (int) min((int64_t) 8, N - n0);
+    const T * wr = (const T *) (w + m * w_nb1);
+    pdl_wait();
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int64_t k = threadIdx.x; k < K; k += blockDim.x) {
+        const float wv = w_as_f32<T>(wr[k]);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) if (c < nc) acc[c] += wv * x[(n0 + c) * x_ld + k];
+    }
+    __shared__ float part[4][8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) { const float s = warp_sum(acc[c]); if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5][c] = s; }
+    __syncthreads();
+    if (threadIdx.x < nc) d[(n0 + threadIdx.x) * d_ld + m] = part[0][threadIdx.x] + part[1][threadIdx.x] + part[2][threadIdx.x] + part[3][threadIdx.x];
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_argsort(const b200_tensor * x, const b200_tensor * dst, int order, void * stream) {
+    return argsort_common(x, dst, order, dst ? (int) dst->ne[0] : 0, stream, "argsort");
+}
+extern "C" int b200_top_k(const b200_tensor * x, const b200_tensor * dst, void * stream) {
+    return argsort_common(x, dst, 1, dst ? (int) dst->ne[0] : 0, stream, "top_k");
+}
+
+extern "C" int b200_add_id(const b200_tensor * a, const b200_tensor * b, const b200_tensor * ids, const b200_tensor * d, void * stream) {
+    if (!a || !b || !ids || !d) return B200_ERR_ARG;
+    if (a->type != B200_F32 || b->type != B200_F32 || d->type != B200_F32 || ids->type != B200_I32) return B200_ERR_UNSUPPORTED;
+    if (a->nb[0] != 4 || b->nb[0] != 4 || d->nb[0] != 4 || a->ne[3] != 1 || d->ne[3] != 1 || b->ne[2] != 1 || b->ne[3] != 1) return B200_ERR_UNSUPPORTED;
+    if (b->ne[0] != a->ne[0] || ids->ne[0] != a->ne[1] || ids->ne[1] != a->ne[2] || ids->ne[2] != 1 || ids->ne[3] != 1) return B200_ERR_UNSUPPORTED;
+    for (int i = 0; i < 4; ++i) if (d->ne[i] != a->ne[i]) return B200_ERR_UNSUPPORTED;
+    if (a->ne[1] * a->ne[2] > 0x7fffffff) return B200_ERR_UNSUPPORTED;
+    if (VALIDATE_ONLY(stream)) return B200_OK;
+    if (nelements(*d) == 0) return B200_OK;
+    add_id_kernel<<<(unsigned) (a->ne[1] * a->ne[2]), 256, 0, (cudaStream_t) stream>>>((const char *) a->data, (const char *) b->data, (const char *) ids->data, (char *) d->data,
+        a->ne[0], a->ne[1], a->nb[1], a->nb[2], b->nb[1], ids->nb[0], ids->nb[1], d->nb[1], d->nb[2]);
+    count_launch();
+    return check_launch("add_id");
+}
+
+extern "C" int b200_sum_rows(const b200_tensor * x, const b200_tensor * d, void * stream) {
+    if (!x || !d || x->type != B200_F32 || d->type != B200_F32 || x->nb[0] != 4 || d->ne[0] != 1) return B200_ERR_UNSUPPORTED;
+    if (d->ne[1] != x->ne[1] || d->ne[2] != x->ne[2] || d->ne[3] != x->ne[3] || nrows(*x) > 0x7fffffff) return B200_ERR_UNSUPPORTED;
+    if (VALIDATE_ONLY(stream)) return B200_OK;
+    if (nrows(*x) == 0) return B200_OK;
+    sum_rows_kernel<<<(unsigned) nrows(*x), 256, 0, (cudaStream_t) stream>>>((const char *) x->data, (char *) d->data, x->ne[0], x->ne[1], x->ne[2],
+        x->nb[1], x->nb[2], x->nb[3], d->nb[1], d->nb[2], d->nb[3]);
+    count_launch();
+    return check_launch("sum_rows");
+}
+
+extern "C" int b200_clamp(const b200_tensor * x, const b200_tensor * d, float lo, float hi, void * stream) {
+    if (!x || !d || x->type != B200_F32 || d->type != B200_F32 || !is_contiguous(*x) || !is_contiguous(*d) || nelements(*x) != nelements(*d)) return B200_ERR_UNSUPPORTED;
+    if (VALIDATE_ONLY(stream)) return B200_OK;
+    const int64_t n = nelements(*x);
+    if (n == 0) return B200_OK;
+    clamp_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, (cudaStream_t) stream>>>((const float *) x->data, (float *) d->data, lo, hi, n);
+    count_launch();
+    return check_launch("clamp");
+}
+
+extern "C" int b200_mul_mat_f(const b200_tensor * w, const b200_tensor * x, const b200_tensor * d, void * stream) {
+    if (!w || !x || !d) return B200_ERR_ARG;
+    if (w->type != B200_F32 && w->type != B200_F16 && w->type != B200_BF16) return B200_ERR_UNSUPPORTED;
+    if (x->type != B200_F32 || d->type != B200_F32 || w->nb[0] != (int64_t) b200_type_size(w->type) || x->nb[0] != 4 || d->nb[0] != 4) return B200_ERR_UNSUPPORTED;
+    if (w->ne[2] != 1 || w->ne[3] != 1 || x->ne[2] != 1 || x->ne[3] != 1 || d->ne[2] != 1 || d->ne[3] != 1) return B200_ERR_UNSUPPORTED;
+    if (x->ne[0] != w->ne[0] || d->ne[0] != w->ne[1] || d->ne[1] != x->ne[1] || x->nb[1] % 4 || d->nb[1] % 4 || w->nb[1] % (int64_t) b200_type_size(w->type)) return B200_ERR_UNSUPPORTED;
+    if (w->ne[1] > 0x7fffffff || (x->ne[1] + 7) / 8 > 65535) return B200_ERR_UNSUPPORTED;
+    if (VALIDATE_ONLY(stream)) return B200_OK;
+    if (nelements(*d) == 0) return B200_OK;
+    dim3 grid((unsigned) w->ne[1], (unsigned) ((x->ne[1] + 7) / 8));
+    cudaStream_t st = (cudaStream_t) stream;
+    const char * pw = (const char *) w->data; const float * px = (const float *) x->data; float * pd = (float *) d->data;
+    switch (w->type) {
+        case B200_F32: mul_mat_f_kernel<float><<<grid, 128, 0, st>>>(pw, px, pd, w->ne[0], x->ne[1], w->nb[1], x->nb[1] / 4, d->nb[1] / 4); break;
+        case B200_F16: mul_mat_f_kernel<__half><<<grid, 128, 0, st>>>(pw, px, pd, w->ne[0], x->ne[1], w->nb[1], x->nb[1] / 4, d->nb[1] / 4); break;
+        default:       mul_mat_f_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>(pw, px, pd, w->ne[0], x->ne[1], w->nb[1], x->nb[1] / 4, d->nb[1] / 4); break;
+    }
+    count_launch();
+    return check_launch("mul_mat_f");
+}

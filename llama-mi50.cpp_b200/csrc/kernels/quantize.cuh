@@ -45,6 +45,25 @@ __device__ __forceinline__ int quantize_block32_quad(const float x[4], float & d
     return (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((q[3] & 0xff) << 24);
 }
 
+// Four lanes own one block, eight consecutive elements per lane; returns them packed as two int8x4 words.
+__device__ __forceinline__ int2 quantize_block32_oct(const float x[8], float & d_out, int & sum_out) {
+    float amax = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(x[i]));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+    const float d  = __fdiv_rn(amax, 127.0f);
+    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+    int q[8], s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { q[i] = (int) roundf(__fmul_rn(x[i], id)); s += q[i]; }
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    d_out = d; sum_out = s;
+    return make_int2((q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((q[3] & 0xff) << 24),
+                     (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((q[7] & 0xff) << 24));
+}
+
 __device__ __forceinline__ __half2 q8_1_scales(float d, int sum) {
     return __halves2half2(__float2half_rn(d), __float2half_rn(__fmul_rn((float) sum, d)));
 }

@@ -18,7 +18,7 @@
 
 static std::vector<std::vector<float>> run(const char * path, int ngl, int n_prompt, int n_decode) {
     llama_model_params mp = llama_model_default_params();
-    mp.n_gpu_layers = ngl;
+    mp.n_gpu_layers = ngl < 0 ? 0 : ngl;
     if (ngl > 0 && getenv("B200_PARITY_SPLIT_ROW")) mp.split_mode = LLAMA_SPLIT_MODE_ROW;
     llama_model * m = llama_model_load_from_file(path, mp);
     if (!m) { fprintf(stderr, "model load failed\n"); exit(3); }
@@ -26,7 +26,8 @@ static std::vector<std::vector<float>> run(const char * path, int ngl, int n_pro
     llama_context_params cp = llama_context_default_params();
     cp.n_ctx = getenv("B200_PARITY_NCTX") ? atoi(getenv("B200_PARITY_NCTX")) : 1024;
     cp.n_batch = 512; cp.flash_attn_type = LLAMA_FLASH_ATTN_TYPE_ENABLED; cp.n_threads = 8; cp.n_threads_batch = 8;
-    if (const char * kv = getenv("B200_PARITY_KV")) {
+    const char * kv_override = ngl == 0 ? nullptr : getenv("B200_PARITY_KV2");     // second run only (sensitivity probe, below)
+    if (const char * kv = kv_override ? kv_override : getenv("B200_PARITY_KV")) {
         const ggml_type t = !strcmp(kv, "q8_0") ? GGML_TYPE_Q8_0 : !strcmp(kv, "q4_0") ? GGML_TYPE_Q4_0 : GGML_TYPE_F16;
         cp.type_k = t; cp.type_v = t;
     }
@@ -55,8 +56,12 @@ int main(int argc, char ** argv) {
     const double tol = argc > 6 ? atof(argv[6]) : 2e-3;
     ggml_backend_load_all_from_path(argv[2]);
     const auto ref = run(argv[1], 0, n_prompt, n_decode);            // only CPU devices are registered at this point
-    if (!ggml_backend_load(argv[3])) { fprintf(stderr, "cannot load plugin %s\n", argv[3]); return 5; }
-    const auto got = run(argv[1], 999, n_prompt, n_decode);
+    // plugin.so == "cpu": sensitivity probe of the MODEL, not a parity run: the second run is the CPU backend again, with
+    // the KV-cache type of B200_PARITY_KV2 (e.g. q8_0: a relative perturbation of ~0.4 % on K and V).  The NMSE it prints
+    // is how much the logits of this model move under a perturbation of the size of one quantisation step.
+    const bool probe = !strcmp(argv[3], "cpu");
+    if (!probe && !ggml_backend_load(argv[3])) { fprintf(stderr, "cannot load plugin %s\n", argv[3]); return 5; }
+    const auto got = run(argv[1], probe ? -1 : 999, n_prompt, n_decode);
     int bad = 0;
     for (size_t s = 0; s < ref.size(); ++s) {
         double num = 0, den = 0; int am_r = 0, am_g = 0;

@@ -62,7 +62,9 @@ def test_plugin_llama3_8b_matches_cpu_backend(tmp_path):
     """The model the bench times (BASELINE.json configs[1], Llama-3-8B-shape Q4_K_M: the 161-phase decode chain and the
     tcgen05 prefill GEMM at their real sizes): a 64-token prompt and 3 decode steps against the CPU backend.  Tolerance
     5e-3: 32 layers of q8_1 (here) vs Q8_K (CPU) activation rounding compound; every matmul alone is gated at 5e-4 by
-    test-backend-ops (tests/test_gpu_tbo.py)."""
+    test-backend-ops (tests/test_gpu_tbo.py).  The model's own sensitivity — the reference CPU backend against itself with a
+    q8_0 instead of an f16 KV cache — is 5e-4..8e-4 on these weights (gguf_synth.py _DEEP; with N(0, 0.02) weights
+    everywhere it is 0.25-0.48 and the comparison would mean nothing)."""
     from llama_mi50_b200 import gguf_synth as gs
     model_dir = os.environ.get("B200_MODEL_DIR", "/tmp/b200_models")
     os.makedirs(model_dir, exist_ok=True)
@@ -104,11 +106,13 @@ def test_plugin_decodes_across_kv_padding_boundaries(chain, tmp_path):
 @pytest.mark.parametrize("kv", ["f16", "q8_0"])
 def test_plugin_long_context(kv, chain, tmp_path):
     """Context beyond 1024 positions through the plugin: the chain hands attention over to the split-KV kernels
-    (fattn_dec_mma_kernel from 1024 positions on), and the prompt (1000 tokens) runs the prefill attention in two batches."""
+    (fattn_dec_mma_kernel from 1024 positions on), and the prompt (1000 tokens) runs the prefill attention in two batches.
+    q8_0 cache: 5e-3 — the CPU backend quantises Q to q8_0 for its K dot products (vec_dot_type of q8_0) while the kernels
+    here keep Q in f16/f32, so the two sides differ by one more 8-bit rounding per attention (measured 3e-4..2.5e-3)."""
     from llama_mi50_b200 import gguf_synth as gs
     path = str(tmp_path / "tiny-q4_k_m.gguf")
     gs.write_gguf(path, gs.SHAPES["tiny-q4_k_m"])
     env = {"B200_PARITY_NCTX": "2048", "B200_PARITY_KV": kv}
     if not chain:
         env["GGML_B200_DISABLE_CHAIN"] = "1"
-    _parity(path, 1000, 60, 2e-3, env)
+    _parity(path, 1000, 60, 2e-3 if kv == "f16" else 5e-3, env)
