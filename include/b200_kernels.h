@@ -315,6 +315,18 @@ typedef struct b200_fattn_args {
 B200_API size_t b200_fattn_scratch_size(const b200_fattn_args * a);
 B200_API int    b200_flash_attn_ext(const b200_fattn_args * a, void * stream);
 
+/* FLASH_ATTN_EXT for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.
+ * Same arguments, kernels and results as b200_flash_attn_ext, but a->scratch / a->scratch_size are IGNORED: the split-KV
+ * scratch is a file-scope `static __device__` array of B200_FATTN_STATIC_SCRATCH_BYTES inside the library (every GPU that
+ * loads the library holds it until exit).  The call performs no cudaMalloc / cudaFree / allocating library routine.
+ * Shapes whose b200_fattn_scratch_size() exceeds the array are rejected with B200_ERR_ARG (b200_last_error() names both
+ * sizes).  All calls on a device share the one array: calls that overlap on the GPU (different streams) race — serialise
+ * them on one stream.  The array keeps the previous call's contents; the arrival counters are cleared on `stream` by every
+ * call that uses them. */
+#define B200_FATTN_STATIC_SCRATCH_BYTES (8u << 20)
+B200_API int    b200_flash_attn_ext_static(const b200_fattn_args * a, void * stream);
+
 #ifdef __cplusplus
 }
 #endif

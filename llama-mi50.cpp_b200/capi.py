@@ -234,12 +234,16 @@ def get_rows(src_bytes, src_type, src_ne, ids):
     return d
 
 
-def flash_attn(q, k_bytes, v_bytes, kv_type, n_kv, H_kv, mask=None, sinks=None, scale=1.0, max_bias=0.0, softcap=0.0):
+def flash_attn(q, k_bytes, v_bytes, kv_type, n_kv, H_kv, mask=None, sinks=None, scale=1.0, max_bias=0.0, softcap=0.0,
+               static_scratch=False, dst=None):
     """q: f32 [H, n_q, D] CUDA (ggml [D, n_q, H]); k/v: packed rows, ggml [D, n_kv, H_kv] contiguous;
-    mask: f16 [n_q, n_kv]; returns f32 [n_q, H, D]."""
+    mask: f16 [n_q, n_kv]; returns f32 [n_q, H, D].
+    static_scratch: call b200_flash_attn_ext_static (the library's own static device scratch; nothing is allocated by the
+    call — pass `dst` to keep this wrapper allocation-free too)."""
     import torch
     H, n_q, D = q.shape
-    dst = torch.empty(n_q, H, D, dtype=torch.float32, device=q.device)
+    if dst is None:
+        dst = torch.empty(n_q, H, D, dtype=torch.float32, device=q.device)
     a = FattnArgs()
     a.q = from_torch(q)
     a.k = make_tensor(k_bytes.data_ptr(), kv_type, [D, n_kv, H_kv, 1])
@@ -255,6 +259,10 @@ def flash_attn(q, k_bytes, v_bytes, kv_type, n_kv, H_kv, mask=None, sinks=None, 
     L.b200_fattn_scratch_size.restype = C.c_size_t
     L.b200_fattn_scratch_size.argtypes = [C.c_void_p]
     L.b200_flash_attn_ext.argtypes = [C.c_void_p, C.c_void_p]
+    if static_scratch:
+        L.b200_flash_attn_ext_static.argtypes = [C.c_void_p, C.c_void_p]
+        check(L.b200_flash_attn_ext_static(C.byref(a), stream_ptr()), "flash_attn_ext_static")
+        return dst
     n = L.b200_fattn_scratch_size(C.byref(a))
     assert n > 0, "flash_attn: unsupported shape"
     scratch = torch.zeros(n, dtype=torch.uint8, device=q.device)

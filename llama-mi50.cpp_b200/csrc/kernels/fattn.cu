@@ -866,3 +866,44 @@ extern "C" int b200_flash_attn_ext(const b200_fattn_args * a, void * stream) {
     count_launch();
     return check_launch("flash_attn_ext");
 }
+
+// ---- FLASH_ATTN_EXT without any allocation on the caller's side -------------------------------------------------------
+// Same kernels as b200_flash_attn_ext; the split-KV scratch (arrival counters + partials) is a file-scope device array
+// instead of a caller-provided buffer.  Every GPU that loads the library holds B200_FATTN_STATIC_SCRATCH_BYTES until exit.
+// All calls on a device share the array: calls that overlap on the GPU (different streams) race.  It keeps the previous
+// call's contents; the only part that must start at zero, the arrival counters, is cleared by the launcher on the stream
+// (cudaMemsetAsync on existing memory: not an allocation).
+static __device__ __align__(256) unsigned char fattn_static_scratch[B200_FATTN_STATIC_SCRATCH_BYTES];
+
+extern "C" int b200_flash_attn_ext_static(const b200_fattn_args * a, void * stream) {
+    fattn_plan pl;
+    if (!a) return B200_ERR_ARG;
+    if (!fattn_make_plan(a, pl)) return B200_ERR_UNSUPPORTED;
+    const size_t need = pl.counter_bytes + pl.part_bytes;
+    if (need > (size_t) B200_FATTN_STATIC_SCRATCH_BYTES) {
+        set_error("flash_attn_ext_static: this shape needs %zu bytes of scratch, the static array holds %zu (use b200_flash_attn_ext with a caller buffer)",
+                  need, (size_t) B200_FATTN_STATIC_SCRATCH_BYTES);
+        return B200_ERR_ARG;
+    }
+    if (stream == B200_STREAM_VALIDATE) return B200_OK;
+    // In host code the array's name is a host-side stand-in, not a device address: resolve it once per device, with that
+    // device current.
+    static std::mutex mu;
+    static void * dev_ptr[64] = {};
+    int dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return B200_ERR_ARG;
+    void * ptr;
+    {
+        std::lock_guard<std::mutex> g(mu);
+        if (!dev_ptr[dev]) {
+            void * sym = nullptr;
+            B200_CUDA_TRY(cudaGetSymbolAddress(&sym, fattn_static_scratch));
+            dev_ptr[dev] = sym;
+        }
+        ptr = dev_ptr[dev];
+    }
+    b200_fattn_args b = *a;
+    b.scratch = ptr; b.scratch_size = (size_t) B200_FATTN_STATIC_SCRATCH_BYTES;
+    return b200_flash_attn_ext(&b, stream);
+}
