@@ -130,7 +130,8 @@ static bool gs_finish_phase(gs_phase & ph, int stage_payload) {
         int R = (stage_payload - 64) / (g.rb * g.nsub);
         if (R > 64) R = 64;
         if (R < 1) return false;
-        if (g.nsub == 1 && R > GS_RB) R -= R % GS_RB;    // whole warp passes per chunk
+        const int opp = (g.KS == 1 ? 4 : GS_RB) / g.nsub;  // output rows per warp pass (gemv_stream.cuh, consume_segment)
+        if (R > opp) R -= R % opp;                         // whole warp passes per chunk
         g.R = R;
         g.byte_prefix = prefix;
         prefix += (int64_t) g.rb * g.nsub * g.M;

@@ -500,90 +500,120 @@ __device__ __forceinline__ void gs_put(const gs_params & p, const gs_phase & ph,
     }
 }
 
-// Rows of a chunk are dealt round-robin to the RG row groups (a row group = the KS warps that share a row), starting one
-// group further every chunk, so short chunks (4-6 rows of a K = 14336 matrix) keep every warp busy.  A pass of a warp covers
-// up to GS_RB = 2 rows of its group (for a GLU pair: the gate row and the up row of ONE output row).  The two row sums are
-// reduced TOGETHER: after the first exchange lane parity selects the row, so 5 shuffles serve both rows and the totals land
-// in lanes 0 and 1, which then run the epilogue of "their" row.
-template <int TYPE, int SPW, bool COHERENT, bool PEER>
+// Rows of a chunk are dealt to the RG row groups (a row group = the KS warps that share a row) in PASSES of RB weight rows,
+// round-robin, starting one group further every chunk, so short chunks keep every warp busy over time.
+//   RB = 4 (rows whose K fits one warp, KS == 1): four plain rows, or two output rows of a GLU pair (gate0, up0, gate1, up1).
+//            The kernel is issue-bound: the per-pass bookkeeping, the shuffle reduction (6 shuffles for 4 rows instead of 12) and
+//            the epilogue are paid once per four rows.
+//   RB = 2 (KS > 1): two plain rows, or the gate row and the up row of ONE output row; the KS warps of the group meet at a
+//            named barrier of their own and warp ks == 0 sums their values in fixed order.
+// The row sums of a pass are reduced TOGETHER: every exchange halves the number of values a lane carries, so the totals land
+// in lanes 0..RB-1, which then run the epilogue of "their" row.  Results are bit-deterministic (fixed order, no atomics).
+template <int TYPE, int SPW, int RB, bool COHERENT, bool PEER>
 __device__ __forceinline__ void consume_segment(const gs_params & p, const gs_ctx & c, const gs_phase & ph, const gs_seg & sg, int r0, int r1, gs_pos & pos, int warp, int lane) {
-    static_assert(GS_RB == 2, "the paired reduction below is written for two rows per pass");
-    const int KS = sg.KS, ksl = 31 - __clz(KS), ks = warp & (KS - 1), rg = warp >> ksl, RG = GS_NW >> ksl;
+    static_assert(RB == 2 || RB == 4, "passes of two or four rows");
+    const int KS = RB == 4 ? 1 : sg.KS, ksl = 31 - __clz(KS), ks = warp & (KS - 1), rg = warp >> ksl, RG = GS_NW >> ksl;
     item<TYPE> itm[SPW];
 #pragma unroll
     for (int s = 0; s < SPW; ++s) itm[s].init((ks + s * KS) * 32 + lane, sg.ipr, c.aq, c.ads);
     const int rb = sg.rb, R = sg.R;
     const bool pair = sg.nsub == 2;
-    int off = 0;                                           // row group that gets the first row of the current chunk
+    const int opp = pair ? RB / 2 : RB;                    // output rows per pass
+    int off = 0;                                           // row group that gets the first pass of the current chunk
     uint32_t ga0 = (uint32_t) ((uintptr_t) (sg.w[0] + (int64_t) r0 * rb) & 15);
     uint32_t ga1 = pair ? (uint32_t) ((uintptr_t) (sg.w[1] + (int64_t) r0 * rb) & 15) : 0u;
     const uint32_t gstep = (uint32_t) R * (uint32_t) rb;
     gs_shared & sh = *c.sh;
-    const volatile gs_seg & vs = sg;                       // epilogue fields are re-read where they are used (two lanes per pass):
+    const volatile gs_seg & vs = sg;                       // epilogue fields are re-read where they are used (few lanes per pass):
                                                            // hoisted into registers they cost more in the dot-product loops
-    const bool epi = ks == 0 && lane < GS_RB;
+    // output row (relative to the pass) whose epilogue this lane runs: the paired reduction leaves row j in lane perm(j)
+    //   RB = 2: lane 0 -> row 0, lane 1 -> row 1;   RB = 4: lane 0 -> row 0, lane 1 -> row 2, lane 2 -> row 1, lane 3 -> row 3
+    // GLU pair: rows are (gate, up) per output: RB = 2: lane 0 owns the output; RB = 4: lanes 0 / 1 own outputs 0 / 1 (up in lanes 2 / 3)
+    const int myj = RB == 2 ? lane : (pair ? lane : ((lane & 1) << 1) | ((lane >> 1) & 1));
+    const bool epi = ks == 0 && lane < opp;
     int par = 0;
     for (int row = r0; row < r1; row += R) {
         const int nr = min(R, r1 - row);
         const uint8_t * sub0 = c.ring + pos.st * c.stage_stride + ga0;
         const uint8_t * sub1 = sub0 - ga0 + ((ga0 + (uint32_t) nr * rb + 15u) & ~15u) + ga1;
-        if ((c.flags & 4) && warp == 0 && lane == 0 && p.dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) {
-            // debug: time warp 0 spends waiting for weight bytes, and the chunks it saw ([3] ns, [4] chunks)
-            const unsigned long long t0 = gs_now();
-            mbar_wait(&sh.full[pos.st], pos.full_par);
-            unsigned long long * dd = p.dbg + (ph.self_tag * 2 + (blockIdx.x ? 1 : 0)) * 8;
-            dd[3] += gs_now() - t0; dd[4] += 1;
-        } else
         mbar_wait(&sh.full[pos.st], pos.full_par);
-        // passes of this chunk ((gate, up) of one output row, or two consecutive plain rows) are dealt round-robin to the row
-        // groups, starting one group further every chunk
-        const int npass = pair ? nr : (nr + 1) >> 1;
+        const int npass = (nr + opp - 1) / opp;
         int first = rg - off; if (first < 0) first += RG;
         off += npass; while (off >= RG) off -= RG;
         for (int q = first; q < npass; q += RG) {
-            // rows of this pass; an odd last row is computed alone (the kernel is issue-bound: a duplicate row computed and
-            // dropped costs what a real one does)
-            const int jb = pair ? q : 2 * q;
-            const int j1 = pair ? jb : (jb + 1 < nr ? jb + 1 : jb);
-            const bool two = pair || j1 != jb;             // warp-uniform
-            const uint8_t * rowp[GS_RB];
-            rowp[0] = sub0 + jb * rb; rowp[1] = (pair ? sub1 : sub0) + j1 * rb;
-            const int my = lane == 0 ? jb : j1;            // the row whose epilogue this lane runs
-            const bool live = epi && (lane == 0 || (!pair && j1 != jb));
+            const int ob = q * opp;                        // first output row of the pass (relative to the chunk)
+            const int cnt = min(opp, nr - ob);             // output rows of this pass (warp-uniform)
+            const uint8_t * rowp[RB];
+            if (pair) {
+#pragma unroll
+                for (int j = 0; j < RB / 2; ++j) {
+                    const int o = ob + (j < cnt ? j : 0);
+                    rowp[2 * j] = sub0 + o * rb; rowp[2 * j + 1] = sub1 + o * rb;
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < RB; ++j) rowp[j] = sub0 + (ob + (j < cnt ? j : 0)) * rb;
+            }
+            const int my = ob + myj;                       // the output row whose epilogue this lane runs
+            const bool live = epi && myj < cnt;
             float bv = 0.0f; unsigned long long bw = 0ull;      // epilogue operand, requested before the dot products
             if (live && vs.bias) {
                 if (COHERENT && vs.bias_ll) bw = ll_load1<PEER>((const unsigned long long *) vs.bias_ll + row + my);
                 else bv = COHERENT ? __ldcg((const float *) vs.bias + row + my) : ((const float *) vs.bias)[row + my];
             }
-            float acc[GS_RB] = {0.0f, 0.0f};
+            float acc[RB];
+#pragma unroll
+            for (int j = 0; j < RB; ++j) acc[j] = 0.0f;
             if (!(c.flags & 1)) {
-                if (two) {
+                // a short last pass computes only the rows it has (the kernel is issue-bound: a duplicate row computed and
+                // dropped costs what a real one does)
+                const int nrows = pair ? 2 * cnt : cnt;    // warp-uniform
+                if (RB == 4 && nrows > 2) {
 #pragma unroll
                     for (int s = 0; s < SPW; ++s)
-                        if (itm[s].ok) itm[s].template dot<GS_RB>(rowp, acc);
+                        if (itm[s].ok) itm[s].template dot<RB>(rowp, acc);
+                } else if (nrows >= 2) {
+#pragma unroll
+                    for (int s = 0; s < SPW; ++s)
+                        if (itm[s].ok) itm[s].template dot<2>(rowp, acc);
                 } else {
 #pragma unroll
                     for (int s = 0; s < SPW; ++s)
                         if (itm[s].ok) itm[s].template dot<1>(rowp, acc);
                 }
             }
-            // paired reduction: even lanes end with the total of row 0, odd lanes with the total of row 1
-            float v = (lane & 1) ? acc[1] : acc[0];
-            v += __shfl_xor_sync(0xffffffffu, (lane & 1) ? acc[0] : acc[1], 1);
+            float v;
+            if (RB == 2) {
+                // even lanes end with the total of row 0, odd lanes with the total of row 1
+                v = (lane & 1) ? acc[1] : acc[0];
+                v += __shfl_xor_sync(0xffffffffu, (lane & 1) ? acc[0] : acc[1], 1);
 #pragma unroll
-            for (int o = 2; o < 32; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-            if (KS > 1) {
-                if (lane < GS_RB) sh.slots[par][warp][lane] = v;
+                for (int o = 2; o < 32; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            } else {
+                // lanes with bit 0 clear keep rows 0, 1, the others rows 2, 3; then bit 1 selects within the pair
+                const bool b0 = lane & 1, b1 = lane & 2;
+                float x0 = b0 ? acc[RB - 2] : acc[0], x1 = b0 ? acc[RB - 1] : acc[1];
+                x0 += __shfl_xor_sync(0xffffffffu, b0 ? acc[0] : acc[RB - 2], 1);
+                x1 += __shfl_xor_sync(0xffffffffu, b0 ? acc[1] : acc[RB - 1], 1);
+                v = b1 ? x1 : x0;
+                v += __shfl_xor_sync(0xffffffffu, b1 ? x0 : x1, 2);
+#pragma unroll
+                for (int o = 4; o < 32; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                // lane l (0..3) now holds row ((l & 1) << 1) | (l >> 1): 0, 2, 1, 3
+            }
+            if (RB == 2 && KS > 1) {
+                if (lane < RB) sh.slots[par][warp][lane] = v;
                 named_bar_sync(4 + rg, KS * 32);
-                if (epi) {
+                if (ks == 0 && lane < RB) {
                     float t = 0.0f;
                     for (int k = 0; k < KS; ++k) t += sh.slots[par][warp + k][lane];
                     v = t;
                 }
                 par ^= 1;
             }
-            if (pair) {                                    // lane 0: gate total, lane 1: up total
-                const float up = __shfl_sync(0xffffffffu, v, 1);
+            if (pair) {
+                // RB = 2: lane 0 gate, lane 1 up.  RB = 4: rows (gate0, up0, gate1, up1) sit in lanes (0, 2, 1, 3)
+                const float up = RB == 2 ? __shfl_sync(0xffffffffu, v, 1) : __shfl_down_sync(0xffffffffu, v, 2);
                 if (live) v = gs_glu(ph.glu_op, v, up, ph.glu_alpha, ph.glu_limit);
             }
             if (live) {
@@ -601,10 +631,17 @@ __device__ __forceinline__ void consume_segment(const gs_params & p, const gs_ct
 
 template <int TYPE, bool COHERENT, bool PEER>
 __device__ __forceinline__ void consume_dispatch(const gs_params & p, const gs_ctx & c, const gs_phase & ph, const gs_seg & sg, int r0, int r1, gs_pos & pos, int warp, int lane) {
-    if (sg.spw == 1)      consume_segment<TYPE, 1, COHERENT, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
-    else if (sg.spw == 2) consume_segment<TYPE, 2, COHERENT, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
+    if (sg.KS == 1) {                                      // one warp per row: passes of four rows
+        if (sg.spw == 1)      consume_segment<TYPE, 1, 4, COHERENT, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
+        else if (sg.spw == 2) consume_segment<TYPE, 2, 4, COHERENT, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
+        else if (item<TYPE>::max_spw >= 4)
+            consume_segment<TYPE, (item<TYPE>::max_spw >= 4 ? 4 : 1), 4, COHERENT, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
+        return;
+    }
+    if (sg.spw == 1)      consume_segment<TYPE, 1, 2, COHERENT, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
+    else if (sg.spw == 2) consume_segment<TYPE, 2, 2, COHERENT, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
     else if (item<TYPE>::max_spw >= 4)
-        consume_segment<TYPE, (item<TYPE>::max_spw >= 4 ? 4 : 1), COHERENT, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
+        consume_segment<TYPE, (item<TYPE>::max_spw >= 4 ? 4 : 1), 2, COHERENT, PEER>(p, c, ph, sg, r0, r1, pos, warp, lane);
 }
 
 #define GS_STAMP(ip, k) do { if (p.dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) \
