@@ -165,6 +165,8 @@ B200_API void         b200_chain_destroy(b200_chain * chain);
  * stamps of the first and last CTA (tools/timeline_chain.py), bit 3 publish a phase with __threadfence in every thread before
  * the CTA barrier instead of one release RED by thread 0 after it, bits 4-7 ring depth, bits 8-15 stage KiB */
 B200_API int          b200_chain_debug_read(b200_chain * chain, unsigned long long * out, int n_phases);
+/* same flag: %globaltimer of EVERY CTA when it entered a phase and when its rows were consumed: out[n_phases][b200_chain_grid()][2] */
+B200_API int          b200_chain_debug_read_ctas(b200_chain * chain, unsigned long long * out, int n_phases);
 
 /* ---- row split across GPUs: the decode chain over NVLink peer memory --------------------------------
  * Replaces the reference's row-split matmul (ggml-cuda.cu:791-804 get_row_split, :1497-1700 ggml_cuda_op_mul_mat:

@@ -484,8 +484,10 @@ static b200_chain * gs_chain_create(const b200_phase * phases_in, int n_phases, 
     ch->p.act_qs_bytes = cfg.act_qs; ch->p.stage_stride = cfg.stage_payload + GS_STAGE_SLACK; ch->p.n_stages = cfg.n_stages;
     ch->p.attn_floats = cfg.attn_floats; ch->p.flags = flags;
     if (flags & 4) {
-        if (cudaMalloc((void **) &ch->d_dbg, sizeof(unsigned long long) * 16 * (size_t) n_phases) == cudaSuccess)
-            cudaMemset(ch->d_dbg, 0, sizeof(unsigned long long) * 16 * (size_t) n_phases);
+        // [n_phases][2][8] stamps of CTA 0 / the last CTA, then [n_phases][grid][2] (phase entered, rows consumed) of every CTA
+        const size_t n64 = (16 + 2 * (size_t) grid) * (size_t) n_phases;
+        if (cudaMalloc((void **) &ch->d_dbg, sizeof(unsigned long long) * n64) == cudaSuccess)
+            cudaMemset(ch->d_dbg, 0, sizeof(unsigned long long) * n64);
         ch->p.dbg = ch->d_dbg;
     }
     ch->smem = cfg.smem; ch->grid = grid; ch->t0 = types[0]; ch->t1 = types[1];
@@ -541,6 +543,13 @@ extern "C" int b200_chain_launch(b200_chain * ch, void * stream) {
 extern "C" int b200_chain_debug_read(b200_chain * ch, unsigned long long * out, int n_phases) {
     if (!ch || !ch->d_dbg || n_phases > ch->p.n_phases) return B200_ERR_ARG;
     B200_CUDA_TRY(cudaMemcpy(out, ch->d_dbg, sizeof(unsigned long long) * 16 * (size_t) n_phases, cudaMemcpyDeviceToHost));
+    return B200_OK;
+}
+
+// debug (flags bit 2): %globaltimer of every CTA at [phase][cta][phase entered | rows consumed]
+extern "C" int b200_chain_debug_read_ctas(b200_chain * ch, unsigned long long * out, int n_phases) {
+    if (!ch || !ch->d_dbg || n_phases > ch->p.n_phases) return B200_ERR_ARG;
+    B200_CUDA_TRY(cudaMemcpy(out, ch->d_dbg + 16 * (size_t) ch->p.n_phases, sizeof(unsigned long long) * 2 * (size_t) ch->grid * (size_t) n_phases, cudaMemcpyDeviceToHost));
     return B200_OK;
 }
 

@@ -29,7 +29,7 @@ constexpr int GS_STAGE_BYTES = 56 * 1024;              // preferred stage payloa
 constexpr int GS_STAGE_SLACK = 128;                    // slack for 16 B alignment of both ends / funnel over-read
 constexpr int GS_RED_FLOATS  = 2304;                   // per parity: rows * (KS*32 + 4) <= GS_RED_FLOATS
 constexpr int GS_SMEM_MAX    = 220 * 1024;             // dynamic; ~3 KB of static shared memory on top
-constexpr int GS_RB          = 2;                      // rows per warp pass (two independent dp4a chains)
+constexpr int GS_RB          = 2;                      // rows per warp pass of the K-split segments (KS > 1); KS == 1 segments run passes of four
 constexpr int GS_MAX_PHASES  = 1024;
 
 // Inside a chain every value a later phase reads travels as a TAGGED WORD {f32 bits, tag of (launch, producing phase)} in a
@@ -160,23 +160,38 @@ __device__ __forceinline__ void ll_spin_check(unsigned int & spins, unsigned lon
         if (!t0) t0 = now; else if (now - t0 > 20000000000ull) __trap();          // 20 s
     }
 }
+// The spins are out of line (one copy per kernel): the callers' fast path is "load, compare the tag, done".  Code size matters
+// here: the chain kernel runs a different stretch of code in every phase, and what does not fit the instruction cache is
+// fetched again at every phase boundary, on the critical path.
+template <bool SYS>
+__device__ __noinline__ unsigned long long ll_spin1(const void * p, unsigned int tag) {
+    unsigned int spins = 0; unsigned long long t0 = 0;
+    unsigned long long w = ll_load1<SYS>(p);
+    while (!ll_ok(w, tag)) { ll_spin_check(spins, t0); w = ll_load1<SYS>(p); }
+    return w;
+}
 template <bool SYS>
 __device__ __forceinline__ float ll_settle1(unsigned long long w, const void * p, unsigned int tag) {
-    unsigned int spins = 0; unsigned long long t0 = 0;
-    while (!ll_ok(w, tag)) { ll_spin_check(spins, t0); w = ll_load1<SYS>(p); }
+    if (!ll_ok(w, tag)) w = ll_spin1<SYS>(p, tag);
     return __uint_as_float((unsigned int) w);
 }
 template <bool SYS>
 __device__ __forceinline__ float ll_read(const void * p, unsigned int tag) { return ll_settle1<SYS>(ll_load1<SYS>(p), p, tag); }
 template <bool SYS>
-__device__ __forceinline__ void ll_settle2(ulonglong2 & a, const void * p, unsigned int tag) {
+__device__ __noinline__ ulonglong2 ll_spin2(const void * p, unsigned int tag) {
     unsigned int spins = 0; unsigned long long t0 = 0;
+    ulonglong2 a = ll_load2<SYS>(p);
     while (!ll_ok(a.x, tag) || !ll_ok(a.y, tag)) { ll_spin_check(spins, t0); a = ll_load2<SYS>(p); }
+    return a;
+}
+template <bool SYS>
+__device__ __forceinline__ void ll_settle2(ulonglong2 & a, const void * p, unsigned int tag) {
+    if (!ll_ok(a.x, tag) || !ll_ok(a.y, tag)) a = ll_spin2<SYS>(p, tag);
 }
 // one lane waits (with back-off) until the word at p carries `tag`: the gate in front of a many-thread read, so that CTAs
 // waiting for a phase to finish do not flood L2 with retries
 template <bool SYS>
-__device__ __forceinline__ void ll_gate(const void * p, unsigned int tag) {
+__device__ __noinline__ void ll_gate(const void * p, unsigned int tag) {
     unsigned int spins = 0; unsigned long long t0 = 0;
     while (!ll_ok(ll_load1<SYS>(p), tag)) { ll_spin_check(spins, t0); __nanosleep(100); }
 }
@@ -398,7 +413,7 @@ template <> struct item<B200_MXFP4> {
     }
 };
 
-__device__ __forceinline__ float gs_glu(int op, float g, float x, float alpha, float limit) {
+static __device__ __noinline__ float gs_glu(int op, float g, float x, float alpha, float limit) {      // one or two lanes per pass: one copy
     switch (op) {
         case B200_GLU_REGLU:  return fmaxf(g, 0.0f) * x;
         case B200_GLU_GEGLU: { const float c = 0.79788456080286535587989211986876f, a = 0.044715f;
@@ -411,6 +426,9 @@ __device__ __forceinline__ float gs_glu(int op, float g, float x, float alpha, f
     }
 }
 
+// debug stamps: the SM's cycle counter.  (%globaltimer costs ~0.3 us per read on B200: five stamps per phase made the stamped
+// CTAs the slowest of the grid.)  Stamps of one CTA are comparable with each other, not across CTAs.
+__device__ __forceinline__ unsigned long long gs_clk() { return (unsigned long long) clock64(); }
 __device__ __forceinline__ unsigned long long gs_now() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -565,22 +583,11 @@ __device__ __forceinline__ void consume_segment(const gs_params & p, const gs_ct
 #pragma unroll
             for (int j = 0; j < RB; ++j) acc[j] = 0.0f;
             if (!(c.flags & 1)) {
-                // a short last pass computes only the rows it has (the kernel is issue-bound: a duplicate row computed and
-                // dropped costs what a real one does)
-                const int nrows = pair ? 2 * cnt : cnt;    // warp-uniform
-                if (RB == 4 && nrows > 2) {
+                // a short last pass computes duplicates of its first row and drops them: one copy of the dot-product code per
+                // variant (code that is not executed still spreads the hot code over more instruction-cache lines)
 #pragma unroll
-                    for (int s = 0; s < SPW; ++s)
-                        if (itm[s].ok) itm[s].template dot<RB>(rowp, acc);
-                } else if (nrows >= 2) {
-#pragma unroll
-                    for (int s = 0; s < SPW; ++s)
-                        if (itm[s].ok) itm[s].template dot<2>(rowp, acc);
-                } else {
-#pragma unroll
-                    for (int s = 0; s < SPW; ++s)
-                        if (itm[s].ok) itm[s].template dot<1>(rowp, acc);
-                }
+                for (int s = 0; s < SPW; ++s)
+                    if (itm[s].ok) itm[s].template dot<RB>(rowp, acc);
             }
             float v;
             if (RB == 2) {
@@ -645,9 +652,9 @@ __device__ __forceinline__ void consume_dispatch(const gs_params & p, const gs_c
 }
 
 #define GS_STAMP(ip, k) do { if (p.dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) \
-    p.dbg[((ip) * 2 + (blockIdx.x ? 1 : 0)) * 8 + (k)] = gs_now(); } while (0)
+    p.dbg[((ip) * 2 + (blockIdx.x ? 1 : 0)) * 8 + (k)] = gs_clk(); } while (0)
 #define GS_STAMP_MAX(ip, k) do { if (p.dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) \
-    atomicMax(p.dbg + ((ip) * 2 + (blockIdx.x ? 1 : 0)) * 8 + (k), gs_now()); } while (0)
+    atomicMax(p.dbg + ((ip) * 2 + (blockIdx.x ? 1 : 0)) * 8 + (k), gs_clk()); } while (0)
 
 // ---------------------------------------------------------------- phase pieces
 // prologue of a GEMV phase (consumers + finalizer): x -> [rms norm * w] -> q8_1 in shared memory.
@@ -795,7 +802,7 @@ __device__ __forceinline__ float gs_attn_ld(const float * base, const unsigned l
     return ll ? ll_read<PEER>(ll + i, tag) : __ldcg(base + i);
 }
 template <int D, bool PEER>
-__device__ __forceinline__ void gs_attn_item(unsigned int ltag, unsigned int self_tag, const gs_attn & a, int h, float * sm, int warp, int lane) {
+__device__ __noinline__ void gs_attn_item(unsigned int ltag, unsigned int self_tag, const gs_attn & a, int h, float * sm, int warp, int lane) {
     constexpr int LPP = D / 32, PPB = 32 / LPP, DPL = D / 32;     // lanes per position, positions per batch, dims per lane (V)
     const int tid = warp * 32 + lane;
     const int gqa = a.H / a.H_kv, g = h / gqa;
@@ -977,7 +984,7 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
     c.ring = smem;                                                            // n_stages x stage_stride
     c.aq   = smem + p.n_stages * p.stage_stride;                              // activation int8, padded layout
     c.ads  = (float2 *) (c.aq + p.act_qs_bytes);                              // (d, d*sum) per unit; sized with act_qs_bytes/4
-    c.attn = (float *) ((uint8_t *) c.ads + (p.act_qs_bytes >> 2) + 64);      // attention scratch
+    c.attn = (float *) (((uintptr_t) ((uint8_t *) c.ads + (p.act_qs_bytes >> 2) + 64) + 15) & ~(uintptr_t) 15);   // attention scratch (read as float4)
     c.sh = &sh; c.stage_stride = p.stage_stride; c.flags = p.flags;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -1015,7 +1022,7 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
                 mbar_wait(&sh.empty[pos.st], pos.full_par ^ 1);
                 if ((p.flags & 4) && p.dbg && wt.row == wt_first_row(wt, s_pp) && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) {
                     unsigned long long * dd = p.dbg + (wt.ip * 2 + (blockIdx.x ? 1 : 0)) * 8;
-                    if (!dd[7]) dd[7] = gs_now();                  // debug: when the FIRST chunk of this phase was requested
+                    if (!dd[7]) dd[7] = gs_clk();                  // debug: when the FIRST chunk of this phase was requested
                 }
                 uint8_t * dstp = c.ring + pos.st * p.stage_stride;
                 const uintptr_t g0 = (uintptr_t) (sg.w[0] + (int64_t) wt.row * sg.rb);
@@ -1052,6 +1059,7 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
         named_bar_sync(1, GS_CON_THREADS);                         // descriptor staged; every warp has left phase ip - 1
         if (!CHAIN) { gs_stage_ranges(s_rng[0], &ph, nullptr, 0, blockIdx.x, gridDim.x, tid); named_bar_sync(1, GS_CON_THREADS); }
         if (CHAIN && tid == 0) GS_STAMP(ip, 0);
+        if (CHAIN && tid == 0 && p.dbg) p.dbg[16 * (size_t) n_phases + ((size_t) ip * gridDim.x + blockIdx.x) * 2] = gs_now();
         if (ph.kind == 0) {
             gs_prologue<CHAIN, PEER>(p, c, ph, warp, lane);
             if (CHAIN && tid == 0) GS_STAMP(ip, 1);
@@ -1064,11 +1072,13 @@ __global__ void __launch_bounds__(GS_THREADS, 1) gemv_stream_kernel(const __grid
             }
         } else if (CHAIN && ph.kind == 1) {
             for (int h = blockIdx.x; h < ph.attn.H; h += gridDim.x) {
+                unsigned long long * dbg = p.dbg && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1) ? p.dbg + (ip * 2 + (blockIdx.x ? 1 : 0)) * 8 : nullptr;
                 if (ph.attn.D == 128) gs_attn_item<128, PEER>(sh.tag, ph.self_tag, ph.attn, h, c.attn, warp, lane);
                 else                  gs_attn_item<64, PEER>(sh.tag, ph.self_tag, ph.attn, h, c.attn, warp, lane);
             }
         }
         if (CHAIN && tid == 0) GS_STAMP(ip, 2);
+        if (CHAIN && tid == 0 && p.dbg) p.dbg[16 * (size_t) n_phases + ((size_t) ip * gridDim.x + blockIdx.x) * 2 + 1] = gs_now();
         if (PEER && ph.peer_mode == 2) {
             // outputs read after the launch (the logits) went to the other ranks as plain stores: CTA barrier, one
             // system-scope fence, then the arrival is counted on every rank

@@ -22,7 +22,8 @@ out = np.zeros(n * 16, np.uint64)
 L = capi.lib()
 L.b200_chain_debug_read.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
 assert L.b200_chain_debug_read(sess.chain.h, out.ctypes.data_as(C.c_void_p), n) == 0
-d = out.reshape(n, 2, 8).astype(np.int64)
+# stamps are SM cycle counters (clock64): converted to ns at the SM clock the bench reports under load (1965 MHz)
+d = (out.reshape(n, 2, 8).astype(np.float64) / 1.965).astype(np.int64)
 # stamps per phase and CTA (0 = CTA 0, 1 = last CTA): [0] phase entered (descriptor staged, every warp of the CTA has left the
 # previous phase), [5] inputs present (tagged words settled: the dependency wait + the L2 round trip), [6] normalised + quantised,
 # [1] prologue done (CTA barrier), [2] rows consumed (warp 0)
@@ -36,6 +37,9 @@ for cta in (0, 1):
         a1 = a[1] if a[1] else a[0]
         s5 = a[5] if a[5] else a[0]
         s6 = a[6] if a[6] else a1
+        if nm == "attn" and a[5] and i == 6: print("attn stamps rel. to entry:", [int(x - a[0]) for x in (a[5], a[3], a[4], a[6], a[2])])
+        if nm == "attn" and a[5]:      # attention: [5] q/k/v present and rotated, [6] warp 0 through its positions
+            a1 = a[6]; s6 = a[5]       # columns: wait+load = inputs, norm+quant = positions, consume = combine + store
         nxt = d[i + 1, cta, 0] if i + 1 < n else a[2]
         # [3] ns warp 0 waited for weight bytes, [4] chunks it consumed, [7] when the producer requested the phase's first chunk
         lead = (a[0] - a[7]) if a[7] else 0
