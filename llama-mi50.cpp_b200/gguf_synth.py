@@ -109,6 +109,30 @@ def sample_q6_k(rng: np.random.Generator, n_blocks: int, sigma: float) -> np.nda
     return out.reshape(-1)
 
 
+def sample_q8_0(rng: np.random.Generator, n_blocks: int, sigma: float) -> np.ndarray:
+    """Random valid q8_0 blocks (large tensors only: drawing and quantising 35 G normals took 9 minutes for the Qwen2.5-32B
+    shape): quants uniform in [-127, 127] (std 73), d such that std(w) = sigma."""
+    out = rng.integers(0, 256, size=(n_blocks, 34), dtype=np.uint8)
+    q = out[:, 2:].view(np.int8)
+    q[q == -128] = 0
+    d = (sigma / 73.0) * (0.75 + 0.5 * rng.random(n_blocks, dtype=np.float32))
+    out[:, 0:2] = d.astype(np.float16).view(np.uint8).reshape(-1, 2)
+    return out.reshape(-1)
+
+
+def sample_mxfp4(rng: np.random.Generator, n_blocks: int, sigma: float) -> np.ndarray:
+    """Random valid mxfp4 blocks: nibbles uniform (|kvalue| mean-square 34.25 -> std 5.85 in units of 2^(e-128)), e chosen per
+    tensor so that std(w) ~ sigma, +-1 per block."""
+    out = rng.integers(0, 256, size=(n_blocks, 17), dtype=np.uint8)
+    e0 = int(round(128 + np.log2(max(sigma, 1e-12) / 5.85)))
+    out[:, 0] = np.clip(e0 + rng.integers(-1, 2, size=n_blocks), 1, 254).astype(np.uint8)
+    return out.reshape(-1)
+
+
+SAMPLE_FROM = 1 << 26      # elements: tensors at least this large are sampled in the packed domain (throughput does not depend on
+                           # the values; the exact quantizers stay the reference for tests and small tensors)
+
+
 def make_tensor_bytes(rng: np.random.Generator, ttype: int, ne, sigma: float = 0.02, value: float | None = None) -> np.ndarray:
     """Packed bytes of a random-init tensor with ggml shape `ne` (ne[0] fastest)."""
     n = int(np.prod(ne))
@@ -123,6 +147,18 @@ def make_tensor_bytes(rng: np.random.Generator, ttype: int, ne, sigma: float = 0
         return sample_q4_k(rng, nb, sigma)
     if ttype == Q6_K:
         return sample_q6_k(rng, nb, sigma)
+    if n >= SAMPLE_FROM and ttype in (Q8_0, MXFP4):
+        # a pool of 4 M random valid blocks, laid down repeatedly at random rotations (the generator delivers ~0.3 GB/s; a
+        # 63 GB model would take minutes of GPU-box time for values nothing depends on)
+        fn = sample_q8_0 if ttype == Q8_0 else sample_mxfp4
+        pool_blocks = min(nb, 1 << 22)
+        pool = fn(rng, pool_blocks, sigma).reshape(pool_blocks, bb)
+        out = np.empty((nb, bb), np.uint8)
+        for b0 in range(0, nb, pool_blocks):
+            b1 = min(nb, b0 + pool_blocks)
+            r = int(rng.integers(0, pool_blocks))
+            out[b0:b1] = np.roll(pool, r, axis=0)[:b1 - b0] if r else pool[:b1 - b0]
+        return out.reshape(-1)
     out = np.empty(nb * bb, np.uint8)
     step = 1 << 20  # blocks per chunk, bounds the f32 temporary
     fn = {Q4_0: quantize_q4_0, Q8_0: quantize_q8_0, MXFP4: quantize_mxfp4}[ttype]
@@ -171,7 +207,15 @@ SHAPES = {
     "llama3-8b-q4_k_m": ModelShape("llama3-8b", "llama", 32, 4096, 14336, 32, 8, 128, 128256, "q4_k_m", extra=_DEEP),
     "qwen2.5-32b-q8_0": ModelShape("qwen2.5-32b", "qwen2", 64, 5120, 27648, 40, 8, 128, 152064, "q8_0", 32768, 1000000.0, 1e-6, qkv_bias=True, extra=_DEEP),
     "llama3-70b-q4_k_m": ModelShape("llama3-70b", "llama", 80, 8192, 28672, 64, 8, 128, 128256, "q4_k_m", extra=_DEEP),
+    # gpt-oss-120b (reference src/models/openai-moe-iswa.cpp, src/llama-model.cpp:2262-2280, 6570-6609): 36 layers, 128 experts / 4
+    # used, expert FFN 2880, sliding window 128 on every other layer, attention sinks, biases everywhere; experts MXFP4, the rest
+    # Q8_0 (ftype MXFP4_MOE).  YaRN (factor 32 over 4096) as the released model has it.
+    "gpt-oss-120b-mxfp4": ModelShape("gpt-oss-120b", "gpt-oss", 36, 2880, 2880, 64, 8, 64, 201088, "mxfp4_moe", 131072, 150000.0, 1e-5,
+                                      n_expert=128, n_expert_used=4, swa=128, qkv_bias=True,
+                                      extra={**_DEEP, "yarn_factor": 32.0, "yarn_orig_ctx": 4096}),
     # test-size models (same graph topology, seconds on a CPU)
+    "tiny-moe-mxfp4": ModelShape("tiny-moe", "gpt-oss", 2, 256, 256, 8, 2, 32, 512, "mxfp4_moe", 512, 10000.0, 1e-5,
+                                  n_expert=8, n_expert_used=2, swa=64, qkv_bias=True),
     "tiny-q4_0": ModelShape("tiny", "llama", 2, 256, 512, 4, 2, 64, 512, "q4_0", 512, 10000.0),
     "tiny-q4_k_m": ModelShape("tiny-k", "llama", 4, 512, 1024, 8, 2, 64, 1024, "q4_k_m", 512, 10000.0),
     "tiny-q8_0": ModelShape("tiny-q8", "qwen2", 2, 256, 512, 4, 2, 64, 512, "q8_0", 512, 10000.0, 1e-6, qkv_bias=True),
@@ -184,6 +228,8 @@ def use_more_bits(i_layer: int, n_layers: int) -> bool:
 
 def tensor_plan(s: ModelShape):
     """[(name, ggml_type, ne)] in file order; the weight-type mix of the ftype."""
+    if s.arch == "gpt-oss":
+        return tensor_plan_gpt_oss(s)
     base = {"q4_0": Q4_0, "q8_0": Q8_0, "q4_k_m": Q4_K}[s.ftype]
     out_t = {"q4_0": Q6_K, "q8_0": Q8_0, "q4_k_m": Q6_K}[s.ftype]
     E, F, KVD, QD = s.n_embd, s.n_ff, s.n_head_kv * s.head_dim, s.n_head * s.head_dim
@@ -210,12 +256,46 @@ def tensor_plan(s: ModelShape):
     return plan
 
 
+def tensor_plan_gpt_oss(s: ModelShape):
+    """gpt-oss (reference src/llama-model.cpp:6570-6609): expert tensors MXFP4 [K, M, n_expert], everything else Q8_0 / F32."""
+    E, F, KVD, QD, X = s.n_embd, s.n_ff, s.n_head_kv * s.head_dim, s.n_head * s.head_dim, s.n_expert
+    plan = [("token_embd.weight", Q8_0, (E, s.n_vocab))]
+    for i in range(s.n_layer):
+        p = f"blk.{i}."
+        plan += [(p + "attn_norm.weight", F32, (E,)),
+                 (p + "attn_q.weight", Q8_0, (E, QD)), (p + "attn_q.bias", F32, (QD,)),
+                 (p + "attn_k.weight", Q8_0, (E, KVD)), (p + "attn_k.bias", F32, (KVD,)),
+                 (p + "attn_v.weight", Q8_0, (E, KVD)), (p + "attn_v.bias", F32, (KVD,)),
+                 (p + "attn_output.weight", Q8_0, (QD, E)), (p + "attn_output.bias", F32, (E,)),
+                 (p + "attn_sinks.weight", F32, (s.n_head,)),
+                 (p + "post_attention_norm.weight", F32, (E,)),
+                 (p + "ffn_gate_inp.weight", F32, (E, X)), (p + "ffn_gate_inp.bias", F32, (X,)),
+                 (p + "ffn_gate_exps.weight", MXFP4, (E, F, X)), (p + "ffn_gate_exps.bias", F32, (F, X)),
+                 (p + "ffn_up_exps.weight", MXFP4, (E, F, X)), (p + "ffn_up_exps.bias", F32, (F, X)),
+                 (p + "ffn_down_exps.weight", MXFP4, (F, E, X)), (p + "ffn_down_exps.bias", F32, (E, X))]
+    plan += [("output_norm.weight", F32, (E,)), ("output.weight", Q8_0, (E, s.n_vocab))]
+    return plan
+
+
 def matmul_weight_bytes(s: ModelShape) -> int:
     """Algorithmic weight bytes read per generated token: every MUL_MAT weight once."""
     total = 0
     for name, t, ne in tensor_plan(s):
         if name.endswith(".weight") and len(ne) == 2 and name != "token_embd.weight":
             total += tensor_nbytes(t, ne)
+        elif name.endswith("_exps.weight"):                 # MUL_MAT_ID: the n_expert_used selected experts of n_expert
+            total += tensor_nbytes(t, ne) // ne[2] * s.n_expert_used
+    return total
+
+
+def matmul_weight_params(s: ModelShape) -> int:
+    """Weight elements of every MUL_MAT of one token (2 flop each): the prefill GEMM work per prompt token."""
+    total = 0
+    for name, t, ne in tensor_plan(s):
+        if name.endswith(".weight") and len(ne) == 2 and name != "token_embd.weight":
+            total += int(ne[0]) * int(ne[1])
+        elif name.endswith("_exps.weight"):
+            total += int(ne[0]) * int(ne[1]) * s.n_expert_used
     return total
 
 
@@ -273,6 +353,16 @@ def model_kv(s: ModelShape) -> dict:
     if s.n_head * s.head_dim != s.n_embd:
         kv[f"{a}.attention.key_length"] = s.head_dim
         kv[f"{a}.attention.value_length"] = s.head_dim
+    if s.n_expert:
+        kv[f"{a}.expert_count"] = s.n_expert
+        kv[f"{a}.expert_used_count"] = s.n_expert_used
+        kv[f"{a}.expert_feed_forward_length"] = s.n_ff
+    if s.swa:
+        kv[f"{a}.attention.sliding_window"] = s.swa
+    if s.extra.get("yarn_factor"):
+        kv[f"{a}.rope.scaling.type"] = "yarn"
+        kv[f"{a}.rope.scaling.factor"] = float(s.extra["yarn_factor"])
+        kv[f"{a}.rope.scaling.original_context_length"] = int(s.extra["yarn_orig_ctx"])
     return kv
 
 

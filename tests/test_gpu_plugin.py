@@ -47,6 +47,23 @@ def test_plugin_row_split_matches_cpu_backend(key, tmp_path):
     assert "plugin-parity: PASS" in out.stdout
 
 
+def test_plugin_gpt_oss_moe_matches_cpu_backend(tmp_path):
+    """BASELINE.json configs[4] at test size: the gpt-oss graph (reference src/models/openai-moe-iswa.cpp: MXFP4 experts through
+    MUL_MAT_ID, softmax-weight top-k routing, ADD_ID expert biases, SWIGLU_OAI, attention sinks, sliding-window layers, q/k/v/o
+    biases) decodes on the plugin with every node on the device; logits of a 20-token prompt and 12 decode steps against the
+    CPU backend."""
+    exe = os.path.join(REF_DIR, "plugin-parity")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/plugin-parity not built")
+    from llama_mi50_b200 import gguf_synth as gs
+    path = str(tmp_path / "tiny-moe.gguf")
+    gs.write_gguf(path, gs.SHAPES["tiny-moe-mxfp4"])
+    env = dict(os.environ, GGML_B200_PRINT_STATS="1")
+    out = subprocess.run([exe, path, REF_DIR, PLUGIN, "20", "12", "2e-3"], capture_output=True, text=True, timeout=600, env=env)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
+    assert "plugin-parity: PASS" in out.stdout
+
+
 def _parity(path, n_prompt, n_decode, tol, env_extra=None, timeout=900):
     exe = os.path.join(REF_DIR, "plugin-parity")
     if not os.path.exists(exe):
