@@ -53,6 +53,15 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def tensor_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        if d.get("bf16_tflops_sustained"):
+            return float(d["bf16_tflops_sustained"]), "measured (MEASURED_PEAKS.json bf16_tflops_sustained)"
+    return 1400.0, "fallback (B200_PROFILING.md sustained bf16)"
+
+
 class ClockSampler(threading.Thread):
     """nvidia-smi clocks / throttle reasons sampled during the timed region."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -345,6 +354,16 @@ def main_b200(a):
                                "via": "reference llama-bench (-p 0 -n 128 -fa 1 -ngl 99) driving libggml-b200.so via GGML_BACKEND_PATH"}
                 line["llama_bench"] = {"tg128": round(tg_ts, 2), "pp512": round(pp["avg_ts"], 2), "backends": tg.get("backends"),
                                        "gpu_info": tg.get("gpu_info")}
+                # the prefill half of the metric: matmul flops per prompt token (2 per weight of every MUL_MAT; attention and glue
+                # are not counted) against the measured dense bf16 peak of this pool's B200s (the tensor-core GEMM multiplies
+                # 16-bit operands, csrc/kernels/mmq_tc.cu); the sustained figure, since the kernel runs inside a long step
+                flop_tok = 2.0 * gguf_synth.matmul_weight_params(shape)
+                tf_peak, tf_src = tensor_peak()
+                tflops = flop_tok * pp["avg_ts"] / 1e12
+                line["roofline_prefill"] = {"bound": "tensor", "kernel": "mmq_tc_kernel (tcgen05.mma kind::f16 over in-smem expanded GGUF blocks)",
+                                            "flops": flop_tok * 512, "flop_per_token": flop_tok, "achieved": round(tflops, 1), "peak": tf_peak,
+                                            "unit": "TFLOP/s", "frac": round(tflops / tf_peak, 4), "peak_source": tf_src,
+                                            "tok_s": round(pp["avg_ts"], 2), "via": "reference llama-bench pp512 driving the plugin"}
             line["cpu_baseline"] = cpu_baseline(gguf)
         except Exception as e:  # the C-ABI numbers above stand on their own
             line["llama_bench_error"] = str(e)[-400:]
