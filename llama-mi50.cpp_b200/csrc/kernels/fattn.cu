@@ -746,7 +746,11 @@ static bool fattn_use_dec_mma(const b200_fattn_args * a) {
     if (!on) return false;
     const b200_tensor & q = a->q; const b200_tensor & k = a->k; const b200_tensor & v = a->v;
     const int64_t D = q.ne[0], n_kv = k.ne[1];
-    if ((D != 64 && D != 128) || a->logit_softcap != 0.0f || a->max_bias != 0.0f || n_kv < 1024 || n_kv % 2) return false;
+    // from 1024 positions on; with four or more query columns per KV head (GQA) from 256 on: the vector kernel with 4-8 columns is
+    // ~8 k instructions of unrolled code that runs cold in every layer (the SM instruction cache holds ~32 KB): gpt-oss decode
+    // (gqa 8, 256 positions) spent 31 us per layer in it
+    const int64_t cols = q.ne[1] * (q.ne[2] / k.ne[2]);
+    if ((D != 64 && D != 128) || a->logit_softcap != 0.0f || a->max_bias != 0.0f || n_kv < (cols >= 4 ? 256 : 1024) || n_kv % 2) return false;
     if (k.type == B200_Q8_0) {
         if (((uintptr_t) k.data | (uintptr_t) v.data) % 4) return false;
         for (int i = 1; i < 4; ++i) if (k.nb[i] % 4 || v.nb[i] % 4) return false;

@@ -7,6 +7,7 @@
 #include <cuda_bf16.h>
 
 #include <mutex>
+#include <type_traits>
 
 #include "common.cuh"
 
@@ -20,16 +21,19 @@ namespace b200 {
 template <int ORDER>
 __global__ void __launch_bounds__(1024) argsort_kernel(const float * x, int32_t * dst, int n, int n_pad, int64_t x_row, int64_t d_row, int n_out) {
     extern __shared__ int32_t s_idx[];
+    float * s_val = (float *) (s_idx + n_pad);                   // the row itself: 28 compare steps at n = 128 would each go to global memory
     pdl_launch_dependents();
     const float * row = x + (int64_t) blockIdx.x * x_row;
     for (int i = threadIdx.x; i < n_pad; i += blockDim.x) s_idx[i] = i;
     pdl_wait();
+    const bool staged = n_pad <= 16384;                          // longer rows: indices alone fill the shared memory, values stay in global
+    if (staged) for (int i = threadIdx.x; i < n; i += blockDim.x) s_val[i] = row[i];
     __syncthreads();
     // a < b in the target order; indices >= n (padding) are larger than everything
     auto before = [&](int a, int b) {
         if (a >= n) return false;
         if (b >= n) return true;
-        const float va = row[a], vb = row[b];
+        const float va = staged ? s_val[a] : row[a], vb = staged ? s_val[b] : row[b];
         return ORDER == 0 ? va < vb : va > vb;
     };
     for (int k = 2; k <= n_pad; k <<= 1) {
@@ -59,7 +63,7 @@ static int argsort_common(const b200_tensor * x, const b200_tensor * d, int orde
     if (VALIDATE_ONLY(stream)) return B200_OK;
     if (rows == 0) return B200_OK;
     int n_pad = 1; while (n_pad < x->ne[0]) n_pad <<= 1;
-    const size_t smem = (size_t) n_pad * 4;
+    const size_t smem = (size_t) n_pad * (n_pad <= 16384 ? 8 : 4);      // indices (+ values)
     static std::once_flag once[64]; int dev = 0; B200_CUDA_TRY(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64) return B200_ERR_ARG;
     cudaError_t rc = cudaSuccess;
@@ -77,7 +81,9 @@ static int argsort_common(const b200_tensor * x, const b200_tensor * d, int orde
 
 // ------------------------------------------------------------------ ADD_ID: dst[:, e, t] = a[:, e, t] + b[:, ids[e, t]]
 __global__ void __launch_bounds__(256) add_id_kernel(const char * a, const char * b, const char * ids, char * d, int64_t ne0, int64_t ne1,
-                                                     int64_t a_nb1, int64_t a_nb2, int64_t b_nb1, int64_t i_nb0, int64_t i_nb1, int64_t d_nb1, int64_t d_nb2) {
+                                                     int64_t a_nb1, int64_t a_nb2, int64_t b_nb1, int64_t i_nb0, int64_t i_nb1, int64_t d_nb1, int64_t d_nb2, int vec) {
+    // one element group per thread (grid.y walks the row): a decode call is 4 rows of 2880 floats, and the bias rows come from
+    // HBM: one round trip instead of a dozen dependent ones
     pdl_launch_dependents();
     const int64_t e = blockIdx.x % ne1, t = blockIdx.x / ne1;
     pdl_wait();
@@ -85,7 +91,12 @@ __global__ void __launch_bounds__(256) add_id_kernel(const char * a, const char 
     const float * pa = (const float *) (a + e * a_nb1 + t * a_nb2);
     const float * pb = (const float *) (b + (int64_t) id * b_nb1);
     float * pd = (float *) (d + e * d_nb1 + t * d_nb2);
-    for (int64_t i = threadIdx.x; i < ne0; i += blockDim.x) pd[i] = pa[i] + pb[i];
+    const int64_t i = ((int64_t) blockIdx.y * blockDim.x + threadIdx.x) * (vec ? 4 : 1);
+    if (i >= ne0) return;
+    if (vec) {
+        const float4 x = *(const float4 *) (pa + i), y = *(const float4 *) (pb + i);
+        *(float4 *) (pd + i) = make_float4(x.x + y.x, x.y + y.y, x.z + y.z, x.w + y.w);
+    } else pd[i] = pa[i] + pb[i];
 }
 
 // ------------------------------------------------------------------ SUM_ROWS / CLAMP
@@ -128,6 +139,18 @@ __global__ void __launch_bounds__(128) mul_mat_f_kernel(const char * w, const fl
     const T * wr = (const T *) (w + m * w_nb1);
     pdl_wait();
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (std::is_same<T, float>::value && nc == 1 && K % 4 == 0 && (((uintptr_t) wr | (uintptr_t) (x + n0 * x_ld)) % 16) == 0) {
+        // decode: the router matrix of a MoE layer (f32 [n_embd, n_expert]) times one column: 128-bit loads, four in flight
+        const float4 * w4 = (const float4 *) wr; const float4 * x4 = (const float4 *) (x + n0 * x_ld);
+        const int64_t K4 = K / 4;
+        float a0 = 0.0f;
+#pragma unroll 4
+        for (int64_t k = threadIdx.x; k < K4; k += blockDim.x) {
+            const float4 a = w4[k], b = x4[k];
+            a0 += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+        }
+        acc[0] = a0;
+    } else
     for (int64_t k = threadIdx.x; k < K; k += blockDim.x) {
         const float wv = w_as_f32<T>(wr[k]);
 #pragma unroll
@@ -160,8 +183,13 @@ extern "C" int b200_add_id(const b200_tensor * a, const b200_tensor * b, const b
     if (a->ne[1] * a->ne[2] > 0x7fffffff) return B200_ERR_UNSUPPORTED;
     if (VALIDATE_ONLY(stream)) return B200_OK;
     if (nelements(*d) == 0) return B200_OK;
-    add_id_kernel<<<(unsigned) (a->ne[1] * a->ne[2]), 256, 0, (cudaStream_t) stream>>>((const char *) a->data, (const char *) b->data, (const char *) ids->data, (char *) d->data,
-        a->ne[0], a->ne[1], a->nb[1], a->nb[2], b->nb[1], ids->nb[0], ids->nb[1], d->nb[1], d->nb[2]);
+    const int vec = a->ne[0] % 4 == 0 && (((uintptr_t) a->data | (uintptr_t) b->data | (uintptr_t) d->data) % 16) == 0 &&
+                    (a->nb[1] | a->nb[2] | b->nb[1] | d->nb[1] | d->nb[2]) % 16 == 0;
+    const int64_t per_block = 256 * (vec ? 4 : 1);
+    if ((a->ne[0] + per_block - 1) / per_block > 65535) return B200_ERR_UNSUPPORTED;
+    dim3 grid((unsigned) (a->ne[1] * a->ne[2]), (unsigned) ((a->ne[0] + per_block - 1) / per_block));
+    add_id_kernel<<<grid, 256, 0, (cudaStream_t) stream>>>((const char *) a->data, (const char *) b->data, (const char *) ids->data, (char *) d->data,
+        a->ne[0], a->ne[1], a->nb[1], a->nb[2], b->nb[1], ids->nb[0], ids->nb[1], d->nb[1], d->nb[2], vec);
     count_launch();
     return check_launch("add_id");
 }

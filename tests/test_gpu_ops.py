@@ -153,6 +153,6 @@ def test_flash_attn_decode(orc, kv_type, D, H, H_kv, n_q, n_kv, extras):
                        C.c_int64(n_kv), C.c_float(scale), C.c_float(max_bias), C.c_float(softcap))
     # reference gate: NMSE <= 5e-4 (tests/test-backend-ops.cpp:6082-6084); the f32 vector kernel is far tighter.  Many query
     # positions over an f16 cache run on the tensor cores (Q and P rounded to f16, f32 accumulation): 2e-6
-    dec_mma = bool(int(os.environ.get("B200_FATTN_DECODE_MMA", "1"))) and n_kv >= 1024 and D in (64, 128)   # tensor-core decode kernel (long contexts)
+    dec_mma = bool(int(os.environ.get("B200_FATTN_DECODE_MMA", "1"))) and n_kv >= (256 if n_q * (H // H_kv) >= 4 else 1024) and D in (64, 128)   # tensor-core decode kernel (long contexts; GQA groups from 256 positions)
     mma = ((n_q >= 16 and extras in ("plain", "mask")) or (dec_mma and extras in ("plain", "mask", "mask+sinks"))) and n_kv % 2 == 0
     assert orc.orc_nmse(ptr(want), ptr(np.ascontiguousarray(got)), C.c_size_t(want.size)) < (2e-6 if mma else 1e-8)
