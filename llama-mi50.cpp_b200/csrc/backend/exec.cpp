@@ -457,6 +457,48 @@ int run_fused(exec_state & st, ggml_cgraph * g, int i, bool fusion, int node_lim
                 }
             }
         }
+        // MoE expert matmuls (reference fusions: ggml-cuda.cu:3783-3837; graph: src/llama-graph.cpp build_moe_ffn)
+        if (n->op == GGML_OP_MUL_MAT_ID && !is_split_tensor(n->src[0])) {
+            const ggml_tensor * ids = n->src[2];
+            // {MUL_MAT_ID(up), ADD_ID(up_b), MUL_MAT_ID(gate), ADD_ID(gate_b), GLU}: one GEMV launch reads the up row and the gate
+            // row of an expert, adds both expert biases and applies the GLU (gpt-oss: SWIGLU_OAI)
+            if (i + 4 < node_limit) {
+                ggml_tensor * a1 = g->nodes[i + 1]; ggml_tensor * m2 = g->nodes[i + 2]; ggml_tensor * a2 = g->nodes[i + 3]; ggml_tensor * glu = g->nodes[i + 4];
+                if (a1->op == GGML_OP_ADD_ID && a1->src[0] == n && a1->src[2] == ids &&
+                    m2->op == GGML_OP_MUL_MAT_ID && m2->src[1] == n->src[1] && m2->src[2] == ids && m2->src[0]->type == n->src[0]->type &&
+                    !is_split_tensor(m2->src[0]) && a2->op == GGML_OP_ADD_ID && a2->src[0] == m2 && a2->src[2] == ids &&
+                    glu->op == GGML_OP_GLU && glu->src[0] && glu->src[1] && glu->op_params[1] == 0 &&
+                    ((glu->src[0] == a2 && glu->src[1] == a1) || (glu->src[0] == a1 && glu->src[1] == a2)) &&
+                    ggml_node_has_n_uses(g, i, 1) && ggml_node_has_n_uses(g, i + 1, 1) && ggml_node_has_n_uses(g, i + 2, 1) && ggml_node_has_n_uses(g, i + 3, 1) &&
+                    same_shape(n, m2) && same_shape(n, a1) && same_shape(n, a2) && same_shape(n, glu) && same_shape(n->src[0], m2->src[0])) {
+                    const bool gate_second = glu->src[0] == a2;                 // glu(gate, up): src[0] is the activated operand
+                    const ggml_tensor * gate_mm = gate_second ? m2 : n;  const ggml_tensor * up_mm = gate_second ? n : m2;
+                    const ggml_tensor * gate_b = gate_second ? a2->src[1] : a1->src[1];
+                    const ggml_tensor * up_b = gate_second ? a1->src[1] : a2->src[1];
+                    float alpha, limit; memcpy(&alpha, (const float *) glu->op_params + 2, 4); memcpy(&limit, (const float *) glu->op_params + 3, 4);
+                    ggml_tensor tmp = *glu;
+                    tmp.op = GGML_OP_MUL_MAT_ID; tmp.src[0] = up_mm->src[0]; tmp.src[1] = n->src[1]; tmp.src[2] = const_cast<ggml_tensor *>(ids);
+                    exec_state probe = st; probe.validate = true;
+                    if (run_mul_mat(probe, &tmp, up_b, gate_mm->src[0], gate_b, (int) ggml_get_glu_op(glu), alpha, limit) == B200_OK) {
+                        run_mul_mat(st, &tmp, up_b, gate_mm->src[0], gate_b, (int) ggml_get_glu_op(glu), alpha, limit);
+                        return 5;
+                    }
+                }
+            }
+            // {MUL_MAT_ID, ADD_ID}: the expert bias rides in the GEMV epilogue
+            if (i + 1 < node_limit) {
+                ggml_tensor * a1 = g->nodes[i + 1];
+                if (a1->op == GGML_OP_ADD_ID && a1->src[0] == n && a1->src[2] == ids && ggml_node_has_n_uses(g, i, 1) && same_shape(a1, n)) {
+                    ggml_tensor tmp = *a1;
+                    tmp.op = GGML_OP_MUL_MAT_ID; tmp.src[0] = n->src[0]; tmp.src[1] = n->src[1]; tmp.src[2] = const_cast<ggml_tensor *>(ids);
+                    exec_state probe = st; probe.validate = true;
+                    if (run_mul_mat(probe, &tmp, a1->src[1], nullptr, nullptr, B200_GLU_NONE, 0, 0) == B200_OK) {
+                        run_mul_mat(st, &tmp, a1->src[1], nullptr, nullptr, B200_GLU_NONE, 0, 0);
+                        return 2;
+                    }
+                }
+            }
+        }
         // {MUL_MAT, ADD} with many columns: the residual stream rides in the epilogue of the tensor-core GEMM
         if (n->op == GGML_OP_MUL_MAT && !is_split_tensor(n->src[0]) && i + 1 < node_limit && n->ne[1] > 8 && n->ne[2] == 1 && n->ne[3] == 1) {
             ggml_tensor * add = g->nodes[i + 1];

@@ -77,6 +77,7 @@ __global__ void __launch_bounds__(32 * NW) mmvq_generic_kernel(const mmvq_params
     for (int c = 0; c < NCOLS; ++c) { acc[c] = 0.0f; accg[c] = 0.0f; }
 
     const int64_t nunits = p.K / 32;
+#pragma unroll 4                                       // a lane's units are independent: their weight bytes are requested together
     for (int64_t u = lane; u < nunits; u += 32) {
         unit_w w;
         F::unpack(wrow, u, w);
