@@ -295,6 +295,13 @@ B200_API int b200_soft_max(const b200_tensor * x, const b200_tensor * mask, cons
 B200_API int b200_argsort(const b200_tensor * x, const b200_tensor * dst, int order, void * stream);
 /* TOP_K: dst i32 [k, rows] = indices of the k largest values of each row (descending) */
 B200_API int b200_top_k(const b200_tensor * x, const b200_tensor * dst, void * stream);
+/* fused routing (reference ggml-cuda/topk-moe.cu:314, softmax over the selected logits): logits f32 [n_expert <= 512, n_tok];
+ * ids i32 [n_used, n_tok] (row stride free: the first n_used slots of an ARGSORT row) = the n_used largest logits in
+ * descending order (lowest index first on ties); weights f32 [n_used, n_tok] = softmax of those logits */
+B200_API int b200_topk_moe(const b200_tensor * logits, const b200_tensor * ids, const b200_tensor * weights, void * stream);
+/* weighted sum over the selected experts (the MUL + VIEWs + ADDs at the end of build_moe_ffn): x f32 [n, n_used, n_tok],
+ * w f32 [1, n_used, n_tok], dst f32 [n, n_tok] = sum_e x[:, e, t] * w[e, t] (products rounded, added left to right) */
+B200_API int b200_moe_weighted_sum(const b200_tensor * x, const b200_tensor * w, const b200_tensor * dst, void * stream);
 /* ADD_ID: dst[:, e, t] = a[:, e, t] + b[:, ids[e, t]]; a f32 [n, n_used, n_tok], b f32 [n, n_expert], ids i32 [n_used, n_tok] (strided) */
 B200_API int b200_add_id(const b200_tensor * a, const b200_tensor * b, const b200_tensor * ids, const b200_tensor * dst, void * stream);
 /* SUM_ROWS: dst[0, i1, i2, i3] = sum over ne0; CLAMP: dst = min(max(x, lo), hi) (contiguous) */

@@ -457,6 +457,62 @@ int run_fused(exec_state & st, ggml_cgraph * g, int i, bool fusion, int node_lim
                 }
             }
         }
+        // MoE routing with softmax-weight gating (gpt-oss): {ARGSORT desc, VIEW(first n_used), GET_ROWS(probs, selected), RESHAPE,
+        // SOFT_MAX} -> one warp-per-token kernel (reference fusion: ggml_cuda_topk_moe_fusion, ggml-cuda.cu:3122, topk-moe.cu:314)
+        if (n->op == GGML_OP_ARGSORT && i + 4 < node_limit && n->op_params[0] == GGML_SORT_ORDER_DESC) {
+            const ggml_tensor * probs = n->src[0];
+            ggml_tensor * view = g->nodes[i + 1]; ggml_tensor * gr = g->nodes[i + 2]; ggml_tensor * rs = g->nodes[i + 3]; ggml_tensor * sm = g->nodes[i + 4];
+            float sm_scale = 0.0f, sm_bias = 1.0f;
+            if (sm->op == GGML_OP_SOFT_MAX) { memcpy(&sm_scale, (const float *) sm->op_params + 0, 4); memcpy(&sm_bias, (const float *) sm->op_params + 1, 4); }
+            if (view->op == GGML_OP_VIEW && view->src[0] == n && view->view_offs == 0 && view->ne[1] == n->ne[1] && view->ne[2] == 1 && view->ne[3] == 1 &&
+                view->nb[1] == n->nb[1] && gr->op == GGML_OP_GET_ROWS && gr->src[1] == view && gr->src[0]->data == probs->data &&
+                gr->src[0]->type == GGML_TYPE_F32 && gr->src[0]->ne[0] == 1 && gr->src[0]->ne[1] == probs->ne[0] && gr->src[0]->ne[2] == probs->ne[1] &&
+                gr->src[0]->nb[1] == 4 && gr->src[0]->nb[2] == probs->nb[1] &&
+                rs->op == GGML_OP_RESHAPE && rs->src[0] == gr && rs->ne[0] == view->ne[0] && rs->ne[1] == view->ne[1] &&
+                sm->op == GGML_OP_SOFT_MAX && sm->src[0] == rs && !sm->src[1] && !sm->src[2] && sm_scale == 1.0f && sm_bias == 0.0f &&
+                probs->ne[2] == 1 && probs->ne[3] == 1 && ggml_is_contiguous(sm) &&
+                ggml_node_has_n_uses(g, i, 1) && ggml_node_has_n_uses(g, i + 2, 1) && ggml_node_get_use_count(g, i + 3) == 1 &&
+                !(rs->flags & GGML_TENSOR_FLAG_OUTPUT)) {       // (the RESHAPE is a view: ggml_node_has_n_uses declines views)
+                b200_tensor tl = b200_desc(probs), ti = b200_desc(view), tw = b200_desc(sm);
+                if (b200_topk_moe(&tl, &ti, &tw, B200_STREAM_VALIDATE) == B200_OK) {
+                    if (!st.sizing) { B200_KCHECK(b200_topk_moe(&tl, &ti, &tw, st.stream)); st.launches++; }
+                    return 5;
+                }
+            }
+        }
+        // weighted sum over the selected experts: {MUL(experts, weights), VIEW x n_used, ADD x (n_used - 1)} (build_moe_ffn)
+        if (n->op == GGML_OP_MUL && n->type == GGML_TYPE_F32 && n->src[0] && n->src[1] && n->ne[1] >= 2 && n->ne[1] <= 64 && n->ne[3] == 1 &&
+            n->src[1]->ne[0] == 1 && n->src[1]->ne[1] == n->ne[1] && n->src[1]->ne[2] == n->ne[2] && ggml_are_same_shape(n, n->src[0])) {
+            const int nu = (int) n->ne[1];
+            if (i + 2 * nu - 1 < node_limit) {
+                // the graph lists them in build order of the left fold: v0, v1, ADD, v2, ADD, ...
+                bool ok = ggml_node_has_n_uses(g, i, nu);
+                const ggml_tensor * views[64] = {nullptr};
+                const ggml_tensor * acc = nullptr;
+                int next = 1, nviews = 0;
+                for (int j = i + 1; ok && j < i + 2 * nu; ++j) {
+                    const ggml_tensor * t = g->nodes[j];
+                    if (t->op == GGML_OP_VIEW) {
+                        const size_t e = n->nb[1] ? t->view_offs / n->nb[1] : 0;
+                        ok = t->src[0] == n && e < (size_t) nu && !views[e] && t->view_offs == e * n->nb[1] && t->ne[0] == n->ne[0] && t->ne[1] == n->ne[2] &&
+                             t->ne[2] == 1 && t->ne[3] == 1 && t->nb[1] == n->nb[2] && ggml_node_get_use_count(g, j) == 1 && !(t->flags & GGML_TENSOR_FLAG_OUTPUT);
+                        if (ok) { views[e] = t; ++nviews; }
+                    } else if (t->op == GGML_OP_ADD) {
+                        const ggml_tensor * lhs = acc ? acc : views[0];
+                        ok = lhs && next < nu && views[next] && t->src[0] == lhs && t->src[1] == views[next] && (next == nu - 1 || ggml_node_has_n_uses(g, j, 1));
+                        acc = t; ++next;
+                    } else ok = false;
+                }
+                ok = ok && nviews == nu && next == nu && acc;
+                if (ok) {
+                    b200_tensor tx = b200_desc(n->src[0]), tw = b200_desc(n->src[1]), td = b200_desc(acc);
+                    if (b200_moe_weighted_sum(&tx, &tw, &td, B200_STREAM_VALIDATE) == B200_OK) {
+                        if (!st.sizing) { B200_KCHECK(b200_moe_weighted_sum(&tx, &tw, &td, st.stream)); st.launches++; }
+                        return 2 * nu;
+                    }
+                }
+            }
+        }
         // MoE expert matmuls (reference fusions: ggml-cuda.cu:3783-3837; graph: src/llama-graph.cpp build_moe_ffn)
         if (n->op == GGML_OP_MUL_MAT_ID && !is_split_tensor(n->src[0])) {
             const ggml_tensor * ids = n->src[2];

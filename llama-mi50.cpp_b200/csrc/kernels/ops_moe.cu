@@ -163,9 +163,101 @@ __global__ void __launch_bounds__(128) mul_mat_f_kernel(const char * w, const fl
     if (threadIdx.x < nc) d[(n0 + threadIdx.x) * d_ld + m] = part[0][threadIdx.x] + part[1][threadIdx.x] + part[2][threadIdx.x] + part[3][threadIdx.x];
 }
 
+// ------------------------------------------------------------------ fused routing of a MoE layer (softmax-weight gating)
+// Replaces {ARGSORT desc, VIEW(first n_used), GET_ROWS(probs, selected), SOFT_MAX} (reference fusion: ggml-cuda/topk-moe.cu:314,
+// "delayed softmax" variant; graph: src/llama-graph.cpp build_moe_ffn, gpt-oss).  One warp per token: the logits of all experts
+// live in registers (lane l holds experts l, l + 32, ...), n_used rounds of warp arg-max (the lowest index wins a tie) pick the
+// experts in descending order, then a softmax over the picked values.  ids go to the first n_used slots of the ARGSORT row
+// (the only part of it the graph reads), weights to the SOFT_MAX output.
+template <int EPT>
+__global__ void __launch_bounds__(128) topk_moe_kernel(const float * logits, int32_t * ids, float * weights, int n_expert, int n_used, int64_t n_tok,
+                                                       int64_t l_row, int64_t i_row, int64_t w_row) {
+    pdl_launch_dependents();
+    const int lane = threadIdx.x & 31;
+    const int64_t t = (int64_t) blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (t >= n_tok) return;
+    pdl_wait();
+    const float * row = logits + t * l_row;
+    float v[EPT];
+#pragma unroll
+    for (int i = 0; i < EPT; ++i) { const int e = lane + 32 * i; v[i] = e < n_expert ? row[e] : -INFINITY; }
+    float mine = -INFINITY;                              // lane k keeps the k-th picked value (n_used <= 32)
+    for (int k = 0; k < n_used; ++k) {
+        float bv = -INFINITY; int bi = 0x7fffffff;
+#pragma unroll
+        for (int i = 0; i < EPT; ++i) if (v[i] > bv) { bv = v[i]; bi = lane + 32 * i; }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, bv, o); const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+#pragma unroll
+        for (int i = 0; i < EPT; ++i) if (lane + 32 * i == bi) v[i] = -INFINITY;      // taken
+        if (lane == 0) ids[t * i_row + k] = bi;
+        if (lane == k) mine = bv;
+    }
+    const float top = __shfl_sync(0xffffffffu, mine, 0);                              // the row maximum
+    const float e = lane < n_used ? expf(mine - top) : 0.0f;
+    const float sum = warp_sum(e);
+    if (lane < n_used) weights[t * w_row + lane] = e / sum;
+}
+
+// ------------------------------------------------------------------ weighted sum over the selected experts
+// Replaces {MUL(experts, weights), VIEW x n_used, ADD x (n_used - 1)} at the end of build_moe_ffn: dst[:, t] = sum_e experts[:, e, t] * w[e, t],
+// products rounded first and added left to right, exactly like the separate nodes.
+__global__ void __launch_bounds__(256) moe_weighted_sum_kernel(const char * x, const char * w, char * d, int64_t ne0, int n_used,
+                                                               int64_t x_nb1, int64_t x_nb2, int64_t w_nb1, int64_t w_nb2, int64_t d_nb1) {
+    pdl_launch_dependents();
+    const int64_t t = blockIdx.y, i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ne0) return;
+    pdl_wait();
+    float acc = 0.0f;
+    for (int e = 0; e < n_used; ++e) {
+        const float p = __fmul_rn(*(const float *) (x + i * 4 + e * x_nb1 + t * x_nb2), *(const float *) (w + e * w_nb1 + t * w_nb2));
+        acc = e == 0 ? p : __fadd_rn(acc, p);
+    }
+    *(float *) (d + i * 4 + t * d_nb1) = acc;
+}
+
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" int b200_moe_weighted_sum(const b200_tensor * x, const b200_tensor * w, const b200_tensor * d, void * stream) {
+    if (!x || !w || !d) return B200_ERR_ARG;
+    if (x->type != B200_F32 || w->type != B200_F32 || d->type != B200_F32 || x->nb[0] != 4 || d->nb[0] != 4) return B200_ERR_UNSUPPORTED;
+    const int64_t E = x->ne[0], n_used = x->ne[1], n_tok = x->ne[2];
+    if (x->ne[3] != 1 || w->ne[0] != 1 || w->ne[1] != n_used || w->ne[2] != n_tok || w->ne[3] != 1) return B200_ERR_UNSUPPORTED;
+    if (d->ne[0] != E || d->ne[1] != n_tok || d->ne[2] != 1 || d->ne[3] != 1 || n_used < 1 || n_used > 1024 || n_tok > 65535) return B200_ERR_UNSUPPORTED;
+    if (VALIDATE_ONLY(stream)) return B200_OK;
+    if (E == 0 || n_tok == 0) return B200_OK;
+    dim3 grid((unsigned) ((E + 255) / 256), (unsigned) n_tok);
+    moe_weighted_sum_kernel<<<grid, 256, 0, (cudaStream_t) stream>>>((const char *) x->data, (const char *) w->data, (char *) d->data, E, (int) n_used,
+                                                                    x->nb[1], x->nb[2], w->nb[1], w->nb[2], d->nb[1]);
+    count_launch();
+    return check_launch("moe_weighted_sum");
+}
+
+extern "C" int b200_topk_moe(const b200_tensor * logits, const b200_tensor * ids, const b200_tensor * weights, void * stream) {
+    if (!logits || !ids || !weights) return B200_ERR_ARG;
+    if (logits->type != B200_F32 || ids->type != B200_I32 || weights->type != B200_F32 || logits->nb[0] != 4 || ids->nb[0] != 4 || weights->nb[0] != 4) return B200_ERR_UNSUPPORTED;
+    const int64_t n_expert = logits->ne[0], n_tok = logits->ne[1], n_used = ids->ne[0];
+    if (logits->ne[2] != 1 || logits->ne[3] != 1 || ids->ne[1] != n_tok || ids->ne[2] != 1 || ids->ne[3] != 1) return B200_ERR_UNSUPPORTED;
+    if (weights->ne[0] != n_used || weights->ne[1] != n_tok || weights->ne[2] != 1 || weights->ne[3] != 1) return B200_ERR_UNSUPPORTED;
+    if (n_expert < 1 || n_expert > 512 || n_used < 1 || n_used > 32 || n_used > n_expert || n_tok < 1) return B200_ERR_UNSUPPORTED;
+    if (logits->nb[1] % 4 || ids->nb[1] % 4 || weights->nb[1] % 4) return B200_ERR_UNSUPPORTED;
+    if (VALIDATE_ONLY(stream)) return B200_OK;
+    const unsigned blocks = (unsigned) ((n_tok + 3) / 4);
+    cudaStream_t st = (cudaStream_t) stream;
+    const float * pl = (const float *) logits->data; int32_t * pi = (int32_t *) ids->data; float * pw = (float *) weights->data;
+    const int64_t lr = logits->nb[1] / 4, ir = ids->nb[1] / 4, wr = weights->nb[1] / 4;
+    if (n_expert <= 32)       topk_moe_kernel<1><<<blocks, 128, 0, st>>>(pl, pi, pw, (int) n_expert, (int) n_used, n_tok, lr, ir, wr);
+    else if (n_expert <= 128) topk_moe_kernel<4><<<blocks, 128, 0, st>>>(pl, pi, pw, (int) n_expert, (int) n_used, n_tok, lr, ir, wr);
+    else if (n_expert <= 256) topk_moe_kernel<8><<<blocks, 128, 0, st>>>(pl, pi, pw, (int) n_expert, (int) n_used, n_tok, lr, ir, wr);
+    else                      topk_moe_kernel<16><<<blocks, 128, 0, st>>>(pl, pi, pw, (int) n_expert, (int) n_used, n_tok, lr, ir, wr);
+    count_launch();
+    return check_launch("topk_moe");
+}
 
 extern "C" int b200_argsort(const b200_tensor * x, const b200_tensor * dst, int order, void * stream) {
     return argsort_common(x, dst, order, dst ? (int) dst->ne[0] : 0, stream, "argsort");
