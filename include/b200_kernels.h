@@ -146,10 +146,11 @@ typedef struct b200_attn_phase {
     const b200_tensor * pos;         /* i32 [1]: position of the token (RoPE) */
     const b200_tensor * slot;        /* i64 [1]: cache row the token is written to */
     const b200_tensor * mask;        /* f16 [n_kv] (0 / -inf) or NULL */
-    b200_rope_params rope;           /* modes NORMAL(0) / NEOX(2), no YaRN (ext_factor 0, attn_factor 1) */
+    b200_rope_params rope;           /* modes NORMAL(0) / NEOX(2); YaRN as in ggml_rope_ext (ext_factor, attn_factor, beta_fast / beta_slow) */
     float scale;
     b200_tensor dst;                 /* f32 [D*H] */
     const b200_tensor * slot_v;      /* i64 [1]: cache row of V (NULL: same as slot; ggml passes k_idxs / v_idxs separately) */
+    const b200_tensor * sinks;       /* f32 [H] attention sinks (one extra logit per head with no value: gpt-oss), or NULL */
 } b200_attn_phase;
 typedef struct b200_phase {
     int32_t kind;                    /* b200_phase_kind */

@@ -318,7 +318,8 @@ def gemv_fused(x, segs, **kw):
 class AttnPhase(C.Structure):
     _fields_ = [("q", Tensor), ("k_new", Tensor), ("v_new", Tensor), ("k_cache", Tensor), ("v_cache", Tensor),
                 ("pos", C.POINTER(Tensor)), ("slot", C.POINTER(Tensor)), ("mask", C.POINTER(Tensor)),
-                ("rope", RopeParams), ("scale", C.c_float), ("dst", Tensor), ("slot_v", C.POINTER(Tensor))]
+                ("rope", RopeParams), ("scale", C.c_float), ("dst", Tensor), ("slot_v", C.POINTER(Tensor)),
+                ("sinks", C.POINTER(Tensor))]
 
 
 class Phase(C.Structure):

@@ -163,7 +163,9 @@ struct matcher {
             if (g->nodes[j]->op == GGML_OP_FLASH_ATTN_EXT) { f = j; break; }
         if (f < 0) return 0;
         const ggml_tensor * fa = g->nodes[f];
-        if (fa->src[4] || fa->type != GGML_TYPE_F32) return 0;
+        if (fa->type != GGML_TYPE_F32) return 0;
+        const ggml_tensor * sinks = fa->src[4];
+        if (sinks && (sinks->type != GGML_TYPE_F32 || sinks->op != GGML_OP_NONE || sinks->nb[0] != sizeof(float))) return 0;
         float scale, max_bias, softcap;
         memcpy(&scale, (const float *) fa->op_params + 0, 4); memcpy(&max_bias, (const float *) fa->op_params + 1, 4); memcpy(&softcap, (const float *) fa->op_params + 2, 4);
         if (max_bias != 0.0f || softcap != 0.0f) return 0;
@@ -294,7 +296,8 @@ struct matcher {
         memcpy(&a.rope.attn_factor, p + 8, 4); memcpy(&a.rope.beta_fast, p + 9, 4); memcpy(&a.rope.beta_slow, p + 10, 4);
         a.scale = scale;
         a.dst = vec_desc(fa->data, D * H);
-        if ((a.rope.mode != 0 && a.rope.mode != 2) || a.rope.ext_factor != 0.0f || a.rope.attn_factor != 1.0f || a.rope.n_dims > D ||
+        if (sinks) { if (sinks->ne[0] != H || ggml_nelements(sinks) != H) return 0; a.sinks = keep(sinks); }
+        if ((a.rope.mode != 0 && a.rope.mode != 2) || a.rope.n_dims > D ||
             (D != 64 && D != 128) || kc->type != GGML_TYPE_F16 || vc->type != GGML_TYPE_F16) return 0;
 
         // foreign nodes that only read graph inputs (the f32 -> f16 mask cast of the first layer) run BEFORE the projection

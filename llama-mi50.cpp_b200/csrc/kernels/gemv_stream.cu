@@ -252,7 +252,9 @@ static bool gs_build_attn(const b200_attn_phase * a, gs_phase & ph, int & attn_f
     if (!a->pos || a->pos->type != B200_I32 || !a->slot || a->slot->type != B200_I64 || (a->slot_v && a->slot_v->type != B200_I64)) return false;
     if (a->mask && (a->mask->type != B200_F16 || a->mask->nb[0] != 2 || a->mask->ne[0] < n_kv)) return false;
     const b200_rope_params & r = a->rope;
-    if ((r.mode != 0 && r.mode != 2) || r.n_dims <= 0 || r.n_dims % 2 || r.n_dims > D || r.ext_factor != 0.0f || r.attn_factor != 1.0f) return false;
+    if ((r.mode != 0 && r.mode != 2) || r.n_dims <= 0 || r.n_dims % 2 || r.n_dims > D) return false;
+    if (r.ext_factor != 0.0f && (r.freq_scale <= 0.0f || r.freq_base <= 1.0f || r.n_ctx_orig <= 0)) return false;
+    if (a->sinks && (a->sinks->type != B200_F32 || a->sinks->nb[0] != 4 || a->sinks->ne[0] != H)) return false;
     memset(&ph, 0, sizeof(ph));
     ph.kind = 1;
     gs_attn & g = ph.attn;
@@ -264,6 +266,14 @@ static bool gs_build_attn(const b200_attn_phase * a, gs_phase & ph, int & attn_f
     g.D = (int32_t) D; g.H = (int32_t) H; g.H_kv = (int32_t) H_kv; g.n_kv = (int32_t) n_kv;
     g.rope_mode = r.mode; g.n_dims = r.n_dims; g.scale = a->scale;
     g.theta_scale = powf(r.freq_base, -2.0f / (float) r.n_dims); g.freq_scale = r.freq_scale;
+    g.ext_factor = r.ext_factor; g.attn_factor = r.attn_factor;
+    {   // ggml_rope_yarn_corr_dims (reference ggml/src/ggml.c)
+        const float PI = 3.14159265358979323846f;
+        auto corr_dim = [&](float n_rot) { return r.n_dims * logf(r.n_ctx_orig / (n_rot * 2.0f * PI)) / (2.0f * logf(r.freq_base)); };
+        g.corr0 = r.ext_factor != 0.0f ? fmaxf(0.0f, floorf(corr_dim(r.beta_fast))) : 0.0f;
+        g.corr1 = r.ext_factor != 0.0f ? fminf((float) r.n_dims - 1.0f, ceilf(corr_dim(r.beta_slow))) : 1.0f;
+    }
+    g.sinks = a->sinks ? (const float *) a->sinks->data : nullptr;
     attn_floats = std::max(attn_floats, (int) (3 * D + GS_NW * (D + 2)));
     return true;
 }

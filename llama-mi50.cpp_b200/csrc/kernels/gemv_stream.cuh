@@ -55,6 +55,8 @@ struct gs_attn {
     int64_t k_nb1, k_nb2, v_nb1, v_nb2;
     int32_t D, H, H_kv, n_kv, rope_mode, n_dims;
     float scale, theta_scale, freq_scale;
+    float ext_factor, attn_factor, corr0, corr1;           // YaRN (ggml_rope_ext): ramp between interpolated and extrapolated angles
+    const float * sinks;                                    // one extra logit per head (no value), or null
     // tagged shadows of q / k_new / v_new (null: plain) and the index of the phase that produced them; shadow of dst
     const unsigned long long * q_ll; const unsigned long long * k_ll; const unsigned long long * v_ll;
     unsigned long long * dst_ll;
@@ -801,6 +803,19 @@ template <bool PEER>
 __device__ __forceinline__ float gs_attn_ld(const float * base, const unsigned long long * ll, int64_t i, unsigned int tag) {
     return ll ? ll_read<PEER>(ll + i, tag) : __ldcg(base + i);
 }
+// (cos, sin) of the rotation of pair i at position pos, YaRN included (reference ggml-cpu/ops.cpp rope_yarn); one copy, out of line
+static __device__ __noinline__ float2 gs_rope_angle(int pos, float theta_scale, int i, float freq_scale, float ext_factor, float attn_factor, float corr0, float corr1) {
+    const float theta_extrap = (float) pos * powf(theta_scale, (float) i);
+    float theta = freq_scale * theta_extrap, mscale = attn_factor;
+    if (ext_factor != 0.0f) {
+        const float y = ((float) i - corr0) / fmaxf(0.001f, corr1 - corr0);
+        const float ramp_mix = (1.0f - fminf(1.0f, fmaxf(0.0f, y))) * ext_factor;
+        theta = theta * (1.0f - ramp_mix) + theta_extrap * ramp_mix;
+        mscale *= 1.0f + 0.1f * logf(1.0f / freq_scale);
+    }
+    float sn, cs; sincosf(theta, &sn, &cs);
+    return make_float2(cs * mscale, sn * mscale);
+}
 template <int D, bool PEER>
 __device__ __noinline__ void gs_attn_item(unsigned int ltag, unsigned int self_tag, const gs_attn & a, int h, float * sm, int warp, int lane) {
     constexpr int LPP = D / 32, PPB = 32 / LPP, DPL = D / 32;     // lanes per position, positions per batch, dims per lane (V)
@@ -821,8 +836,8 @@ __device__ __noinline__ void gs_attn_item(unsigned int ltag, unsigned int self_t
             float * dst = isk ? s_k : s_q;
             if (i < half_d) {
                 const int i0 = a.rope_mode == 2 ? i : 2 * i, i1 = a.rope_mode == 2 ? i + half_d : 2 * i + 1;
-                const float theta = (float) pos * powf(a.theta_scale, (float) i) * a.freq_scale;
-                float sn, cs; sincosf(theta, &sn, &cs);
+                const float2 csn = gs_rope_angle(pos, a.theta_scale, i, a.freq_scale, a.ext_factor, a.attn_factor, a.corr0, a.corr1);
+                const float cs = csn.x, sn = csn.y;
                 const float x0 = gs_attn_ld<PEER>(src, sll, so + i0, stag), x1 = gs_attn_ld<PEER>(src, sll, so + i1, stag);
                 float y0 = x0 * cs - x1 * sn, y1 = x0 * sn + x1 * cs;
                 if (isk) { y0 = __half2float(__float2half_rn(y0)); y1 = __half2float(__float2half_rn(y1)); }
@@ -924,6 +939,10 @@ __device__ __noinline__ void gs_attn_item(unsigned int ltag, unsigned int self_t
             const float mw = s_part[w * (D + 2) + D];
             const float wgt = mw == -INFINITY ? 0.0f : __expf(mw - M);
             A += wgt * s_part[w * (D + 2) + tid]; L += wgt * s_part[w * (D + 2) + D + 1];
+        }
+        if (a.sinks) {                                            // the sink: one more logit in the softmax, no value
+            const float sk = a.sinks[h], M2 = fmaxf(M, sk), c0 = M == -INFINITY ? 0.0f : __expf(M - M2);
+            A *= c0; L = L * c0 + __expf(sk - M2);
         }
         const float o = A / L;
         a.dst[(int64_t) h * D + tid] = o;

@@ -214,8 +214,8 @@ SHAPES = {
                                       n_expert=128, n_expert_used=4, swa=128, qkv_bias=True,
                                       extra={**_DEEP, "yarn_factor": 32.0, "yarn_orig_ctx": 4096}),
     # test-size models (same graph topology, seconds on a CPU)
-    "tiny-moe-mxfp4": ModelShape("tiny-moe", "gpt-oss", 2, 256, 256, 8, 2, 32, 512, "mxfp4_moe", 512, 10000.0, 1e-5,
-                                  n_expert=8, n_expert_used=2, swa=64, qkv_bias=True),
+    "tiny-moe-mxfp4": ModelShape("tiny-moe", "gpt-oss", 2, 256, 256, 4, 2, 64, 512, "mxfp4_moe", 512, 10000.0, 1e-5,
+                                  n_expert=8, n_expert_used=2, swa=64, qkv_bias=True, extra={"yarn_factor": 4.0, "yarn_orig_ctx": 128}),
     "tiny-q4_0": ModelShape("tiny", "llama", 2, 256, 512, 4, 2, 64, 512, "q4_0", 512, 10000.0),
     "tiny-q4_k_m": ModelShape("tiny-k", "llama", 4, 512, 1024, 8, 2, 64, 1024, "q4_k_m", 512, 10000.0),
     "tiny-q8_0": ModelShape("tiny-q8", "qwen2", 2, 256, 512, 4, 2, 64, 512, "q8_0", 512, 10000.0, 1e-6, qkv_bias=True),
