@@ -142,7 +142,7 @@ enum b200_phase_kind { B200_PHASE_GEMV = 0, B200_PHASE_ATTN = 1,
                        B200_PHASE_NOP = 2 /* nothing to compute (a rank that owns no rows of a matrix); takes part in the barrier */ };
 typedef struct b200_attn_phase {
     b200_tensor q, k_new, v_new;     /* f32 raw projections of the current token: [D*H], [D*H_kv], [D*H_kv] */
-    b200_tensor k_cache, v_cache;    /* f16 [D, n_kv, H_kv] views of the layer's cache (nb[1] = position stride) */
+    b200_tensor k_cache, v_cache;    /* f16 or q8_0 [D, n_kv, H_kv] views of the layer's cache (nb[1] = position stride) */
     const b200_tensor * pos;         /* i32 [1]: position of the token (RoPE) */
     const b200_tensor * slot;        /* i64 [1]: cache row the token is written to */
     const b200_tensor * mask;        /* f16 [n_kv] (0 / -inf) or NULL */

@@ -242,7 +242,7 @@ struct matcher {
         if (sr_v->data != v_leaf->data || sr_v->nb[1] != v_leaf->nb[1] || sr_v->ne[0] != D * H_kv) return 0;
         for (const ggml_tensor * sr : {sr_k, sr_v}) {
             const ggml_tensor * ids = sr->src[1];
-            if (ids->type != GGML_TYPE_I64 || ggml_nelements(ids) != 1 || !is_f32_vec(sr->src[0], D * H_kv) || sr->type != GGML_TYPE_F16) return 0;
+            if (ids->type != GGML_TYPE_I64 || ggml_nelements(ids) != 1 || !is_f32_vec(sr->src[0], D * H_kv) || sr->type != kc->type) return 0;
         }
         if (rq->src[2] || rk->src[2] || rq->src[1] != rk->src[1] || rq->src[1]->type != GGML_TYPE_I32 || ggml_nelements(rq->src[1]) != 1) return 0;
         if (memcmp(rq->op_params, rk->op_params, sizeof(rq->op_params)) != 0) return 0;
@@ -298,7 +298,7 @@ struct matcher {
         a.dst = vec_desc(fa->data, D * H);
         if (sinks) { if (sinks->ne[0] != H || ggml_nelements(sinks) != H) return 0; a.sinks = keep(sinks); }
         if ((a.rope.mode != 0 && a.rope.mode != 2) || a.rope.n_dims > D ||
-            (D != 64 && D != 128) || kc->type != GGML_TYPE_F16 || vc->type != GGML_TYPE_F16) return 0;
+            (D != 64 && D != 128) || kc->type != vc->type || (kc->type != GGML_TYPE_F16 && kc->type != GGML_TYPE_Q8_0)) return 0;
 
         // foreign nodes that only read graph inputs (the f32 -> f16 mask cast of the first layer) run BEFORE the projection
         // phase when what they write cannot disturb it, so that they do not split the chain

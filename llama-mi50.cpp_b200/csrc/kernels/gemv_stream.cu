@@ -241,9 +241,12 @@ static bool gs_build_attn(const b200_attn_phase * a, gs_phase & ph, int & attn_f
     const b200_tensor & q = a->q; const b200_tensor & k = a->k_cache; const b200_tensor & v = a->v_cache;
     const int64_t D = k.ne[0], n_kv = k.ne[1], H_kv = k.ne[2];
     if (D != 64 && D != 128) return false;
-    if (k.type != B200_F16 || v.type != B200_F16 || k.nb[0] != 2 || v.nb[0] != 2 || k.ne[3] != 1 || v.ne[3] != 1) return false;
+    if (k.type != v.type || (k.type != B200_F16 && k.type != B200_Q8_0) || k.ne[3] != 1 || v.ne[3] != 1) return false;
+    if (k.nb[0] != (int64_t) b200_type_size(k.type) || v.nb[0] != k.nb[0]) return false;
     if (v.ne[0] != D || v.ne[1] != n_kv || v.ne[2] != H_kv || n_kv < 1 || H_kv < 1) return false;
-    if (((uintptr_t) k.data | (uintptr_t) v.data) % 16 || k.nb[1] % 16 || k.nb[2] % 16 || v.nb[1] % 16 || v.nb[2] % 16) return false;
+    // f16 rows are read as 16-byte words; q8_0 rows (34-byte blocks) as aligned words around 2-byte aligned block starts
+    const int64_t al = k.type == B200_F16 ? 16 : 2;
+    if (((uintptr_t) k.data | (uintptr_t) v.data) % al || k.nb[1] % al || k.nb[2] % al || v.nb[1] % al || v.nb[2] % al) return false;
     if (q.type != B200_F32 || q.nb[0] != 4 || nelements(q) % D != 0) return false;
     const int64_t H = nelements(q) / D;
     if (H < 1 || H % H_kv != 0) return false;
@@ -274,6 +277,7 @@ static bool gs_build_attn(const b200_attn_phase * a, gs_phase & ph, int & attn_f
         g.corr1 = r.ext_factor != 0.0f ? fminf((float) r.n_dims - 1.0f, ceilf(corr_dim(r.beta_slow))) : 1.0f;
     }
     g.sinks = a->sinks ? (const float *) a->sinks->data : nullptr;
+    g.kv_type = (uint32_t) k.type;
     attn_floats = std::max(attn_floats, (int) (3 * D + GS_NW * (D + 2)));
     return true;
 }

@@ -60,7 +60,7 @@ struct gs_attn {
     // tagged shadows of q / k_new / v_new (null: plain) and the index of the phase that produced them; shadow of dst
     const unsigned long long * q_ll; const unsigned long long * k_ll; const unsigned long long * v_ll;
     unsigned long long * dst_ll;
-    uint32_t q_tag, k_tag, v_tag, _pad;
+    uint32_t q_tag, k_tag, v_tag, kv_type;                 // kv_type: B200_F16 or B200_Q8_0 (rows of 34-byte blocks)
 };
 struct alignas(16) gs_phase {
     int32_t kind;                  // 0 = GEMV, 1 = attention
@@ -823,7 +823,8 @@ __device__ __noinline__ void gs_attn_item(unsigned int ltag, unsigned int self_t
     const int gqa = a.H / a.H_kv, g = h / gqa;
     const int pos = __ldcg(a.pos), slot = (int) __ldcg(a.slot), slot_v = (int) __ldcg(a.slot_v);
     float * s_q = sm, * s_k = sm + D, * s_v = sm + 2 * D, * s_part = sm + 3 * D;      // s_part: [GS_NW][D + 2]
-    // ---- 1. RoPE(q[h]) * scale, RoPE(k_new[g]) and v_new[g] rounded to f16
+    const bool q8 = a.kv_type == B200_Q8_0;
+    // ---- 1. RoPE(q[h]) * scale, RoPE(k_new[g]) and v_new[g] rounded to f16 (f16 cache) or quantised below (q8_0 cache)
     {
         const int half_d = a.n_dims / 2;
         if (tid < D) {                                            // threads 0..D/2-1: q pairs, D/2..D-1: k pairs
@@ -840,21 +841,46 @@ __device__ __noinline__ void gs_attn_item(unsigned int ltag, unsigned int self_t
                 const float cs = csn.x, sn = csn.y;
                 const float x0 = gs_attn_ld<PEER>(src, sll, so + i0, stag), x1 = gs_attn_ld<PEER>(src, sll, so + i1, stag);
                 float y0 = x0 * cs - x1 * sn, y1 = x0 * sn + x1 * cs;
-                if (isk) { y0 = __half2float(__float2half_rn(y0)); y1 = __half2float(__float2half_rn(y1)); }
+                if (isk) { if (!q8) { y0 = __half2float(__float2half_rn(y0)); y1 = __half2float(__float2half_rn(y1)); } }
                 else     { y0 *= a.scale; y1 *= a.scale; }
                 dst[i0] = y0; dst[i1] = y1;
             }
             for (int d = a.n_dims + i; d < D; d += D / 2) {       // dims beyond n_dims pass through
                 const float y = gs_attn_ld<PEER>(src, sll, so + d, stag);
-                dst[d] = isk ? __half2float(__float2half_rn(y)) : y * a.scale;
+                dst[d] = isk ? (q8 ? y : __half2float(__float2half_rn(y))) : y * a.scale;
             }
         } else if (tid < 2 * D) {
             const int d = tid - D;
-            s_v[d] = __half2float(__float2half_rn(gs_attn_ld<PEER>(a.v_new, a.v_ll, (int64_t) g * D + d, ltag + a.v_tag)));
+            const float y = gs_attn_ld<PEER>(a.v_new, a.v_ll, (int64_t) g * D + d, ltag + a.v_tag);
+            s_v[d] = q8 ? y : __half2float(__float2half_rn(y));
         }
     }
     named_bar_sync(3, GS_CON_THREADS);
-    if (h % gqa == 0 && tid < 2 * D) {                            // KV-cache write of the current token (one writer per group)
+    if (q8) {
+        // q8_0 cache: a warp quantises one 32-element block of the new K / V row with the arithmetic of quantize_row_q8_0_ref
+        // (ggml-quants.c:197-223: d = amax / 127, q = roundf(x / d)); the attention below sees what the cache row decodes to
+        if (tid < 2 * D) {
+            const bool isv = tid >= D;
+            const int d = isv ? tid - D : tid;
+            float * sv = isv ? s_v : s_k;
+            const float x = sv[d];
+            float amax = fabsf(x);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+            const float dd = amax / 127.0f;
+            const float id = dd != 0.0f ? 1.0f / dd : 0.0f;
+            const int qv = (int) roundf(x * id);
+            const __half dh = __float2half_rn(dd);
+            sv[d] = __half2float(dh) * (float) qv;
+            if (h % gqa == 0) {                                   // one writer per group
+                char * blk = (isv ? a.v_cache + (int64_t) slot_v * a.v_nb1 + (int64_t) g * a.v_nb2
+                                  : a.k_cache + (int64_t) slot * a.k_nb1 + (int64_t) g * a.k_nb2) + (d >> 5) * 34;
+                if (lane == 0) *(__half *) blk = dh;
+                ((int8_t *) blk)[2 + lane] = (int8_t) qv;
+            }
+        }
+        named_bar_sync(3, GS_CON_THREADS);
+    } else if (h % gqa == 0 && tid < 2 * D) {                     // KV-cache write of the current token (one writer per group)
         const int d = tid < D ? tid : tid - D;
         char * row = tid < D ? a.k_cache + (int64_t) slot * a.k_nb1 + (int64_t) g * a.k_nb2
                              : a.v_cache + (int64_t) slot_v * a.v_nb1 + (int64_t) g * a.v_nb2;
@@ -878,6 +904,26 @@ __device__ __noinline__ void gs_attn_item(unsigned int ltag, unsigned int self_t
             if (p == slot) {
 #pragma unroll
                 for (int i = 0; i < 32; ++i) s += qreg[i] * s_k[qsub * 32 + i];
+            } else if (q8) {
+                // block qsub of row p: 34 bytes from a 2-byte aligned address, read as aligned words + funnel shifts
+                const uintptr_t addr = (uintptr_t) (kb + (int64_t) p * a.k_nb1 + qsub * 34);
+                const uint32_t sh = (uint32_t) (addr & 3) * 8;
+                const uint32_t * wq = (const uint32_t *) (addr & ~(uintptr_t) 3);
+                uint32_t ww[10];
+#pragma unroll
+                for (int u = 0; u < 9; ++u) ww[u] = wq[u];
+                ww[9] = 0u;
+                uint32_t xx[9];
+#pragma unroll
+                for (int u = 0; u < 9; ++u) xx[u] = __funnelshift_r(ww[u], ww[u + 1], sh);
+                const unsigned short db = (unsigned short) (xx[0] & 0xFFFFu);
+#pragma unroll
+                for (int v = 0; v < 8; ++v) {
+                    const uint32_t y = __funnelshift_r(xx[v], xx[v + 1], 16);
+                    s += qreg[4 * v] * (float) (int8_t) (y & 0xFF) + qreg[4 * v + 1] * (float) (int8_t) ((y >> 8) & 0xFF) +
+                         qreg[4 * v + 2] * (float) (int8_t) ((y >> 16) & 0xFF) + qreg[4 * v + 3] * (float) (int8_t) (y >> 24);
+                }
+                s *= __half2float(*(const __half *) &db);
             } else {
                 const uint4 * kr = (const uint4 *) (kb + (int64_t) p * a.k_nb1 + qsub * 64);
 #pragma unroll
@@ -913,6 +959,16 @@ __device__ __noinline__ void gs_attn_item(unsigned int ltag, unsigned int self_t
                 if (pp == slot_v) {
 #pragma unroll
                     for (int i = 0; i < DPL; ++i) acc[i] += pj * s_v[lane * DPL + i];
+                } else if (q8) {
+                    // dims lane * DPL .. of row pp: DPL int8 inside block (lane * DPL) / 32, and the block's scale
+                    const char * blk = vb + (int64_t) pp * a.v_nb1 + ((lane * DPL) >> 5) * 34;
+                    const float dv = pj * __half2float(*(const __half *) blk);
+                    const unsigned short * qp = (const unsigned short *) (blk + 2 + ((lane * DPL) & 31));
+#pragma unroll
+                    for (int i = 0; i < DPL / 2; ++i) {
+                        const unsigned short t = qp[i];
+                        acc[2 * i] += dv * (float) (int8_t) (t & 0xFF); acc[2 * i + 1] += dv * (float) (int8_t) (t >> 8);
+                    }
                 } else {
                     const __half * vr = (const __half *) (vb + (int64_t) pp * a.v_nb1) + lane * DPL;
                     if (DPL == 4) { const uint2 t = *(const uint2 *) vr; const __half2 * hp = (const __half2 *) &t;
