@@ -87,6 +87,17 @@ typedef struct b200_mmvq_args {
 
 B200_API int b200_mmvq_supported(const b200_mmvq_args * a);
 B200_API int b200_mul_mat_vec_q(const b200_mmvq_args * a, void * stream);
+/* MUL_MAT_ID with many tokens (prefill): the (expert slot, token) pairs are bucketed by expert on the device (reference
+ * mm_ids_helper, mmid.cu:28-116) and multiplied in windows of up to 8 pairs of one expert, so an expert matrix is read once per
+ * 8 columns instead of once per column (reference: mmq over expert_bounds, mmq.cu:160-217).  `a` as for b200_mul_mat_vec_q with
+ * ids set and no fused epilogue; scratch: device memory of b200_mul_mat_id_grouped_scratch_size() bytes, 16-byte aligned.
+ * Results are bit-identical to the one-column-per-pair path. */
+/* MUL_MAT with 2-D weights and ANY number of columns in one launch (every 8-column window; no ids, no epilogue, no column
+ * window): the fallback of the tensor-core GEMM for rows that are not 16-byte multiples (reference: mul_mat_vec_q / mmq router,
+ * ggml-cuda.cu:2183-2266) */
+B200_API int    b200_mul_mat_vec_q_wide(const b200_mmvq_args * a, void * stream);
+B200_API size_t b200_mul_mat_id_grouped_scratch_size(const b200_mmvq_args * a);
+B200_API int    b200_mul_mat_id_grouped(const b200_mmvq_args * a, void * scratch, size_t scratch_size, void * stream);
 
 
 /* ---- K4s: streaming fused GEMV (the decode hot path) ---------------------------------------------

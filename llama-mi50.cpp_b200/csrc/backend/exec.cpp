@@ -225,13 +225,33 @@ int run_mul_mat(exec_state & st, const ggml_tensor * dst, const ggml_tensor * bi
 
     const b200_tensor tx = b200_desc(x);
     const size_t q8_bytes = b200_q8_1_buffer_size(&tx, a.xq_ne0_padded);
-    if (st.sizing) { st.need_q8 = std::max(st.need_q8, q8_bytes); return B200_OK; }
+    const bool grouped = ids && !bias && !gate && !gate_bias && dst->ne[1] * dst->ne[2] >= 16 &&
+                         b200_mul_mat_id_grouped(&a, nullptr, 0, B200_STREAM_VALIDATE) == B200_OK;
+    if (st.sizing) {
+        st.need_q8 = std::max(st.need_q8, q8_bytes);
+        if (grouped) st.need_fa = std::max(st.need_fa, b200_mul_mat_id_grouped_scratch_size(&a));
+        return B200_OK;
+    }
     GGML_ASSERT(q8_bytes <= st.ctx->q8_size);
     if (st.q8_src != x || st.q8_src_data != x->data) {
         B200_KCHECK(b200_quantize_q8_1(&tx, st.ctx->q8_scratch, a.xq_ne0_padded, st.stream));
         st.q8_src = x; st.q8_src_data = x->data; st.launches++;
     }
     a.xq = st.ctx->q8_scratch;
+    if (grouped) {      // MUL_MAT_ID of a batch: pairs bucketed by expert, 8 columns per weight read (scratch shared with flash attention:
+                        // both are consumed inside their own op, in stream order)
+        B200_KCHECK(b200_mul_mat_id_grouped(&a, st.ctx->fa_scratch, st.ctx->fa_size, st.stream));
+        st.launches += 2;
+        return B200_OK;
+    }
+    if (nwin > 1 && !ids && !bias && !gate && !gate_bias && x->ne[2] == 1 && x->ne[3] == 1) {      // all windows in one launch
+        a.col_begin = a.col_count = 0;
+        if (b200_mul_mat_vec_q_wide(&a, B200_STREAM_VALIDATE) == B200_OK) {
+            B200_KCHECK(b200_mul_mat_vec_q_wide(&a, st.stream));
+            st.launches++;
+            return B200_OK;
+        }
+    }
     for (int wi = 0; wi < nwin; ++wi) {
         if (nwin > 1) { a.col_begin = wi * 8; a.col_count = (int) std::min<int64_t>(8, ncols - wi * 8); }
         B200_KCHECK(b200_mul_mat_vec_q(&a, st.stream));

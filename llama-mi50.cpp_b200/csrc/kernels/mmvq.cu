@@ -112,6 +112,189 @@ __global__ void __launch_bounds__(32 * NW) mmvq_generic_kernel(const mmvq_params
     }
 }
 
+// ---------------------------------------------------------------- MUL_MAT_ID with many tokens: (expert slot, token) pairs grouped by expert
+// The ids path above multiplies one column per pair: a 512-token batch of a 4-of-128 MoE layer read every expert matrix 16
+// times.  Here the pairs are bucketed by expert first (reference mm_ids_helper, ggml-cuda/mmid.cu:28-116) and cut into windows
+// of up to 8 pairs of ONE expert; a warp then reads a weight row once per window and multiplies it with the window's 8 activation
+// columns (reference: mmq over expert_bounds, mmq.cu:160-217; here still the dp4a GEMV, 8 columns wide).  Every pair's value is
+// computed independently of its window mates, so the bucket order (atomics) does not change a bit of the result.
+struct moe_windows {            // device scratch filled by moe_group_kernel
+    int32_t n_win; int32_t _pad[3];
+    // followed by: int32 win_expert[w_max], win_start[w_max], win_count[w_max], order[n_pairs]
+};
+__global__ void __launch_bounds__(1024) moe_group_kernel(const int32_t * ids, int64_t ids_nb1, int n_used, int n_tok, int n_expert, int w_max, int32_t * scratch) {
+    extern __shared__ int32_t s_cnt[];       // [n_expert] counts, then [n_expert] offsets, then [n_expert] fill
+    int32_t * s_off = s_cnt + n_expert; int32_t * s_fill = s_off + n_expert;
+    moe_windows * hdr = (moe_windows *) scratch;
+    int32_t * win_expert = scratch + 4; int32_t * win_start = win_expert + w_max; int32_t * win_count = win_start + w_max; int32_t * order = win_count + w_max;
+    pdl_launch_dependents();
+    for (int e = threadIdx.x; e < n_expert; e += blockDim.x) { s_cnt[e] = 0; s_fill[e] = 0; }
+    pdl_wait();
+    __syncthreads();
+    const int n_pairs = n_used * n_tok;
+    for (int i = threadIdx.x; i < n_pairs; i += blockDim.x) {
+        const int e = ids[(i % n_used) + (int64_t) (i / n_used) * ids_nb1];
+        if (e >= 0 && e < n_expert) atomicAdd(&s_cnt[e], 1);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int off = 0, nw = 0;
+        for (int e = 0; e < n_expert; ++e) {
+            s_off[e] = off;
+            for (int c = 0; c < s_cnt[e]; c += 8) { win_expert[nw] = e; win_start[nw] = off + c; win_count[nw] = min(8, s_cnt[e] - c); ++nw; }
+            off += s_cnt[e];
+        }
+        hdr->n_win = nw;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < n_pairs; i += blockDim.x) {
+        const int e = ids[(i % n_used) + (int64_t) (i / n_used) * ids_nb1];
+        if (e >= 0 && e < n_expert) order[s_off[e] + atomicAdd(&s_fill[e], 1)] = i;
+    }
+}
+
+// A warp owns RT rows of one window.  K is walked in passes of 32 units (lane = unit); in a pass the lane holds the q8_1 unit of
+// all 8 columns in registers and runs the RT rows against them, so an activation word is loaded once per RT dot products (the
+// first version reloaded it for every row: one load per dp4a, 2.9 ms per MUL_MAT_ID of a 512-token gpt-oss-120B batch).  Units
+// are met in the same order as in the one-column-per-pair kernel and summed by the same warp reduction: bit-identical results.
+template <int TYPE, int NW, int RT>
+__global__ void __launch_bounds__(32 * NW) mmvq_grouped_kernel(const mmvq_params p, const int32_t * scratch, int w_max, int n_used) {
+    using F = fmt<TYPE>;
+    pdl_launch_dependents();
+    const int lane = threadIdx.x;
+    const int64_t row0 = ((int64_t) blockIdx.x * NW + threadIdx.y) * RT;
+    pdl_wait();
+    const int w = blockIdx.y;
+    if (row0 >= p.M || w >= scratch[0]) return;
+    const int32_t * win_expert = scratch + 4; const int32_t * win_start = win_expert + w_max; const int32_t * win_count = win_start + w_max; const int32_t * order = win_count + w_max;
+    const int expert = win_expert[w], start = win_start[w], cnt = win_count[w];
+    const uint8_t * wbase = p.w + (int64_t) expert * p.w_nb2 + row0 * p.w_nb1;
+    int64_t xo[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        const int pair = order[start + min(c, cnt - 1)];
+        xo[c] = (int64_t) ((pair % n_used) % p.ne11) * p.xq_chan + (int64_t) (pair / n_used) * p.xq_samp;
+    }
+    float acc[RT][8];
+#pragma unroll
+    for (int r = 0; r < RT; ++r)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[r][c] = 0.0f;
+    const int64_t nunits = p.K / 32;
+    for (int64_t u = lane; u < nunits; u += 32) {
+        int xv[8][8]; float xd[8]; int su[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const blk_q8_1 * xb = p.xq + xo[c] + u;
+            const int * q = (const int *) xb->qs;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) xv[c][i] = q[i];
+            xd[c] = __low2float(xb->ds);
+            su[c] = 0;
+            if (F::has_min) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) su[c] = __dp4a(0x01010101, xv[c][i], su[c]);
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < RT; ++r) {
+            if (row0 + r < p.M) {
+                unit_w uw;
+                F::unpack(wbase + r * p.w_nb1, u, uw);
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    int s0 = 0, s1 = 0;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) { s0 = __dp4a(uw.v[i], xv[c][i], s0); s1 = __dp4a(uw.v[4 + i], xv[c][4 + i], s1); }
+                    float t = uw.wd[0] * (float) s0 + uw.wd[1] * (float) s1;          // same expression as unit_dot
+                    if (F::has_min) t -= uw.wm * (float) su[c];
+                    acc[r][c] += xd[c] * t;
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < RT; ++r)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[r][c] = warp_sum(acc[r][c]);
+    if (lane == 0) {
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            if (c < cnt) {
+                const int pair = order[start + c];
+                float * d = p.dst + (int64_t) (pair % n_used) * p.dst_chan + (int64_t) (pair / n_used) * p.dst_samp + row0;
+#pragma unroll
+                for (int r = 0; r < RT; ++r) if (row0 + r < p.M) d[r] = acc[r][c];
+            }
+        }
+    }
+}
+
+// MUL_MAT with many columns that the tensor-core GEMM cannot take (rows that are not 16-byte multiples: K = 2880 Q8_0 / MXFP4):
+// all 8-column windows in ONE launch, a warp owning RT rows of a window with the activation units in registers (as above).
+template <int TYPE, int NW, int RT>
+__global__ void __launch_bounds__(32 * NW) mmvq_wide_kernel(const mmvq_params p, int n_cols) {
+    using F = fmt<TYPE>;
+    pdl_launch_dependents();
+    const int lane = threadIdx.x;
+    const int64_t row0 = ((int64_t) blockIdx.x * NW + threadIdx.y) * RT;
+    pdl_wait();
+    const int c0 = blockIdx.y * 8, cnt = min(8, n_cols - c0);
+    if (row0 >= p.M) return;
+    const uint8_t * wbase = p.w + row0 * p.w_nb1;
+    float acc[RT][8];
+#pragma unroll
+    for (int r = 0; r < RT; ++r)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[r][c] = 0.0f;
+    const int64_t nunits = p.K / 32;
+    for (int64_t u = lane; u < nunits; u += 32) {
+        int xv[8][8]; float xd[8]; int su[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const blk_q8_1 * xb = p.xq + (int64_t) (c0 + min(c, cnt - 1)) * p.xq_col + u;
+            const int * q = (const int *) xb->qs;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) xv[c][i] = q[i];
+            xd[c] = __low2float(xb->ds);
+            su[c] = 0;
+            if (F::has_min) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) su[c] = __dp4a(0x01010101, xv[c][i], su[c]);
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < RT; ++r) {
+            if (row0 + r < p.M) {
+                unit_w uw;
+                F::unpack(wbase + r * p.w_nb1, u, uw);
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    int s0 = 0, s1 = 0;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) { s0 = __dp4a(uw.v[i], xv[c][i], s0); s1 = __dp4a(uw.v[4 + i], xv[c][4 + i], s1); }
+                    float t = uw.wd[0] * (float) s0 + uw.wd[1] * (float) s1;
+                    if (F::has_min) t -= uw.wm * (float) su[c];
+                    acc[r][c] += xd[c] * t;
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < RT; ++r)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[r][c] = warp_sum(acc[r][c]);
+    if (lane == 0) {
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+            if (c < cnt) {
+                float * d = p.dst + (int64_t) (c0 + c) * p.dst_col + row0;
+#pragma unroll
+                for (int r = 0; r < RT; ++r) if (row0 + r < p.M) d[r] = acc[r][c];
+            }
+    }
+}
+
 template <int TYPE, int NCOLS>
 static int launch_generic(const mmvq_params & p, bool ids, bool fused, dim3 grid_cs, cudaStream_t st) {
     constexpr int NW = 4;
@@ -228,4 +411,70 @@ extern "C" int b200_mul_mat_vec_q(const b200_mmvq_args * a, void * stream) {
         case B200_Q6_K:  return launch_type<B200_Q6_K>(p, ncols, a->ids != nullptr, fused, g, st);
         default: return B200_ERR_UNSUPPORTED;
     }
+}
+
+// ---- MUL_MAT_ID, pairs grouped by expert (prefill).  Same arguments as b200_mul_mat_vec_q with ids set and no fused epilogue;
+// scratch: b200_mul_mat_id_grouped_scratch_size() bytes of device memory, 16-byte aligned.
+static int64_t moe_w_max(const b200_mmvq_args * a) { return (a->dst.ne[1] * a->dst.ne[2] + 7) / 8 + a->w.ne[2]; }
+extern "C" size_t b200_mul_mat_id_grouped_scratch_size(const b200_mmvq_args * a) {
+    if (!a || !a->ids) return 0;
+    return (size_t) (16 + 4 * (3 * moe_w_max(a) + a->dst.ne[1] * a->dst.ne[2]));
+}
+extern "C" int b200_mul_mat_id_grouped(const b200_mmvq_args * a, void * scratch, size_t scratch_size, void * stream) {
+    if (!b200_mmvq_supported(a) || !a->ids || a->bias || a->gate_w || a->gate_bias) return B200_ERR_UNSUPPORTED;
+    const b200_tensor & w = a->w; const b200_tensor & d = a->dst;
+    const int64_t n_used = d.ne[1], n_tok = d.ne[2], n_expert = w.ne[2], w_max = moe_w_max(a);
+    if (n_expert < 1 || n_expert > 4096 || n_used * n_tok > (1 << 24) || w_max > 65535) return B200_ERR_UNSUPPORTED;
+    if (stream == B200_STREAM_VALIDATE) return B200_OK;
+    if (!scratch || ((uintptr_t) scratch) % 16 || scratch_size < b200_mul_mat_id_grouped_scratch_size(a)) { set_error("mul_mat_id_grouped: scratch too small"); return B200_ERR_ARG; }
+    if (nelements(d) == 0) return B200_OK;
+    mmvq_params p{};
+    p.w = (const uint8_t *) w.data; p.xq = (const blk_q8_1 *) a->xq; p.dst = (float *) d.data;
+    p.K = w.ne[0]; p.M = w.ne[1]; p.w_nb1 = w.nb[1]; p.w_nb2 = w.nb[2];
+    const int64_t bpr = a->xq_ne0_padded / 32;
+    p.xq_chan = bpr; p.xq_samp = bpr * a->x_ne[1]; p.dst_chan = d.nb[1] / 4; p.dst_samp = d.nb[2] / 4; p.ne11 = (int32_t) a->x_ne[1];
+    cudaStream_t st = (cudaStream_t) stream;
+    moe_group_kernel<<<1, 1024, (size_t) 3 * n_expert * 4, st>>>((const int32_t *) a->ids->data, a->ids->nb[1] / 4, (int) n_used, (int) n_tok, (int) n_expert, (int) w_max, (int32_t *) scratch);
+    count_launch();
+    constexpr int NW = 4, RT = 4;
+    dim3 grid((unsigned) ((p.M + NW * RT - 1) / (NW * RT)), (unsigned) w_max), block(32, NW);
+    switch (w.type) {
+        case B200_Q4_0:  mmvq_grouped_kernel<B200_Q4_0, NW, RT><<<grid, block, 0, st>>>(p, (const int32_t *) scratch, (int) w_max, (int) n_used); break;
+        case B200_Q8_0:  mmvq_grouped_kernel<B200_Q8_0, NW, RT><<<grid, block, 0, st>>>(p, (const int32_t *) scratch, (int) w_max, (int) n_used); break;
+        case B200_MXFP4: mmvq_grouped_kernel<B200_MXFP4, NW, RT><<<grid, block, 0, st>>>(p, (const int32_t *) scratch, (int) w_max, (int) n_used); break;
+        case B200_Q4_K:  mmvq_grouped_kernel<B200_Q4_K, NW, RT><<<grid, block, 0, st>>>(p, (const int32_t *) scratch, (int) w_max, (int) n_used); break;
+        case B200_Q6_K:  mmvq_grouped_kernel<B200_Q6_K, NW, RT><<<grid, block, 0, st>>>(p, (const int32_t *) scratch, (int) w_max, (int) n_used); break;
+        default: return B200_ERR_UNSUPPORTED;
+    }
+    count_launch();
+    return check_launch("mmvq_grouped");
+}
+
+// ---- MUL_MAT, 2-D weights, any number of columns, no epilogue: every 8-column window in one launch (the fallback of the
+// tensor-core GEMM for rows that are not 16-byte multiples).  `a` as for b200_mul_mat_vec_q without ids / bias / gate and without
+// a column window; x_ne[2] == x_ne[3] == 1.
+extern "C" int b200_mul_mat_vec_q_wide(const b200_mmvq_args * a, void * stream) {
+    if (!a || a->ids || a->bias || a->gate_w || a->gate_bias || a->col_begin || a->col_count) return B200_ERR_UNSUPPORTED;
+    const b200_tensor & w = a->w; const b200_tensor & d = a->dst;
+    switch (w.type) { case B200_Q4_0: case B200_Q8_0: case B200_MXFP4: case B200_Q4_K: case B200_Q6_K: break; default: return B200_ERR_UNSUPPORTED; }
+    const int64_t K = w.ne[0], M = w.ne[1], N = a->x_ne[1];
+    if (K <= 0 || M <= 0 || N < 1 || K % b200_blck_size(w.type) != 0 || K != a->x_ne[0] || w.ne[2] != 1 || w.ne[3] != 1) return B200_ERR_UNSUPPORTED;
+    if (a->x_ne[2] != 1 || a->x_ne[3] != 1 || w.nb[0] != (int64_t) b200_type_size(w.type) || d.type != B200_F32 || d.nb[0] != 4) return B200_ERR_UNSUPPORTED;
+    if (d.ne[0] != M || d.ne[1] != N || d.ne[2] != 1 || d.ne[3] != 1 || a->xq_ne0_padded % 32 != 0 || a->xq_ne0_padded < K || (N + 7) / 8 > 65535) return B200_ERR_UNSUPPORTED;
+    if (stream == B200_STREAM_VALIDATE) return B200_OK;
+    mmvq_params p{};
+    p.w = (const uint8_t *) w.data; p.xq = (const blk_q8_1 *) a->xq; p.dst = (float *) d.data;
+    p.K = K; p.M = M; p.w_nb1 = w.nb[1]; p.xq_col = a->xq_ne0_padded / 32; p.dst_col = d.nb[1] / 4;
+    constexpr int NW = 4, RT = 4;
+    dim3 grid((unsigned) ((M + NW * RT - 1) / (NW * RT)), (unsigned) ((N + 7) / 8)), block(32, NW);
+    cudaStream_t st = (cudaStream_t) stream;
+    switch (w.type) {
+        case B200_Q4_0:  mmvq_wide_kernel<B200_Q4_0, NW, RT><<<grid, block, 0, st>>>(p, (int) N); break;
+        case B200_Q8_0:  mmvq_wide_kernel<B200_Q8_0, NW, RT><<<grid, block, 0, st>>>(p, (int) N); break;
+        case B200_MXFP4: mmvq_wide_kernel<B200_MXFP4, NW, RT><<<grid, block, 0, st>>>(p, (int) N); break;
+        case B200_Q4_K:  mmvq_wide_kernel<B200_Q4_K, NW, RT><<<grid, block, 0, st>>>(p, (int) N); break;
+        default:         mmvq_wide_kernel<B200_Q6_K, NW, RT><<<grid, block, 0, st>>>(p, (int) N); break;
+    }
+    count_launch();
+    return check_launch("mmvq_wide");
 }
