@@ -84,6 +84,20 @@ __device__ __forceinline__ uint32_t ld_u32_a1(const void * p) {   // byte aligne
     const uint8_t * q = (const uint8_t *) p;
     return (uint32_t) q[0] | ((uint32_t) q[1] << 8) | ((uint32_t) q[2] << 16) | ((uint32_t) q[3] << 24);
 }
+// N consecutive little-endian u32 words from an arbitrarily aligned global address: N + 1 aligned loads and N funnel shifts
+// (byte loads cost four requests per word).  Reads up to 3 bytes before and after the range: inside the row or the buffer's
+// tail slack (tensors are 256-byte aligned with 256 bytes of slack).
+template <int N>
+__device__ __forceinline__ void ld_words_any(const uint8_t * p, uint32_t * out) {
+    const uintptr_t a = (uintptr_t) p;
+    const uint32_t sh = (uint32_t) (a & 3) * 8;
+    const uint32_t * q = (const uint32_t *) (a & ~(uintptr_t) 3);
+    uint32_t w[N + 1];
+#pragma unroll
+    for (int i = 0; i <= N; ++i) w[i] = q[i];
+#pragma unroll
+    for (int i = 0; i < N; ++i) out[i] = __funnelshift_r(w[i], w[i + 1], sh);
+}
 // Programmatic dependent launch (PDL) controls, sm_90+.
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait()              { asm volatile("griddepcontrol.wait;" ::: "memory"); }

@@ -44,8 +44,10 @@ template <> struct fmt<B200_Q8_0> {
     static __device__ __forceinline__ void unpack(const uint8_t * row, int64_t u, unit_w & w) {
         const uint8_t * b = row + u * 34;
         const float d = __half2float(*(const __half *) b);
+        uint32_t q[8];
+        ld_words_any<8>(b + 2, q);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) w.v[i] = (int) ld_u32_a2(b + 2 + 4 * i);
+        for (int i = 0; i < 8; ++i) w.v[i] = (int) q[i];
         w.wd[0] = w.wd[1] = d; w.wm = 0.0f;
     }
 };
@@ -77,8 +79,10 @@ template <> struct fmt<B200_MXFP4> {
     static __device__ __forceinline__ void unpack(const uint8_t * row, int64_t u, unit_w & w) {
         const uint8_t * b = row + u * 17;
         const float d = e8m0_half_to_f32(b[0]);
+        uint32_t q[4];
+        ld_words_any<4>(b + 1, q);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) mxfp4_expand(ld_u32_a1(b + 1 + 4 * i), w.v[i], w.v[4 + i]);
+        for (int i = 0; i < 4; ++i) mxfp4_expand(q[i], w.v[i], w.v[4 + i]);
         w.wd[0] = w.wd[1] = d; w.wm = 0.0f;
     }
 };
