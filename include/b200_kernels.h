@@ -312,15 +312,16 @@ B200_API int b200_top_k(const b200_tensor * x, const b200_tensor * dst, void * s
  * descending order (lowest index first on ties); weights f32 [n_used, n_tok] = softmax of those logits */
 B200_API int b200_topk_moe(const b200_tensor * logits, const b200_tensor * ids, const b200_tensor * weights, void * stream);
 /* weighted sum over the selected experts (the MUL + VIEWs + ADDs at the end of build_moe_ffn): x f32 [n, n_used, n_tok],
- * w f32 [1, n_used, n_tok], dst f32 [n, n_tok] = sum_e x[:, e, t] * w[e, t] (products rounded, added left to right) */
-B200_API int b200_moe_weighted_sum(const b200_tensor * x, const b200_tensor * w, const b200_tensor * dst, void * stream);
+ * w f32 [1, n_used, n_tok], dst f32 [n, n_tok] = sum_e x[:, e, t] * w[e, t] (products rounded, added left to right)
+ * [+ residual f32 [n, n_tok], or NULL: the ADD of the residual stream that follows] */
+B200_API int b200_moe_weighted_sum(const b200_tensor * x, const b200_tensor * w, const b200_tensor * residual, const b200_tensor * dst, void * stream);
 /* ADD_ID: dst[:, e, t] = a[:, e, t] + b[:, ids[e, t]]; a f32 [n, n_used, n_tok], b f32 [n, n_expert], ids i32 [n_used, n_tok] (strided) */
 B200_API int b200_add_id(const b200_tensor * a, const b200_tensor * b, const b200_tensor * ids, const b200_tensor * dst, void * stream);
 /* SUM_ROWS: dst[0, i1, i2, i3] = sum over ne0; CLAMP: dst = min(max(x, lo), hi) (contiguous) */
 B200_API int b200_sum_rows(const b200_tensor * x, const b200_tensor * dst, void * stream);
 B200_API int b200_clamp(const b200_tensor * x, const b200_tensor * dst, float lo, float hi, void * stream);
-/* MUL_MAT with f32 / f16 / bf16 weights [K, M] (2-D) and f32 activations [K, N]: dst f32 [M, N] */
-B200_API int b200_mul_mat_f(const b200_tensor * w, const b200_tensor * x, const b200_tensor * dst, void * stream);
+/* MUL_MAT with f32 / f16 / bf16 weights [K, M] (2-D) and f32 activations [K, N]: dst f32 [M, N] (+ bias f32 [M] per row, or NULL) */
+B200_API int b200_mul_mat_f(const b200_tensor * w, const b200_tensor * x, const b200_tensor * bias, const b200_tensor * dst, void * stream);
 
 /* ---- K7: FLASH_ATTN_EXT decode (fattn-vec.cuh:19-507, fattn-common.cuh:728-779, launch :781-1036)
  * q f32 [D, n_q, H, n_seq]; k,v f16 or q8_0 [D, n_kv, H_kv, n_seq] (row stride = cache stride);

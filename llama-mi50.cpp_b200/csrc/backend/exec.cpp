@@ -350,7 +350,7 @@ int run_node(exec_state & st, const ggml_tensor * n) {
         case GGML_OP_MUL_MAT:
             if (s0->type == GGML_TYPE_F32 || s0->type == GGML_TYPE_F16 || s0->type == GGML_TYPE_BF16) {     // the MoE router matrix
                 if (is_split_tensor(s0)) return B200_ERR_UNSUPPORTED;
-                b200_tensor a = b200_desc(s0), b = b200_desc(s1), d = b200_desc(n); RUN(b200_mul_mat_f(&a, &b, &d, s));
+                b200_tensor a = b200_desc(s0), b = b200_desc(s1), d = b200_desc(n); RUN(b200_mul_mat_f(&a, &b, nullptr, &d, s));
             }
             return run_mul_mat(st, n, nullptr, nullptr, nullptr, B200_GLU_NONE, 0.0f, 0.0f);
         case GGML_OP_MUL_MAT_ID: return run_mul_mat(st, n, nullptr, nullptr, nullptr, B200_GLU_NONE, 0.0f, 0.0f);
@@ -477,6 +477,21 @@ int run_fused(exec_state & st, ggml_cgraph * g, int i, bool fusion, int node_lim
                 }
             }
         }
+        // {MUL_MAT(float weights), ADD(per-row bias)}: the MoE router (ffn_gate_inp + bias)
+        if (n->op == GGML_OP_MUL_MAT && i + 1 < node_limit && !is_split_tensor(n->src[0]) && n->ne[2] == 1 && n->ne[3] == 1 &&
+            (n->src[0]->type == GGML_TYPE_F32 || n->src[0]->type == GGML_TYPE_F16 || n->src[0]->type == GGML_TYPE_BF16)) {
+            ggml_tensor * add = g->nodes[i + 1];
+            if (add->op == GGML_OP_ADD && (add->src[0] == n || add->src[1] == n) && ggml_node_has_n_uses(g, i, 1) && same_shape(add, n)) {
+                const ggml_tensor * other = add->src[0] == n ? add->src[1] : add->src[0];
+                if (other != n && other->type == GGML_TYPE_F32 && other->ne[0] == n->ne[0] && ggml_nelements(other) == n->ne[0] && other->nb[0] == 4) {
+                    b200_tensor tw = b200_desc(n->src[0]), tx = b200_desc(n->src[1]), tb = b200_desc(other), td = b200_desc(add);
+                    if (b200_mul_mat_f(&tw, &tx, &tb, &td, B200_STREAM_VALIDATE) == B200_OK) {
+                        if (!st.sizing) { B200_KCHECK(b200_mul_mat_f(&tw, &tx, &tb, &td, st.stream)); st.launches++; }
+                        return 2;
+                    }
+                }
+            }
+        }
         // MoE routing with softmax-weight gating (gpt-oss): {ARGSORT desc, VIEW(first n_used), GET_ROWS(probs, selected), RESHAPE,
         // SOFT_MAX} -> one warp-per-token kernel (reference fusion: ggml_cuda_topk_moe_fusion, ggml-cuda.cu:3122, topk-moe.cu:314)
         if (n->op == GGML_OP_ARGSORT && i + 4 < node_limit && n->op_params[0] == GGML_SORT_ORDER_DESC) {
@@ -525,10 +540,18 @@ int run_fused(exec_state & st, ggml_cgraph * g, int i, bool fusion, int node_lim
                 }
                 ok = ok && nviews == nu && next == nu && acc;
                 if (ok) {
-                    b200_tensor tx = b200_desc(n->src[0]), tw = b200_desc(n->src[1]), td = b200_desc(acc);
-                    if (b200_moe_weighted_sum(&tx, &tw, &td, B200_STREAM_VALIDATE) == B200_OK) {
-                        if (!st.sizing) { B200_KCHECK(b200_moe_weighted_sum(&tx, &tw, &td, st.stream)); st.launches++; }
-                        return 2 * nu;
+                    // [+ ADD(sum, residual stream)] right behind the fold
+                    const ggml_tensor * out = acc; const ggml_tensor * res = nullptr;
+                    int consumed = 2 * nu;
+                    if (i + consumed < node_limit && ggml_node_has_n_uses(g, i + consumed - 1, 1)) {
+                        const ggml_tensor * add = g->nodes[i + consumed];
+                        const ggml_tensor * other = add->op == GGML_OP_ADD ? (add->src[0] == acc ? add->src[1] : add->src[1] == acc ? add->src[0] : nullptr) : nullptr;
+                        if (other && other != acc && other->type == GGML_TYPE_F32 && ggml_are_same_shape(other, acc) && ggml_are_same_shape(add, acc) && other->nb[0] == 4) { out = add; res = other; ++consumed; }
+                    }
+                    b200_tensor tx = b200_desc(n->src[0]), tw = b200_desc(n->src[1]), td = b200_desc(out), tr; if (res) tr = b200_desc(res);
+                    if (b200_moe_weighted_sum(&tx, &tw, res ? &tr : nullptr, &td, B200_STREAM_VALIDATE) == B200_OK) {
+                        if (!st.sizing) { B200_KCHECK(b200_moe_weighted_sum(&tx, &tw, res ? &tr : nullptr, &td, st.stream)); st.launches++; }
+                        return consumed;
                     }
                 }
             }

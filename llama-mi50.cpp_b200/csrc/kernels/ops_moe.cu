@@ -132,7 +132,7 @@ template <> __device__ __forceinline__ float w_as_f32<float>(const float & v) { 
 template <> __device__ __forceinline__ float w_as_f32<__half>(const __half & v) { return __half2float(v); }
 template <> __device__ __forceinline__ float w_as_f32<__nv_bfloat16>(const __nv_bfloat16 & v) { return __bfloat162float(v); }
 template <typename T>
-__global__ void __launch_bounds__(128) mul_mat_f_kernel(const char * w, const float * x, float * d, int64_t K, int64_t N, int64_t w_nb1, int64_t x_ld, int64_t d_ld) {
+__global__ void __launch_bounds__(128) mul_mat_f_kernel(const char * w, const float * x, const float * bias, float * d, int64_t K, int64_t N, int64_t w_nb1, int64_t x_ld, int64_t d_ld) {
     pdl_launch_dependents();
     const int64_t m = blockIdx.x, n0 = (int64_t) blockIdx.y * 8;
     const int nc = (int) min((int64_t) 8, N - n0);
@@ -160,7 +160,11 @@ __global__ void __launch_bounds__(128) mul_mat_f_kernel(const char * w, const fl
 #pragma unroll
     for (int c = 0; c < 8; ++c) { const float s = warp_sum(acc[c]); if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5][c] = s; }
     __syncthreads();
-    if (threadIdx.x < nc) d[(n0 + threadIdx.x) * d_ld + m] = part[0][threadIdx.x] + part[1][threadIdx.x] + part[2][threadIdx.x] + part[3][threadIdx.x];
+    if (threadIdx.x < nc) {
+        float r = part[0][threadIdx.x] + part[1][threadIdx.x] + part[2][threadIdx.x] + part[3][threadIdx.x];
+        if (bias) r = __fadd_rn(r, bias[m]);               // the ADD of a per-row bias that follows (MoE router: ffn_gate_inp.bias)
+        d[(n0 + threadIdx.x) * d_ld + m] = r;
+    }
 }
 
 // ------------------------------------------------------------------ fused routing of a MoE layer (softmax-weight gating)
@@ -205,8 +209,8 @@ __global__ void __launch_bounds__(128) topk_moe_kernel(const float * logits, int
 // ------------------------------------------------------------------ weighted sum over the selected experts
 // Replaces {MUL(experts, weights), VIEW x n_used, ADD x (n_used - 1)} at the end of build_moe_ffn: dst[:, t] = sum_e experts[:, e, t] * w[e, t],
 // products rounded first and added left to right, exactly like the separate nodes.
-__global__ void __launch_bounds__(256) moe_weighted_sum_kernel(const char * x, const char * w, char * d, int64_t ne0, int n_used,
-                                                               int64_t x_nb1, int64_t x_nb2, int64_t w_nb1, int64_t w_nb2, int64_t d_nb1) {
+__global__ void __launch_bounds__(256) moe_weighted_sum_kernel(const char * x, const char * w, const char * res, char * d, int64_t ne0, int n_used,
+                                                               int64_t x_nb1, int64_t x_nb2, int64_t w_nb1, int64_t w_nb2, int64_t r_nb1, int64_t d_nb1) {
     pdl_launch_dependents();
     const int64_t t = blockIdx.y, i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= ne0) return;
@@ -216,6 +220,7 @@ __global__ void __launch_bounds__(256) moe_weighted_sum_kernel(const char * x, c
         const float p = __fmul_rn(*(const float *) (x + i * 4 + e * x_nb1 + t * x_nb2), *(const float *) (w + e * w_nb1 + t * w_nb2));
         acc = e == 0 ? p : __fadd_rn(acc, p);
     }
+    if (res) acc = __fadd_rn(acc, *(const float *) (res + i * 4 + t * r_nb1));      // the residual stream (the ADD that follows the fold)
     *(float *) (d + i * 4 + t * d_nb1) = acc;
 }
 
@@ -223,8 +228,9 @@ __global__ void __launch_bounds__(256) moe_weighted_sum_kernel(const char * x, c
 
 using namespace b200;
 
-extern "C" int b200_moe_weighted_sum(const b200_tensor * x, const b200_tensor * w, const b200_tensor * d, void * stream) {
+extern "C" int b200_moe_weighted_sum(const b200_tensor * x, const b200_tensor * w, const b200_tensor * res, const b200_tensor * d, void * stream) {
     if (!x || !w || !d) return B200_ERR_ARG;
+    if (res && (res->type != B200_F32 || res->nb[0] != 4 || res->ne[0] != d->ne[0] || res->ne[1] != d->ne[1] || res->ne[2] != 1 || res->ne[3] != 1)) return B200_ERR_UNSUPPORTED;
     if (x->type != B200_F32 || w->type != B200_F32 || d->type != B200_F32 || x->nb[0] != 4 || d->nb[0] != 4) return B200_ERR_UNSUPPORTED;
     const int64_t E = x->ne[0], n_used = x->ne[1], n_tok = x->ne[2];
     if (x->ne[3] != 1 || w->ne[0] != 1 || w->ne[1] != n_used || w->ne[2] != n_tok || w->ne[3] != 1) return B200_ERR_UNSUPPORTED;
@@ -232,8 +238,8 @@ extern "C" int b200_moe_weighted_sum(const b200_tensor * x, const b200_tensor * 
     if (VALIDATE_ONLY(stream)) return B200_OK;
     if (E == 0 || n_tok == 0) return B200_OK;
     dim3 grid((unsigned) ((E + 255) / 256), (unsigned) n_tok);
-    moe_weighted_sum_kernel<<<grid, 256, 0, (cudaStream_t) stream>>>((const char *) x->data, (const char *) w->data, (char *) d->data, E, (int) n_used,
-                                                                    x->nb[1], x->nb[2], w->nb[1], w->nb[2], d->nb[1]);
+    moe_weighted_sum_kernel<<<grid, 256, 0, (cudaStream_t) stream>>>((const char *) x->data, (const char *) w->data, res ? (const char *) res->data : nullptr, (char *) d->data,
+                                                                    E, (int) n_used, x->nb[1], x->nb[2], w->nb[1], w->nb[2], res ? res->nb[1] : 0, d->nb[1]);
     count_launch();
     return check_launch("moe_weighted_sum");
 }
@@ -307,8 +313,9 @@ extern "C" int b200_clamp(const b200_tensor * x, const b200_tensor * d, float lo
     return check_launch("clamp");
 }
 
-extern "C" int b200_mul_mat_f(const b200_tensor * w, const b200_tensor * x, const b200_tensor * d, void * stream) {
+extern "C" int b200_mul_mat_f(const b200_tensor * w, const b200_tensor * x, const b200_tensor * bias, const b200_tensor * d, void * stream) {
     if (!w || !x || !d) return B200_ERR_ARG;
+    if (bias && (bias->type != B200_F32 || bias->nb[0] != 4 || bias->ne[0] != w->ne[1] || nelements(*bias) != w->ne[1])) return B200_ERR_UNSUPPORTED;
     if (w->type != B200_F32 && w->type != B200_F16 && w->type != B200_BF16) return B200_ERR_UNSUPPORTED;
     if (x->type != B200_F32 || d->type != B200_F32 || w->nb[0] != (int64_t) b200_type_size(w->type) || x->nb[0] != 4 || d->nb[0] != 4) return B200_ERR_UNSUPPORTED;
     if (w->ne[2] != 1 || w->ne[3] != 1 || x->ne[2] != 1 || x->ne[3] != 1 || d->ne[2] != 1 || d->ne[3] != 1) return B200_ERR_UNSUPPORTED;
@@ -319,10 +326,11 @@ extern "C" int b200_mul_mat_f(const b200_tensor * w, const b200_tensor * x, cons
     dim3 grid((unsigned) w->ne[1], (unsigned) ((x->ne[1] + 7) / 8));
     cudaStream_t st = (cudaStream_t) stream;
     const char * pw = (const char *) w->data; const float * px = (const float *) x->data; float * pd = (float *) d->data;
+    const float * pb = bias ? (const float *) bias->data : nullptr;
     switch (w->type) {
-        case B200_F32: mul_mat_f_kernel<float><<<grid, 128, 0, st>>>(pw, px, pd, w->ne[0], x->ne[1], w->nb[1], x->nb[1] / 4, d->nb[1] / 4); break;
-        case B200_F16: mul_mat_f_kernel<__half><<<grid, 128, 0, st>>>(pw, px, pd, w->ne[0], x->ne[1], w->nb[1], x->nb[1] / 4, d->nb[1] / 4); break;
-        default:       mul_mat_f_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>(pw, px, pd, w->ne[0], x->ne[1], w->nb[1], x->nb[1] / 4, d->nb[1] / 4); break;
+        case B200_F32: mul_mat_f_kernel<float><<<grid, 128, 0, st>>>(pw, px, pb, pd, w->ne[0], x->ne[1], w->nb[1], x->nb[1] / 4, d->nb[1] / 4); break;
+        case B200_F16: mul_mat_f_kernel<__half><<<grid, 128, 0, st>>>(pw, px, pb, pd, w->ne[0], x->ne[1], w->nb[1], x->nb[1] / 4, d->nb[1] / 4); break;
+        default:       mul_mat_f_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>(pw, px, pb, pd, w->ne[0], x->ne[1], w->nb[1], x->nb[1] / 4, d->nb[1] / 4); break;
     }
     count_launch();
     return check_launch("mul_mat_f");
