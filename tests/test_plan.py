@@ -51,3 +51,27 @@ def test_decode_graph_is_planned_as_chain(plan_check, key, tmp_path):
     assert len(glu) == L and all("norm=1" in ln for ln in glu)
     if shape.qkv_bias:
         assert all("bias=1" in ln for ln in qkv)
+
+
+def test_gpt_oss_attention_block_is_planned_as_chain(plan_check, tmp_path):
+    """gpt-oss (reference src/models/openai-moe-iswa.cpp): attention sinks, YaRN RoPE, q/k/v/o biases and sliding-window masks do
+    not keep the attention block out of the chain: per layer one qkv phase (norm fused, 3 biased segments), one attention
+    phase and the wo phase; the MoE part of the layer stays plain nodes (fused in csrc/backend/exec.cpp)."""
+    from llama_mi50_b200 import gguf_synth as gs
+    shape = gs.SHAPES["tiny-moe-mxfp4"]
+    path = str(tmp_path / "tiny-moe.gguf")
+    gs.write_gguf(path, shape)
+    out = subprocess.run([plan_check, path, REF_DIR], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = out.stdout.splitlines()
+    m = re.search(r"summary phases (\d+) attn (\d+) plain_compute_nodes (\d+) scratch_floats (\d+)", lines[-1])
+    phases, attn, plain, scratch = map(int, m.groups())
+    L = shape.n_layer
+    assert attn == L
+    assert phases == 3 * L + 1                      # qkv, attention, wo per layer + the logits matmul
+    assert scratch == shape.head_dim * (shape.n_head + 2 * shape.n_head_kv)
+    qkv = [ln for ln in lines if ln.startswith("PHASE gemv") and "segs=3" in ln]
+    assert len(qkv) == L and all("norm=1" in ln and "bias=1" in ln for ln in qkv)
+    plain_ops = {ln.split()[1] for ln in lines if ln.startswith("NODE")}
+    assert {"MUL_MAT_ID", "ADD_ID", "ARGSORT", "SOFT_MAX", "GLU"} <= plain_ops      # the MoE part: plain nodes for exec.cpp's fusions
+    assert "ROPE" not in plain_ops and "FLASH_ATTN_EXT" not in plain_ops and "SET_ROWS" not in plain_ops
