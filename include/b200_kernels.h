@@ -175,7 +175,9 @@ B200_API int          b200_chain_launch(b200_chain * chain, void * stream);
 B200_API void         b200_chain_destroy(b200_chain * chain);
 /* flags at create time (tuning / debug): bit 0 consumers skip the dot products (bandwidth probe), bit 2 per-phase globaltimer
  * stamps of the first and last CTA (tools/timeline_chain.py), bit 3 publish a phase with __threadfence in every thread before
- * the CTA barrier instead of one release RED by thread 0 after it, bits 4-7 ring depth, bits 8-15 stage KiB */
+ * the CTA barrier instead of one release RED by thread 0 after it, bits 4-7 ring depth, bits 8-15 stage KiB, bits 24-27 / 28-30 share
+ * withheld from the CTAs that ran an attention phase in the next / next-but-one phase (steps of 5 % / 1 %; 0 = default 20 % / 4 %,
+ * bits 24-27 = 0xF = even split) */
 B200_API int          b200_chain_debug_read(b200_chain * chain, unsigned long long * out, int n_phases);
 /* same flag: %globaltimer of EVERY CTA when it entered a phase and when its rows were consumed: out[n_phases][b200_chain_grid()][2] */
 B200_API int          b200_chain_debug_read_ctas(b200_chain * chain, unsigned long long * out, int n_phases);

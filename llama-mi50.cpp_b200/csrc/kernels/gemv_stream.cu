@@ -467,10 +467,28 @@ static b200_chain * gs_chain_create(const b200_phase * phases_in, int n_phases, 
     // rows of every segment for every CTA: bytes of a phase are split evenly, a CTA takes the rows that START in its share
     const int grid = gs_sm_count();
     std::vector<int2> ranges((size_t) n_phases * grid * B200_GEMV_MAX_SEG, make_int2(0, 0));
+    // Tuning (flags bits 24-27: s1 in steps of 5 %, bits 28-30: s2 in steps of 1 %): the CTAs that ran an attention phase come
+    // back to the GEMV code with a cold instruction cache and finish the next phases late (profiles/r02b_timeline_ctas_final.txt);
+    // they get (1 - s1) of an even share in the phase right after attention and (1 - s2) in the one after that.
+    // Default 20 % / 4 % (same-box A/B on the 8B chain: 567.1 -> 571.1 tok/s; 20-40 % / 4-7 % all within 0.1 %); bits 24-27 = 0xF: even split.
+    const int f1 = (flags >> 24) & 0xF, f2 = (flags >> 28) & 0x7;
+    const double skew1 = f1 == 0xF ? 0.0 : (f1 || f2) ? 0.05 * f1 : 0.20, skew2 = f1 == 0xF ? 0.0 : (f1 || f2) ? 0.01 * f2 : 0.04;
+    std::vector<int64_t> bound((size_t) grid + 1);
     for (int i = 0; i < n_phases; ++i) {
         if (ph[i].kind != 0) continue;
+        int n_attn = 0; double sk = 0.0;
+        if (i >= 1 && ph[i - 1].kind == 1)      { n_attn = std::min(ph[i - 1].attn.H, grid); sk = skew1; }
+        else if (i >= 2 && ph[i - 2].kind == 1) { n_attn = std::min(ph[i - 2].attn.H, grid); sk = skew2; }
+        {
+            double tot_w = 0.0, acc_w = 0.0;
+            for (int c = 0; c < grid; ++c) tot_w += c < n_attn ? 1.0 - sk : 1.0;
+            bound[0] = 0;
+            for (int c = 0; c < grid; ++c) { acc_w += c < n_attn ? 1.0 - sk : 1.0; bound[(size_t) c + 1] = (int64_t) ((double) ph[i].total_bytes * (acc_w / tot_w)); }
+            bound[(size_t) grid] = ph[i].total_bytes;
+            if (sk == 0.0) for (int c = 0; c <= grid; ++c) bound[(size_t) c] = ph[i].total_bytes * (int64_t) c / grid;      // exact integer split
+        }
         for (int c = 0; c < grid; ++c) {
-            const int64_t lo = ph[i].total_bytes * (int64_t) c / grid, hi = ph[i].total_bytes * (int64_t) (c + 1) / grid;
+            const int64_t lo = bound[(size_t) c], hi = bound[(size_t) c + 1];
             for (int s2 = 0; s2 < ph[i].n_ws; ++s2) {
                 const gs_seg & g = ph[i].seg[s2];
                 const int64_t rbw = (int64_t) g.rb * g.nsub, tot = rbw * g.M;
