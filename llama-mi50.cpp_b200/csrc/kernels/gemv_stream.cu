@@ -472,7 +472,8 @@ static b200_chain * gs_chain_create(const b200_phase * phases_in, int n_phases, 
     // they get (1 - s1) of an even share in the phase right after attention and (1 - s2) in the one after that.
     // Default 20 % / 4 % (same-box A/B on the 8B chain: 567.1 -> 571.1 tok/s; 20-40 % / 4-7 % all within 0.1 %); bits 24-27 = 0xF: even split.
     const int f1 = (flags >> 24) & 0xF, f2 = (flags >> 28) & 0x7;
-    const double skew1 = f1 == 0xF ? 0.0 : (f1 || f2) ? 0.05 * f1 : 0.20, skew2 = f1 == 0xF ? 0.0 : (f1 || f2) ? 0.01 * f2 : 0.04;
+    const bool even = f1 == 0xF || (pg && !f1 && !f2);       // row split over peer memory: even unless asked for (not measured there)
+    const double skew1 = even ? 0.0 : (f1 || f2) ? 0.05 * f1 : 0.20, skew2 = even ? 0.0 : (f1 || f2) ? 0.01 * f2 : 0.04;
     std::vector<int64_t> bound((size_t) grid + 1);
     for (int i = 0; i < n_phases; ++i) {
         if (ph[i].kind != 0) continue;
